@@ -1,0 +1,641 @@
+// sm_100a kernels of the BEAR render core.  FP32 throughout (parity bar: max-abs 1e-5 against
+// the CPU oracle), no tensor cores: the path is HBM/L2-bound complex MACs plus shared-memory
+// FFTs (DESIGN.md "Kernels").
+//
+// Signal flow per call of T periods (reference: visr_bear/src/dsp.cpp:117-205):
+//   mix_kernel        x -> per-ear Lagrange-3 delay -> ramped gain mix -> direct bus partials (48 ch)
+//                     x -> ramped gain mix -> diffuse partials (24 ch)          [a2,a3,a4,a7]
+//   hoa_mix_kernel    hoa in -> ramped matrix -> ambisonic bus (16 ch)                 [a10]
+//   decorrelate_kernel  diffuse bus -> overlap-save FFT conv with the decorrelators    [a5]
+//   bus_fdl_kernel    direct partials + static-delayed decorrelator outputs -> 48 ch bus -> rFFT(2B)
+//                     -> frequency-domain delay line; HOA bus (fixed delay commuted in front of
+//                     the decode filters) -> rFFT(2B) -> FDL                           [a6,a8,a12]
+//   cmac_kernel       Y[e] = sum_{l,p} FDL[2l+e][k-p] * H[view][2l+e][p] (+ HOA decode terms),
+//                     for the new view and, in a view-change block, the old one        [a9,a11]
+//   ifft_out_kernel   sum partial spectra -> irFFT -> overlap-save discard -> view crossfade -> out [a9,a13]
+//   carry_kernel      moves histories / table state to the front for the next call
+#include "kernels.cuh"
+
+namespace bearcuda {
+
+// ----------------------------------------------------------------------------------------------
+// small complex helpers
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
+__device__ __forceinline__ float2 cmul(float2 a, float2 b)
+{
+  return make_float2(fmaf(a.x, b.x, -a.y * b.y), fmaf(a.x, b.y, a.y * b.x));
+}
+__device__ __forceinline__ float2 cmul_conj(float2 a, float2 w)  // a * conj(w)
+{
+  return make_float2(fmaf(a.x, w.x, a.y * w.y), fmaf(a.y, w.x, -a.x * w.y));
+}
+// table of exp(-i pi q / M), q in [0, M); q in [M, 2M) by symmetry
+__device__ __forceinline__ float2 ldtw(const float2 *__restrict__ tw, int q, int M)
+{
+  if (q < M) return __ldg(tw + q);
+  float2 w = __ldg(tw + q - M);
+  return make_float2(-w.x, -w.y);
+}
+
+// ----------------------------------------------------------------------------------------------
+// Complex FFT of length M = 2^logM in shared memory: Stockham autosort, radix 4 with a final
+// radix-2 pass when logM is odd.  Natural order in and out, unnormalised.  `a` holds the input,
+// `b` is scratch of the same size; returns the buffer that holds the result.  All threads of
+// the CTA must call it.
+// ----------------------------------------------------------------------------------------------
+template <bool INV>
+__device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int logM, const float2 *__restrict__ tw)
+{
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  int ls = 0;
+  for (; ls + 2 <= logM; ls += 2) {
+    const int Ns = 1 << ls, Q = M >> 2;
+    __syncthreads();
+    for (int j = tid; j < Q; j += nthr) {
+      const int k = j & (Ns - 1);
+      float2 v0 = a[j], v1 = a[j + Q], v2 = a[j + 2 * Q], v3 = a[j + 3 * Q];
+      if (ls > 0) {
+        const int q = k << (logM - 1 - ls);
+        float2 w1 = ldtw(tw, q, M), w2 = ldtw(tw, 2 * q, M), w3 = ldtw(tw, 3 * q, M);
+        if (INV) {
+          v1 = cmul_conj(v1, w1); v2 = cmul_conj(v2, w2); v3 = cmul_conj(v3, w3);
+        } else {
+          v1 = cmul(v1, w1); v2 = cmul(v2, w2); v3 = cmul(v3, w3);
+        }
+      }
+      float2 s02 = cadd(v0, v2), d02 = csub(v0, v2), s13 = cadd(v1, v3), d13 = csub(v1, v3);
+      // forward: -i*d13, inverse: +i*d13
+      float2 r = INV ? make_float2(-d13.y, d13.x) : make_float2(d13.y, -d13.x);
+      const int j0 = ((j - k) << 2) + k;
+      b[j0] = cadd(s02, s13);
+      b[j0 + Ns] = cadd(d02, r);
+      b[j0 + 2 * Ns] = csub(s02, s13);
+      b[j0 + 3 * Ns] = csub(d02, r);
+    }
+    float2 *t = a; a = b; b = t;
+  }
+  if (ls < logM) {
+    const int Ns = 1 << ls, Hh = M >> 1;  // Ns == M/2
+    __syncthreads();
+    for (int j = tid; j < Hh; j += nthr) {
+      const int k = j & (Ns - 1);
+      float2 v0 = a[j], v1 = a[j + Hh];
+      float2 w = ldtw(tw, k << (logM - ls), M);
+      v1 = INV ? cmul_conj(v1, w) : cmul(v1, w);
+      const int j0 = ((j - k) << 1) + k;
+      b[j0] = cadd(v0, v1);
+      b[j0 + Ns] = csub(v0, v1);
+    }
+    float2 *t = a; a = b; b = t;
+  }
+  __syncthreads();
+  return a;
+}
+
+// real-FFT split: Z = FFT_M(x[2n] + i x[2n+1]);  X[k], X[M-k] of the length-2M real transform
+__device__ __forceinline__ void rfft_post(float2 zk, float2 zm, float2 w, float2 &xk, float2 &xm)
+{
+  float2 bc = make_float2(zm.x, -zm.y);
+  float2 e = make_float2(0.5f * (zk.x + bc.x), 0.5f * (zk.y + bc.y));
+  float2 d = csub(zk, bc);
+  float2 o = make_float2(0.5f * d.y, -0.5f * d.x);
+  float2 wo = cmul(w, o);
+  xk = cadd(e, wo);
+  float2 t = csub(e, wo);
+  xm = make_float2(t.x, -t.y);
+}
+// inverse of the above up to a factor 2 (the unnormalised inverse FFT_M then yields 2M x[n])
+__device__ __forceinline__ void irfft_pre(float2 xk, float2 xm, float2 w, float2 &zk, float2 &zm)
+{
+  float2 b = make_float2(xm.x, -xm.y);
+  float2 ev = cadd(xk, b);
+  float2 od = cmul_conj(csub(xk, b), w);
+  zk = make_float2(ev.x - od.y, ev.y + od.x);
+  zm = make_float2(ev.x + od.y, od.x - ev.y);
+}
+
+// Lagrange order-3 coefficients for position s in [1,2) relative to the first of the nodes 0..3
+__device__ __forceinline__ void lagrange3(float s, float c[4])
+{
+  float s1 = s - 1.0f, s2 = s - 2.0f, s3 = s - 3.0f;
+  c[0] = -(s1 * s2 * s3) * (1.0f / 6.0f);
+  c[1] = (s * s2 * s3) * 0.5f;
+  c[2] = -(s * s1 * s3) * 0.5f;
+  c[3] = (s * s1 * s2) * (1.0f / 6.0f);
+}
+// y = sum_j c_j(1.5 + mu) x[-i - j] with i = floor(d + .5), mu = d - i: realised delay d + 1.5
+__device__ __forceinline__ float delayed_read(const float *__restrict__ x, float d)
+{
+  float fi = floorf(d + 0.5f);
+  float c[4];
+  lagrange3(1.5f + (d - fi), c);
+  const float *q = x - (int)fi;
+  float acc = c[0] * q[0];
+  acc = fmaf(c[1], q[-1], acc);
+  acc = fmaf(c[2], q[-2], acc);
+  acc = fmaf(c[3], q[-3], acc);
+  return acc;
+}
+
+// ----------------------------------------------------------------------------------------------
+// Filter table -> partitioned spectra (one-off, at renderer creation).
+// grid: n_filters * P; block: B/4.  out[(f*P + p)*B + bin], scaled.
+// ----------------------------------------------------------------------------------------------
+__global__ void filter_fft_kernel(const float *__restrict__ taps, int taps_len, int B, int logB, int P,
+                                  const float2 *__restrict__ tw, float2 *__restrict__ out, float scale)
+{
+  extern __shared__ float2 sm[];
+  float2 *a = sm, *b = sm + B;
+  const int f = blockIdx.x / P, p = blockIdx.x % P;
+  const float *src = taps + (size_t)f * taps_len;
+  for (int n = threadIdx.x; n < B; n += blockDim.x) {
+    int t0 = p * B + 2 * n;
+    float v0 = (2 * n < B && t0 < taps_len) ? src[t0] : 0.0f;
+    float v1 = (2 * n + 1 < B && t0 + 1 < taps_len) ? src[t0 + 1] : 0.0f;
+    a[n] = make_float2(v0 * scale, v1 * scale);
+  }
+  float2 *z = fft_shared<false>(a, b, B, logB, tw);
+  float2 *dst = out + (size_t)blockIdx.x * B;
+  for (int k = threadIdx.x; k <= B / 2; k += blockDim.x) {
+    if (k == 0) {
+      dst[0] = make_float2(z[0].x + z[0].y, z[0].x - z[0].y);
+    } else {
+      float2 xk, xm;
+      rfft_post(z[k], z[B - k], __ldg(tw + k), xk, xm);
+      dst[k] = xk;
+      dst[B - k] = xm;
+    }
+  }
+}
+
+void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, int logB, int P, const float2 *tw,
+                       float2 *out, float scale, cudaStream_t st)
+{
+  int threads = B / 4 < 32 ? 32 : B / 4;
+  filter_fft_kernel<<<n_filters * P, threads, 2 * B * sizeof(float2), st>>>(taps, taps_len, B, logB, P, tw, out, scale);
+}
+
+// ----------------------------------------------------------------------------------------------
+// mix_kernel: objects + DirectSpeakers onto the 2L direct bus and the L diffuse bus.
+// grid: (T*B/kMixTile, S); block: kMixTile.  One output sample per thread, all 3*24 outputs in
+// registers; the gains of kMixChunk channels are staged in shared memory with their per-block
+// deltas so the inner loop is one FMA for the ramped gain + one FMA per ear.
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
+{
+  // row = one channel: [g0 | dg | q0 | dq] x 24 speakers, padded by 4 floats so that the staging
+  // stores (consecutive channels, same speaker) spread over 8 banks instead of 1
+  __shared__ __align__(16) float sg[kMixChunk][4 * kMaxSpeakers + 4];
+  __shared__ float sd[kMixChunk][4];
+  const int tid = threadIdx.x;
+  const int t = blockIdx.x * kMixTile + tid;
+  const int k = (blockIdx.x * kMixTile) / p.B;
+  const int n = t - k * p.B;
+  const int s = blockIdx.y;
+  const int C = p.N + p.M;
+  const int per = (C + p.S - 1) / p.S;
+  const int c0 = s * per, c1 = min(C, c0 + per);
+  const float invB = 1.0f / (float)p.B;
+  const float rg = (float)(n + p.goff) * invB;
+  const float rd = (float)(n + p.doff) * invB;
+  const int L = p.L;
+
+  float accL[kMaxSpeakers], accR[kMaxSpeakers], accQ[kMaxSpeakers];
+#pragma unroll
+  for (int l = 0; l < kMaxSpeakers; l++) accL[l] = accR[l] = accQ[l] = 0.0f;
+
+  for (int cb = c0; cb < c1; cb += kMixChunk) {
+    const int cnt = min(kMixChunk, c1 - cb);
+    __syncthreads();
+    for (int idx = tid; idx < cnt * kMaxSpeakers; idx += kMixTile) {
+      const int l = idx / cnt, ii = idx - l * cnt, c = cb + ii;
+      float g0 = 0.f, g1 = 0.f, q0 = 0.f, q1 = 0.f;
+      if (l < L) {
+        if (c < p.N) {
+          g0 = p.g_dir[((size_t)k * L + l) * p.N + c];
+          g1 = p.g_dir[((size_t)(k + 1) * L + l) * p.N + c];
+          q0 = p.g_dif[((size_t)k * L + l) * p.N + c];
+          q1 = p.g_dif[((size_t)(k + 1) * L + l) * p.N + c];
+        } else {
+          const int j = c - p.N;
+          g0 = p.g_ds[((size_t)k * L + l) * p.M + j];
+          g1 = p.g_ds[((size_t)(k + 1) * L + l) * p.M + j];
+        }
+      }
+      sg[ii][l] = g0; sg[ii][kMaxSpeakers + l] = g1 - g0;
+      sg[ii][2 * kMaxSpeakers + l] = q0; sg[ii][3 * kMaxSpeakers + l] = q1 - q0;
+    }
+    for (int idx = tid; idx < cnt * 2; idx += kMixTile) {
+      const int ii = idx >> 1, e = idx & 1, c = cb + ii;
+      float d0, d1;
+      if (c < p.N) {
+        d0 = p.d_dir[(size_t)k * 2 * p.N + 2 * c + e];
+        d1 = p.d_dir[(size_t)(k + 1) * 2 * p.N + 2 * c + e];
+      } else {
+        const int j = c - p.N;
+        d0 = p.d_ds[(size_t)k * 2 * p.M + 2 * j + e];
+        d1 = p.d_ds[(size_t)(k + 1) * 2 * p.M + 2 * j + e];
+      }
+      d0 *= p.fs; d1 *= p.fs;
+      sd[ii][2 * e] = d0; sd[ii][2 * e + 1] = d1 - d0;
+    }
+    __syncthreads();
+    for (int ii = 0; ii < cnt; ii++) {
+      const float *xr = p.xin + (size_t)(cb + ii) * p.xs + p.hist + t;
+      const float xl = delayed_read(xr, fmaf(rd, sd[ii][1], sd[ii][0]));
+      const float xR = delayed_read(xr, fmaf(rd, sd[ii][3], sd[ii][2]));
+      const float x0 = __ldg(xr);
+      const float4 *g0v = reinterpret_cast<const float4 *>(sg[ii]);
+      const float4 *dgv = g0v + kMaxSpeakers / 4;
+      const float4 *q0v = g0v + 2 * kMaxSpeakers / 4;
+      const float4 *dqv = g0v + 3 * kMaxSpeakers / 4;
+#pragma unroll
+      for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
+        float4 g0 = g0v[l4], dg = dgv[l4], q0 = q0v[l4], dq = dqv[l4];
+        float g;
+        g = fmaf(rg, dg.x, g0.x); accL[4 * l4 + 0] = fmaf(g, xl, accL[4 * l4 + 0]); accR[4 * l4 + 0] = fmaf(g, xR, accR[4 * l4 + 0]);
+        g = fmaf(rg, dg.y, g0.y); accL[4 * l4 + 1] = fmaf(g, xl, accL[4 * l4 + 1]); accR[4 * l4 + 1] = fmaf(g, xR, accR[4 * l4 + 1]);
+        g = fmaf(rg, dg.z, g0.z); accL[4 * l4 + 2] = fmaf(g, xl, accL[4 * l4 + 2]); accR[4 * l4 + 2] = fmaf(g, xR, accR[4 * l4 + 2]);
+        g = fmaf(rg, dg.w, g0.w); accL[4 * l4 + 3] = fmaf(g, xl, accL[4 * l4 + 3]); accR[4 * l4 + 3] = fmaf(g, xR, accR[4 * l4 + 3]);
+        accQ[4 * l4 + 0] = fmaf(fmaf(rg, dq.x, q0.x), x0, accQ[4 * l4 + 0]);
+        accQ[4 * l4 + 1] = fmaf(fmaf(rg, dq.y, q0.y), x0, accQ[4 * l4 + 1]);
+        accQ[4 * l4 + 2] = fmaf(fmaf(rg, dq.z, q0.z), x0, accQ[4 * l4 + 2]);
+        accQ[4 * l4 + 3] = fmaf(fmaf(rg, dq.w, q0.w), x0, accQ[4 * l4 + 3]);
+      }
+    }
+  }
+  const size_t col = (size_t)p.B + t;
+#pragma unroll
+  for (int l = 0; l < kMaxSpeakers; l++) {
+    if (l < L) {
+      p.cdir[((size_t)s * 2 * L + 2 * l) * p.cs + col] = accL[l];
+      p.cdir[((size_t)s * 2 * L + 2 * l + 1) * p.cs + col] = accR[l];
+      p.qdif[((size_t)s * L + l) * p.cs + col] = accQ[l];
+    }
+  }
+}
+
+void launch_mix(const Layout &p, int T, cudaStream_t st)
+{
+  dim3 grid(T * p.B / kMixTile, p.S);
+  mix_kernel<<<grid, kMixTile, 0, st>>>(p, T);
+}
+
+// ----------------------------------------------------------------------------------------------
+// hoa_mix_kernel: ambisonic bus amb[m][t] = sum_c G[m,c](ramp) hoa_in[c][t]   (dsp.cpp:178-180)
+// grid: T*B/kMixTile; block kMixTile.
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kMixTile) hoa_mix_kernel(Layout p, int T)
+{
+  const int t = blockIdx.x * kMixTile + threadIdx.x;
+  const int k = (blockIdx.x * kMixTile) / p.B;
+  const int n = t - k * p.B;
+  const float rg = (float)(n + p.goff) / (float)p.B;
+  const float *x0 = p.xin + (size_t)(p.N + p.M) * p.xs + p.hist + t;
+  for (int m0 = 0; m0 < p.A; m0 += 16) {
+    float acc[16];
+#pragma unroll
+    for (int i = 0; i < 16; i++) acc[i] = 0.0f;
+    for (int c = 0; c < p.H; c++) {
+      const float x = __ldg(x0 + (size_t)c * p.xs);
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        const int m = m0 + i;
+        if (m < p.A) {
+          const float g0 = __ldg(p.g_hoa + ((size_t)k * p.A + m) * p.H + c);
+          const float g1 = __ldg(p.g_hoa + ((size_t)(k + 1) * p.A + m) * p.H + c);
+          acc[i] = fmaf(fmaf(rg, g1 - g0, g0), x, acc[i]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i++)
+      if (m0 + i < p.A) p.amb[(size_t)(m0 + i) * p.ws + p.B + p.hist + t] = acc[i];
+  }
+}
+
+void launch_hoa_mix(const Layout &p, int T, cudaStream_t st)
+{
+  hoa_mix_kernel<<<T * p.B / kMixTile, kMixTile, 0, st>>>(p, T);
+}
+
+// ----------------------------------------------------------------------------------------------
+// decorrelate_kernel: w[l] = dec[l] (*) q[l], one partition overlap-save (dsp.cpp:61-72,132-135).
+// grid: T*L (l fastest); block: B/4; smem 2*B float2.
+// ----------------------------------------------------------------------------------------------
+__global__ void decorrelate_kernel(Layout p, int T)
+{
+  extern __shared__ float2 sm[];
+  const int M = p.B;
+  float2 *a = sm, *b = sm + M;
+  const int l = blockIdx.x % p.L, k = blockIdx.x / p.L;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  for (int n = tid; n < M; n += nthr) {
+    float2 z = make_float2(0.f, 0.f);
+    for (int s = 0; s < p.S; s++) {
+      const float2 v = reinterpret_cast<const float2 *>(p.qdif + ((size_t)s * p.L + l) * p.cs + (size_t)k * p.B)[n];
+      z.x += v.x; z.y += v.y;
+    }
+    a[n] = z;
+  }
+  float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw);
+  float2 *o = (z == a) ? b : a;
+  const float2 *h = p.h_dec + (size_t)l * M;
+  for (int kk = tid; kk <= M / 2; kk += nthr) {
+    if (kk == 0) {
+      const float2 h0 = __ldg(h);
+      const float x0 = (z[0].x + z[0].y) * h0.x, xM = (z[0].x - z[0].y) * h0.y;
+      o[0] = make_float2(x0 + xM, x0 - xM);
+    } else {
+      const float2 w = __ldg(p.tw + kk);
+      float2 xk, xm, zk, zm;
+      rfft_post(z[kk], z[M - kk], w, xk, xm);
+      xk = cmul(xk, __ldg(h + kk));
+      xm = cmul(xm, __ldg(h + M - kk));
+      irfft_pre(xk, xm, w, zk, zm);
+      o[kk] = zk;
+      o[M - kk] = zm;
+    }
+  }
+  float2 *y = fft_shared<true>(o, z, M, p.logB, p.tw);
+  float2 *dst = reinterpret_cast<float2 *>(p.w + (size_t)l * p.ws + p.B + p.hist + (size_t)k * p.B);
+  for (int n = tid; n < M / 2; n += nthr) dst[n] = y[M / 2 + n];
+}
+
+void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
+{
+  int threads = p.B / 4 < 32 ? 32 : p.B / 4;
+  decorrelate_kernel<<<T * p.L, threads, 2 * p.B * sizeof(float2), st>>>(p, T);
+}
+
+// ----------------------------------------------------------------------------------------------
+// bus_fdl_kernel: assemble the 2B-sample window [block k-1, block k] of one convolver input and
+// write its packed spectrum into the frequency-domain delay line.
+//   bus channel 2l+e : sum of the direct partials + decorrelator output l read through the
+//                      static delay line 2l+e (dsp.cpp:137-158), ramped when the view changed
+//   HOA channel a    : ambisonic bus a read through the fixed HOA delay.  The reference delays
+//                      the decoder OUTPUT (dsp.cpp:190-197); delay and decode filter are both
+//                      LTI, so the delay is commuted in front and the HOA terms join the same
+//                      frequency-domain accumulation as the BRIR terms.
+// grid: T*CH (channel fastest); block: B/4.
+// ----------------------------------------------------------------------------------------------
+__global__ void bus_fdl_kernel(Layout p, int T, int nch)
+{
+  extern __shared__ float2 sm[];
+  const int M = p.B;
+  float2 *a = sm, *b = sm + M;
+  const int ch = blockIdx.x % nch, k = blockIdx.x / nch;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const float invB = 1.0f / (float)p.B;
+  const int L2 = 2 * p.L;
+  if (ch < L2) {
+    const int l = ch >> 1;
+    const float *wrow = p.w + (size_t)l * p.ws + p.B + p.hist + (size_t)(k - 1) * p.B;
+    const bool dif = p.N > 0;
+    float d0[2], dd[2];
+    for (int h = 0; h < 2; h++) {  // h = 0: block k-1, h = 1: block k
+      const float t0 = p.d_stat[(size_t)(k + h) * L2 + ch] * p.fs;
+      const float t1 = p.d_stat[(size_t)(k + h + 1) * L2 + ch] * p.fs;
+      d0[h] = t0; dd[h] = t1 - t0;
+    }
+    for (int n = tid; n < M; n += nthr) {
+      float2 v = make_float2(0.f, 0.f);
+      for (int s = 0; s < p.S; s++) {
+        const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
+        v.x += c.x; v.y += c.y;
+      }
+      if (dif) {
+        const int t = 2 * n;            // window sample, both of the pair lie in the same block
+        const int h = t >= p.B;
+        const int nn = t - h * p.B;
+        v.x += delayed_read(wrow + t, fmaf((float)(nn + p.doff) * invB, dd[h], d0[h]));
+        v.y += delayed_read(wrow + t + 1, fmaf((float)(nn + 1 + p.doff) * invB, dd[h], d0[h]));
+      }
+      a[n] = v;
+    }
+  } else {
+    const int am = ch - L2;
+    const float *arow = p.amb + (size_t)am * p.ws + p.B + p.hist + (size_t)(k - 1) * p.B;
+    for (int n = tid; n < M; n += nthr)
+      a[n] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
+  }
+  float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw);
+  const int slot = (p.fdl_head + k) % p.R;
+  float2 *dst = p.fdl + ((size_t)ch * p.R + slot) * M;
+  for (int kk = tid; kk <= M / 2; kk += nthr) {
+    if (kk == 0) {
+      dst[0] = make_float2(z[0].x + z[0].y, z[0].x - z[0].y);
+    } else {
+      float2 xk, xm;
+      rfft_post(z[kk], z[M - kk], __ldg(p.tw + kk), xk, xm);
+      dst[kk] = xk;
+      dst[M - kk] = xm;
+    }
+  }
+}
+
+void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
+{
+  int threads = p.B / 4 < 32 ? 32 : p.B / 4;
+  int nch = 2 * p.L + (p.H > 0 ? p.A : 0);
+  bus_fdl_kernel<<<T * nch, threads, 2 * p.B * sizeof(float2), st>>>(p, T, nch);
+}
+
+// ----------------------------------------------------------------------------------------------
+// cmac_kernel: the partitioned complex multiply-accumulate (the roofline kernel).
+//   Y_w[k][e][bin] = sum_{l<L, part<P} FDL[2l+e][k-part][bin] * H[view_w][2l+e][part][bin]
+//                  + sum_{a<A} FDL[2L+a][k][bin] * Hhoa[a][e][bin]            w in {new, old}
+// Terms are split KS ways over blockIdx.y (partial spectra are summed by ifft_out_kernel).
+// Each thread owns two adjacent bins (one 16-byte load per operand per term), consecutive
+// threads consecutive bin pairs: every warp request is 512 contiguous bytes.
+// grid: (B/(2*threads), KS, 2T); block: min(B/2, 128).
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cmac2(float4 &acc, const float4 x, const float4 h)
+{
+  acc.x = fmaf(x.x, h.x, acc.x); acc.x = fmaf(-x.y, h.y, acc.x);
+  acc.y = fmaf(x.x, h.y, acc.y); acc.y = fmaf(x.y, h.x, acc.y);
+  acc.z = fmaf(x.z, h.z, acc.z); acc.z = fmaf(-x.w, h.w, acc.z);
+  acc.w = fmaf(x.z, h.w, acc.w); acc.w = fmaf(x.w, h.z, acc.w);
+}
+// first pair of the packed spectrum: bin 0 holds (DC, Nyquist), both real
+__device__ __forceinline__ void cmac2_packed0(float4 &acc, const float4 x, const float4 h)
+{
+  acc.x = fmaf(x.x, h.x, acc.x);
+  acc.y = fmaf(x.y, h.y, acc.y);
+  acc.z = fmaf(x.z, h.z, acc.z); acc.z = fmaf(-x.w, h.w, acc.z);
+  acc.w = fmaf(x.z, h.w, acc.w); acc.w = fmaf(x.w, h.z, acc.w);
+}
+__device__ __forceinline__ float4 ldg_stream(const float4 *p)
+{
+  float4 v;
+  asm("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+
+template <bool XFADE>
+__device__ __forceinline__ void cmac_body(const Layout &p, int k, int e, int ks, int pair, float4 &accn, float4 &acco)
+{
+  const int B = p.B, P = p.P, L = p.L;
+  const int vnew = p.view[k + 1], vold = p.view[k];
+  const int nb = L * P;
+  const int nterms = nb + (p.H > 0 ? p.A : 0);
+  const int per = (nterms + p.KS - 1) / p.KS;
+  const int t0 = ks * per, t1 = min(nterms, t0 + per);
+  const bool first = pair == 0;
+  const size_t vstride = (size_t)2 * L * P * B;  // float2 per view
+  const int base_slot = p.fdl_head + k + p.R;    // + R keeps the modulo argument positive
+#pragma unroll 4
+  for (int t = t0; t < t1; t++) {
+    const float4 *xp, *hn, *ho;
+    if (t < nb) {
+      const int l = t / P, part = t - l * P;
+      const int ch = 2 * l + e;
+      const int slot = (base_slot - part) % p.R;
+      xp = reinterpret_cast<const float4 *>(p.fdl + ((size_t)ch * p.R + slot) * B) + pair;
+      const size_t ho_ = ((size_t)ch * P + part) * B;
+      hn = reinterpret_cast<const float4 *>(p.h_brir + vnew * vstride + ho_) + pair;
+      ho = reinterpret_cast<const float4 *>(p.h_brir + vold * vstride + ho_) + pair;
+    } else {
+      const int am = t - nb;
+      const int slot = base_slot % p.R;
+      xp = reinterpret_cast<const float4 *>(p.fdl + ((size_t)(2 * L + am) * p.R + slot) * B) + pair;
+      hn = ho = reinterpret_cast<const float4 *>(p.h_hoa + ((size_t)am * 2 + e) * B) + pair;
+    }
+    const float4 x = __ldg(xp);
+    const float4 h = ldg_stream(hn);
+    if (first) cmac2_packed0(accn, x, h); else cmac2(accn, x, h);
+    if (XFADE) {
+      const float4 h2 = __ldg(ho);
+      if (first) cmac2_packed0(acco, x, h2); else cmac2(acco, x, h2);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(128) cmac_kernel(Layout p, int T)
+{
+  const int pair = blockIdx.x * blockDim.x + threadIdx.x;  // bins 2*pair, 2*pair+1
+  const int ks = blockIdx.y;
+  const int k = blockIdx.z >> 1, e = blockIdx.z & 1;
+  const bool xf = p.view[k + 1] != p.view[k];
+  float4 accn = make_float4(0.f, 0.f, 0.f, 0.f), acco = accn;
+  if (xf) cmac_body<true>(p, k, e, ks, pair, accn, acco);
+  else cmac_body<false>(p, k, e, ks, pair, accn, acco);
+  float4 *yn = reinterpret_cast<float4 *>(p.ypart + ((((size_t)k * 2 + e) * 2 + 0) * p.KS + ks) * p.B) + pair;
+  *yn = accn;
+  if (xf) {
+    float4 *yo = reinterpret_cast<float4 *>(p.ypart + ((((size_t)k * 2 + e) * 2 + 1) * p.KS + ks) * p.B) + pair;
+    *yo = acco;
+  }
+}
+
+void launch_cmac(const Layout &p, int T, cudaStream_t st)
+{
+  int threads = p.B / 2 < 128 ? p.B / 2 : 128;
+  dim3 grid(p.B / 2 / threads, p.KS, 2 * T);
+  cmac_kernel<<<grid, threads, 0, st>>>(p, T);
+}
+
+// ----------------------------------------------------------------------------------------------
+// ifft_out_kernel: out[e] block k = irFFT(sum of partial spectra), last B samples; in a
+// view-change block the old-view and new-view results are crossfaded linearly
+// (rcl::InterpolatingFirFilterMatrix with transitionSamples = period, dsp.cpp:73-87).
+// grid: 2T; block: B/4.
+// ----------------------------------------------------------------------------------------------
+__global__ void ifft_out_kernel(Layout p, int T)
+{
+  extern __shared__ float2 sm[];
+  const int M = p.B;
+  float2 *a = sm, *b = sm + M;
+  const int k = blockIdx.x >> 1, e = blockIdx.x & 1;
+  const int tid = threadIdx.x, nthr = blockDim.x;
+  const bool xf = p.view[k + 1] != p.view[k];
+  const float invB = 1.0f / (float)p.B;
+  float2 *dst = reinterpret_cast<float2 *>(p.out + (size_t)e * p.os + (size_t)k * p.B);
+  for (int pass = xf ? 1 : 0; pass >= 0; pass--) {   // pass 1 = old view, pass 0 = new view
+    const float2 *y = p.ypart + ((((size_t)k * 2 + e) * 2 + pass) * p.KS) * M;
+    __syncthreads();
+    for (int kk = tid; kk <= M / 2; kk += nthr) {
+      float2 xk = make_float2(0.f, 0.f), xm = xk;
+      for (int s = 0; s < p.KS; s++) {
+        const float2 u = y[(size_t)s * M + kk];
+        xk.x += u.x; xk.y += u.y;
+        if (kk) {
+          const float2 v = y[(size_t)s * M + M - kk];
+          xm.x += v.x; xm.y += v.y;
+        }
+      }
+      if (kk == 0) {
+        a[0] = make_float2(xk.x + xk.y, xk.x - xk.y);
+      } else {
+        float2 zk, zm;
+        irfft_pre(xk, xm, __ldg(p.tw + kk), zk, zm);
+        a[kk] = zk;
+        a[M - kk] = zm;
+      }
+    }
+    float2 *z = fft_shared<true>(a, b, M, p.logB, p.tw);
+    for (int n = tid; n < M / 2; n += nthr) {
+      float2 v = z[M / 2 + n];
+      if (xf) {
+        const float r0 = (float)(2 * n + p.xoff) * invB, r1 = (float)(2 * n + 1 + p.xoff) * invB;
+        if (pass == 1) {
+          v.x *= (1.0f - r0); v.y *= (1.0f - r1);
+        } else {
+          const float2 o = dst[n];
+          v.x = fmaf(r0, v.x, o.x); v.y = fmaf(r1, v.y, o.y);
+        }
+      }
+      dst[n] = v;
+    }
+  }
+}
+
+void launch_ifft_out(const Layout &p, int T, cudaStream_t st)
+{
+  int threads = p.B / 4 < 32 ? 32 : p.B / 4;
+  ifft_out_kernel<<<2 * T, threads, 2 * p.B * sizeof(float2), st>>>(p, T);
+}
+
+// ----------------------------------------------------------------------------------------------
+// carry_kernel: after a call, move the tail of every history-carrying row to its front
+// (memmove semantics: destination precedes source, chunks processed in ascending order).
+// grid: total rows; block 256.
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) carry_kernel(CarryPlan plan)
+{
+  int e = 0;
+  while (e + 1 < plan.n && (int)blockIdx.x >= plan.row_start[e + 1]) e++;
+  const CarryRow r = plan.e[e];
+  float *row = r.base + (size_t)(blockIdx.x - plan.row_start[e]) * r.stride;
+  for (int c0 = 0; c0 < r.count; c0 += blockDim.x) {
+    const int i = c0 + threadIdx.x;
+    float v = 0.f;
+    if (i < r.count) v = row[i + r.shift];
+    __syncthreads();
+    if (i < r.count) row[i] = v;
+    __syncthreads();
+  }
+}
+
+void launch_carry(const CarryPlan &plan, cudaStream_t st)
+{
+  carry_kernel<<<plan.row_start[plan.n], 256, 0, st>>>(plan);
+}
+
+cudaError_t configure_kernels(int B)
+{
+  const int smem = 2 * B * (int)sizeof(float2);
+  if (smem > 48 * 1024) {
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(filter_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
+    if ((e = cudaFuncSetAttribute(decorrelate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
+    if ((e = cudaFuncSetAttribute(bus_fdl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
+    if ((e = cudaFuncSetAttribute(ifft_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
+  }
+  return cudaSuccess;
+}
+
+}  // namespace bearcuda

@@ -1,0 +1,82 @@
+// Device-side layout shared by kernels.cu and renderer.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace bearcuda {
+
+constexpr int kMaxSpeakers = 24;  // accumulator tile of the mix kernel (L <= 24)
+constexpr int kMixTile = 128;     // samples per CTA in the mix kernels
+constexpr int kMixChunk = 32;     // channels staged in shared memory per pass
+
+// Everything a kernel needs to find its data.  Passed by value (fits the 4 KB param space).
+struct Layout {
+  // sizes
+  int N, M, H;        // objects, DirectSpeakers, HOA input channels
+  int B, logB;        // period (= complex FFT length), log2
+  int P;              // BRIR partitions
+  int L, A;           // virtual loudspeakers, HOA decoder channels
+  int CH;             // FDL channels = 2L + A
+  int V;              // views
+  int Tmax;           // max blocks per call
+  int hist;           // time-domain history (samples) kept in front of every delayed signal
+  int S;              // object splits (partial bus buffers)
+  int KS;             // cMAC splits (partial spectra)
+  int R;              // FDL ring slots
+  int goff, doff, xoff;  // ramp offsets
+  float fs;
+  float hoa_delay;    // samples
+
+  // audio in: [N+M+H][xs], block data from column `hist`
+  float *xin;  size_t xs;
+  // tables, slot 0 = state carried from the previous call
+  float *g_dir, *g_dif;   // [Tmax+1][L][N]
+  float *g_ds;            // [Tmax+1][L][M]
+  float *g_hoa;           // [Tmax+1][A][H]
+  float *d_dir;           // [Tmax+1][2N] seconds
+  float *d_ds;            // [Tmax+1][2M]
+  float *d_stat;          // [Tmax+2][2L]  slots 0,1 = blocks -2,-1
+  int32_t *view;          // [Tmax+1]
+  // time-domain intermediates (row stride, prefix)
+  float *cdir;  size_t cs;   // [S][2L][cs]   prefix B
+  float *qdif;               // [S][L][cs]    prefix B
+  float *w;     size_t ws;   // [L][ws]       prefix B+hist  (decorrelator outputs)
+  float *amb;                // [A][ws]       prefix B+hist  (HOA decoder inputs)
+  // spectra (packed: bin 0 = (DC, Nyquist), bins 1..B-1 complex)
+  float2 *fdl;               // [CH][R][B]
+  const float2 *h_brir;      // [V][2L][P][B], pre-scaled by 1/(2B)
+  const float2 *h_dec;       // [L][B]
+  const float2 *h_hoa;       // [A][2][B]
+  float2 *ypart;             // [Tmax][2][2][KS][B]
+  const float2 *tw;          // [B] exp(-i pi q / B)
+  // out
+  float *out;  size_t os;    // [2][os]
+  int fdl_head;              // ring slot of block 0 of this call
+};
+
+struct CarryRow {
+  float *base;
+  int rows;
+  long long stride;   // floats between rows
+  int count;          // floats to move per row
+  long long shift;    // source offset (floats) relative to destination
+};
+constexpr int kMaxCarry = 16;
+struct CarryPlan {
+  CarryRow e[kMaxCarry];
+  int row_start[kMaxCarry + 1];
+  int n;
+};
+
+void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, int logB, int P, const float2 *tw,
+                       float2 *out, float scale, cudaStream_t st);
+void launch_mix(const Layout &p, int T, cudaStream_t st);
+void launch_hoa_mix(const Layout &p, int T, cudaStream_t st);
+void launch_decorrelate(const Layout &p, int T, cudaStream_t st);
+void launch_bus_fdl(const Layout &p, int T, cudaStream_t st);
+void launch_cmac(const Layout &p, int T, cudaStream_t st);
+void launch_ifft_out(const Layout &p, int T, cudaStream_t st);
+void launch_carry(const CarryPlan &plan, cudaStream_t st);
+cudaError_t configure_kernels(int B);
+
+}  // namespace bearcuda

@@ -1,0 +1,553 @@
+// Host side of libbear_cuda.so: device state of one renderer and the C ABI of include/bear_cuda.h.
+// Replaces the construction and per-period work of bear::DSP (visr_bear/src/dsp.cpp:7-236).
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../../include/bear_cuda.h"
+#include "kernels.cuh"
+#include "tenf.hpp"
+
+using namespace bearcuda;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct CudaFail {
+  std::string msg;
+};
+#define CK(expr)                                                                                          \
+  do {                                                                                                    \
+    cudaError_t e__ = (expr);                                                                             \
+    if (e__ != cudaSuccess)                                                                               \
+      throw CudaFail{std::string(#expr) + ": " + cudaGetErrorName(e__) + " (" + cudaGetErrorString(e__) + ")"}; \
+  } while (0)
+
+struct InvalidArgument { std::string msg; };
+struct Unsupported { std::string msg; };
+
+size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
+
+}  // namespace
+
+struct bear_cuda_renderer {
+  bear_cuda_config cfg{};
+  Layout lay{};
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::vector<void *> allocs;
+  uint64_t device_bytes = 0;
+  uint64_t launches = 0;
+  uint32_t kernels_per_call = 0;
+  std::string error;
+  double default_direct_delay = 0, default_static_delay = 0;
+
+  // staging (device) for the T blocks of the current call: slot 1 of each table
+  float *audio_out = nullptr;
+  // pinned host staging for the single-block API
+  float *h_in = nullptr, *h_out = nullptr;
+  size_t h_in_floats = 0;
+
+  template <class T>
+  T *dalloc(size_t count, bool zero = true)
+  {
+    void *p = nullptr;
+    size_t bytes = round_up(count * sizeof(T) + 16, 256);
+    CK(cudaMalloc(&p, bytes));
+    allocs.push_back(p);
+    device_bytes += bytes;
+    if (zero) CK(cudaMemsetAsync(p, 0, bytes, stream));
+    return static_cast<T *>(p);
+  }
+
+  ~bear_cuda_renderer()
+  {
+    cudaSetDevice(device);
+    if (stream) cudaStreamSynchronize(stream);
+    for (void *p : allocs) cudaFree(p);
+    if (h_in) cudaFreeHost(h_in);
+    if (h_out) cudaFreeHost(h_out);
+    if (stream) cudaStreamDestroy(stream);
+  }
+};
+
+namespace {
+
+int ilog2(uint32_t v)
+{
+  int l = 0;
+  while ((1u << l) < v) l++;
+  return l;
+}
+
+void fill_device(bear_cuda_renderer *r, float *dst, size_t count, float value)
+{
+  std::vector<float> h(count, value);
+  CK(cudaMemcpyAsync(dst, h.data(), count * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+  CK(cudaStreamSynchronize(r->stream));
+}
+
+bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_data &d)
+{
+  const uint32_t B = cfg.period_size;
+  if (B == 0) throw InvalidArgument{"Config: period size must be set"};  // api.cpp:70
+  if (!d.brirs || !d.delays || !d.decorrelation_filters || !d.hoa_irs)
+    throw InvalidArgument{"data tables must not be NULL"};
+  if ((B & (B - 1)) != 0 || B < 128 || B > 4096)
+    throw Unsupported{"period size must be a power of two between 128 and 4096"};
+  if (d.num_virtual_loudspeakers == 0 || d.num_virtual_loudspeakers > (uint32_t)kMaxSpeakers)
+    throw Unsupported{"number of virtual loudspeakers must be 1..24"};
+  if (d.decorrelator_length > B || d.hoa_ir_length > B)
+    throw Unsupported{"decorrelator and HOA decode filters must not be longer than the period"};
+  if (d.num_views == 0 || d.brir_length == 0) throw InvalidArgument{"empty BRIR table"};
+  if (d.front_loudspeaker >= d.num_virtual_loudspeakers)
+    throw InvalidArgument{"front_loudspeaker out of range"};
+  if (cfg.gain_ramp_offset > 1 || cfg.delay_ramp_offset > 1 || cfg.xfade_ramp_offset > 1)
+    throw InvalidArgument{"ramp offsets must be 0 or 1"};
+
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    throw CudaFail{std::string("no usable CUDA device (") + cudaGetErrorString(e) +
+                   "); this library has no CPU fallback"};
+  if (cfg.device < 0 || cfg.device >= ndev) throw InvalidArgument{"device ordinal out of range"};
+
+  std::unique_ptr<bear_cuda_renderer> r(new bear_cuda_renderer);
+  r->cfg = cfg;
+  r->device = cfg.device;
+  CK(cudaSetDevice(r->device));
+  CK(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+  CK(configure_kernels((int)B));
+
+  Layout &p = r->lay;
+  p.N = cfg.num_objects_channels; p.M = cfg.num_direct_speakers_channels; p.H = cfg.num_hoa_channels;
+  p.B = B; p.logB = ilog2(B);
+  p.P = (d.brir_length + B - 1) / B;
+  p.L = d.num_virtual_loudspeakers; p.A = d.num_hoa_decoder_channels;
+  p.CH = 2 * p.L + p.A;
+  p.V = d.num_views;
+  p.Tmax = cfg.max_batch_blocks ? cfg.max_batch_blocks : 1;
+  const uint32_t max_delay = cfg.max_delay_samples ? cfg.max_delay_samples : 256;
+  p.hist = (int)round_up(max_delay + 8, 4);
+  p.goff = cfg.gain_ramp_offset; p.doff = cfg.delay_ramp_offset; p.xoff = cfg.xfade_ramp_offset;
+  p.fs = (float)d.fs;
+  p.hoa_delay = (float)d.hoa_delay;
+  if (d.hoa_delay + 4 > p.hist) throw Unsupported{"hoa delay exceeds max_delay_samples"};
+
+  const int C = p.N + p.M;
+  {
+    const int tiles = p.Tmax * p.B / kMixTile;
+    int S = cfg.object_splits;
+    if (S == 0) S = (2 * 148 + tiles - 1) / tiles;
+    const int maxS = C > 0 ? (C + kMixChunk - 1) / kMixChunk : 1;
+    p.S = std::max(1, std::min(std::min(S, maxS), 16));
+  }
+  {
+    const int nterms = p.L * p.P + (p.H > 0 ? p.A : 0);
+    const int threads = std::min(p.B / 2, 128);
+    const int base = (p.B / 2 / threads) * 2 * p.Tmax;
+    int KS = cfg.cmac_splits;
+    if (KS == 0) KS = (4 * 148 + base - 1) / base;
+    p.KS = std::max(1, std::min(std::min(KS, std::max(1, nterms / 8)), 32));
+  }
+  p.R = p.Tmax + p.P - 1;
+
+  // ---- allocations -----------------------------------------------------------------------
+  const size_t TB = (size_t)p.Tmax * p.B;
+  p.xs = round_up(p.hist + TB, 4);
+  p.xin = r->dalloc<float>((size_t)std::max(1, p.N + p.M + p.H) * p.xs);
+  const size_t T1 = p.Tmax + 1;
+  p.g_dir = r->dalloc<float>(T1 * p.L * std::max(1, p.N));
+  p.g_dif = r->dalloc<float>(T1 * p.L * std::max(1, p.N));
+  p.g_ds = r->dalloc<float>(T1 * p.L * std::max(1, p.M));
+  p.g_hoa = r->dalloc<float>(T1 * std::max(1, p.A) * std::max(1, p.H));
+  p.d_dir = r->dalloc<float>(T1 * 2 * std::max(1, p.N));
+  p.d_ds = r->dalloc<float>(T1 * 2 * std::max(1, p.M));
+  p.d_stat = r->dalloc<float>((T1 + 1) * 2 * p.L);
+  p.view = r->dalloc<int32_t>(T1);
+  p.cs = round_up(p.B + TB, 4);
+  p.cdir = r->dalloc<float>((size_t)p.S * 2 * p.L * p.cs);
+  p.qdif = r->dalloc<float>((size_t)p.S * p.L * p.cs);
+  p.ws = round_up(p.B + p.hist + TB, 4);
+  p.w = r->dalloc<float>((size_t)p.L * p.ws);
+  p.amb = r->dalloc<float>((size_t)std::max(1, p.A) * p.ws);
+  p.fdl = r->dalloc<float2>((size_t)p.CH * p.R * p.B);
+  p.ypart = r->dalloc<float2>((size_t)p.Tmax * 2 * 2 * p.KS * p.B);
+  p.os = round_up(TB, 4);
+  p.out = r->dalloc<float>(2 * p.os);
+  r->audio_out = p.out;
+
+  // twiddles exp(-i pi q / B), computed in double
+  {
+    std::vector<float2> tw(p.B);
+    const double pi = 3.14159265358979323846264338327950288;
+    for (int q = 0; q < p.B; q++) tw[q] = make_float2((float)std::cos(pi * q / p.B), (float)-std::sin(pi * q / p.B));
+    float2 *dtw = r->dalloc<float2>(p.B, false);
+    CK(cudaMemcpyAsync(dtw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice, r->stream));
+    CK(cudaStreamSynchronize(r->stream));
+    p.tw = dtw;
+  }
+
+  // ---- filter spectra ------------------------------------------------------------------------
+  {
+    const float scale = 1.0f / (float)(2 * p.B);
+    auto transform = [&](const float *host, size_t n_filters, int len, int parts) {
+      float *tmp = nullptr;
+      const size_t bytes = n_filters * len * sizeof(float);
+      CK(cudaMalloc(&tmp, bytes));
+      CK(cudaMemcpyAsync(tmp, host, bytes, cudaMemcpyHostToDevice, r->stream));
+      float2 *spec = r->dalloc<float2>(n_filters * parts * p.B, false);
+      // launch in slices to keep grid sizes moderate
+      const size_t slice = 16384;
+      for (size_t f0 = 0; f0 < n_filters; f0 += slice) {
+        size_t nf = std::min(slice, n_filters - f0);
+        launch_filter_fft(tmp + f0 * len, (int)nf, len, p.B, p.logB, parts, p.tw, spec + f0 * parts * p.B, scale,
+                          r->stream);
+        r->launches++;
+      }
+      CK(cudaGetLastError());
+      CK(cudaStreamSynchronize(r->stream));
+      CK(cudaFree(tmp));
+      return spec;
+    };
+    p.h_brir = transform(d.brirs, (size_t)p.V * 2 * p.L, d.brir_length, p.P);
+    p.h_dec = transform(d.decorrelation_filters, p.L, d.decorrelator_length, 1);
+    p.h_hoa = transform(d.hoa_irs, (size_t)std::max(1, p.A) * 2, d.hoa_ir_length, 1);
+  }
+
+  // ---- initial state (dsp.cpp:24-29,41-46,137-144; panner.cpp:172-186) -------------------------
+  const double front = ((double)d.delays[(0 * p.L + d.front_loudspeaker) * 2 + 0] +
+                        (double)d.delays[(0 * p.L + d.front_loudspeaker) * 2 + 1]) / 2.0;
+  r->default_static_delay = front / d.fs;
+  r->default_direct_delay = (front + d.decorrelation_delay) / d.fs;
+  if (front + d.decorrelation_delay + 4 > p.hist) throw Unsupported{"default delay exceeds max_delay_samples"};
+  if (p.N) fill_device(r.get(), p.d_dir, 2 * p.N, (float)r->default_direct_delay);
+  if (p.M) fill_device(r.get(), p.d_ds, 2 * p.M, (float)r->default_direct_delay);
+  fill_device(r.get(), p.d_stat, 2 * 2 * p.L, (float)r->default_static_delay);
+
+  r->h_in_floats = (size_t)std::max(1, p.N + p.M + p.H) * p.B;
+  CK(cudaMallocHost(&r->h_in, r->h_in_floats * sizeof(float)));
+  CK(cudaMallocHost(&r->h_out, 2 * (size_t)p.B * sizeof(float)));
+  CK(cudaStreamSynchronize(r->stream));
+
+  r->kernels_per_call = (C > 0) + (p.H > 0) + (p.N > 0) + 4;
+  return r.release();
+}
+
+// Queue the kernels for T blocks whose audio and tables are already in the staging areas.
+void run_pipeline(bear_cuda_renderer *r, int T)
+{
+  Layout &p = r->lay;
+  cudaStream_t st = r->stream;
+  if (p.N + p.M > 0) launch_mix(p, T, st);
+  if (p.H > 0) launch_hoa_mix(p, T, st);
+  if (p.N > 0) launch_decorrelate(p, T, st);
+  launch_bus_fdl(p, T, st);
+  launch_cmac(p, T, st);
+  launch_ifft_out(p, T, st);
+
+  CarryPlan plan{};
+  int n = 0, rows = 0;
+  auto add = [&](float *base, int nrows, long long stride, int count, long long shift) {
+    if (nrows <= 0 || count <= 0) return;
+    plan.e[n] = CarryRow{base, nrows, stride, count, shift};
+    plan.row_start[n] = rows;
+    rows += nrows;
+    n++;
+  };
+  const long long TB = (long long)T * p.B;
+  add(p.xin, p.N + p.M + p.H, (long long)p.xs, p.hist, TB);
+  if (p.N + p.M > 0) add(p.cdir, p.S * 2 * p.L, (long long)p.cs, p.B, TB);
+  if (p.N > 0) {
+    add(p.qdif, p.S * p.L, (long long)p.cs, p.B, TB);
+    add(p.w, p.L, (long long)p.ws, p.B + p.hist, TB);
+  }
+  if (p.H > 0) {
+    add(p.amb, p.A, (long long)p.ws, p.B + p.hist, TB);
+    add(p.g_hoa, 1, 0, p.A * p.H, (long long)T * p.A * p.H);
+  }
+  if (p.N > 0) {
+    add(p.g_dir, 1, 0, p.L * p.N, (long long)T * p.L * p.N);
+    add(p.g_dif, 1, 0, p.L * p.N, (long long)T * p.L * p.N);
+    add(p.d_dir, 1, 0, 2 * p.N, (long long)T * 2 * p.N);
+  }
+  if (p.M > 0) {
+    add(p.g_ds, 1, 0, p.L * p.M, (long long)T * p.L * p.M);
+    add(p.d_ds, 1, 0, 2 * p.M, (long long)T * 2 * p.M);
+  }
+  add(p.d_stat, 1, 0, 2 * 2 * p.L, (long long)T * 2 * p.L);
+  add(reinterpret_cast<float *>(p.view), 1, 0, 1, T);
+  plan.n = n;
+  plan.row_start[n] = rows;
+  launch_carry(plan, st);
+  CK(cudaGetLastError());
+  r->launches += r->kernels_per_call;
+  p.fdl_head = (p.fdl_head + T) % p.R;
+}
+
+template <class F>
+int guarded(bear_cuda_renderer *r, F &&f)
+{
+  std::string *err = r ? &r->error : &g_create_error;
+  try {
+    if (r) {
+      cudaError_t e = cudaSetDevice(r->device);
+      if (e != cudaSuccess) throw CudaFail{std::string("cudaSetDevice: ") + cudaGetErrorString(e)};
+    }
+    f();
+    return BEAR_CUDA_OK;
+  } catch (const InvalidArgument &e) {
+    *err = e.msg;
+    return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  } catch (const Unsupported &e) {
+    *err = e.msg;
+    return BEAR_CUDA_ERR_UNSUPPORTED;
+  } catch (const CudaFail &e) {
+    *err = e.msg;
+    return BEAR_CUDA_ERR_CUDA;
+  } catch (const std::exception &e) {
+    *err = e.what();
+    return BEAR_CUDA_ERR_DATA_FILE;
+  }
+}
+
+void upload_tables(bear_cuda_renderer *r, int T, const bear_cuda_block_tables *t, bool allow_unchanged)
+{
+  Layout &p = r->lay;
+  cudaStream_t st = r->stream;
+  auto up = [&](float *dev, size_t per_block, size_t slot0_blocks, const float *host, const char *name) {
+    if (per_block == 0) return;
+    float *dst = dev + slot0_blocks * per_block;
+    if (host) {
+      CK(cudaMemcpyAsync(dst, host, (size_t)T * per_block * sizeof(float), cudaMemcpyHostToDevice, st));
+    } else if (allow_unchanged && T == 1) {
+      CK(cudaMemcpyAsync(dst, dst - per_block, per_block * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    } else {
+      throw InvalidArgument{std::string("table must not be NULL: ") + name};
+    }
+  };
+  if (!t) throw InvalidArgument{"tables must not be NULL"};
+  up(p.g_dir, (size_t)p.L * p.N, 1, t->direct_gains, "direct_gains");
+  up(p.g_dif, (size_t)p.L * p.N, 1, t->diffuse_gains, "diffuse_gains");
+  up(p.d_dir, (size_t)2 * p.N, 1, t->direct_delays, "direct_delays");
+  up(p.g_ds, (size_t)p.L * p.M, 1, t->direct_speakers_gains, "direct_speakers_gains");
+  up(p.d_ds, (size_t)2 * p.M, 1, t->direct_speakers_delays, "direct_speakers_delays");
+  up(p.d_stat, (size_t)2 * p.L, 2, t->static_delays, "static_delays");
+  up(p.g_hoa, (size_t)p.A * p.H, 1, t->hoa_gains, "hoa_gains");
+  if (t->brir_index) {
+    for (int k = 0; k < T; k++) {
+      int32_t v = t->brir_index[k];
+      if (allow_unchanged && T == 1 && v < 0) {
+        CK(cudaMemcpyAsync(p.view + 1, p.view, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+        return;
+      }
+      if (v < 0 || v >= p.V) throw InvalidArgument{"brir_index out of range"};
+    }
+    CK(cudaMemcpyAsync(p.view + 1, t->brir_index, (size_t)T * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+  } else if (allow_unchanged && T == 1) {
+    CK(cudaMemcpyAsync(p.view + 1, p.view, sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+  } else {
+    throw InvalidArgument{"table must not be NULL: brir_index"};
+  }
+}
+
+}  // namespace
+
+// ================================================================================================
+extern "C" {
+
+int bear_cuda_create(const bear_cuda_config *config, const bear_cuda_data *data, bear_cuda_renderer **out)
+{
+  if (out) *out = nullptr;
+  return guarded(nullptr, [&] {
+    if (!config || !data || !out) throw InvalidArgument{"NULL argument"};
+    *out = create_impl(*config, *data);
+  });
+}
+
+int bear_cuda_create_from_file(const bear_cuda_config *config, const char *data_path, bear_cuda_renderer **out)
+{
+  if (out) *out = nullptr;
+  return guarded(nullptr, [&] {
+    if (!config || !out) throw InvalidArgument{"NULL argument"};
+    if (config->period_size == 0) throw InvalidArgument{"Config: period size must be set"};          // api.cpp:70
+    if (!data_path || !*data_path) throw InvalidArgument{"Config: data path must be set"};           // api.cpp:71
+    tenf::File tf(data_path);
+    const tenf::Json &m = tf.metadata();
+    auto check = [](bool ok, const char *msg) {
+      if (!ok) throw std::runtime_error(std::string("BEAR data file error: ") + msg);               // panner.cpp:43-46
+    };
+    if (const tenf::Json *v = m.find("bear_data_version")) {                                         // data_file.cpp:6-20
+      if (v->kind != tenf::Json::Number || !v->is_int) throw std::runtime_error("version must be an integer");
+      if (v->inum > 0)
+        throw std::runtime_error("data file version mismatch: expected 0, got " + std::to_string(v->inum));
+    }
+    tenf::FloatTensor views = tf.unpack_f32(m.at("views")), brirs = tf.unpack_f32(m.at("brirs")),
+                      delays = tf.unpack_f32(m.at("delays")), dec = tf.unpack_f32(m.at("decorrelation_filters"));
+    check(views.shape.size() == 2, "views must have 2 dimensions");                                  // panner.cpp:67-92
+    check(brirs.shape.size() == 4, "brirs must have 4 dimensions");
+    check(delays.shape.size() == 3, "delays must have 3 dimensions");
+    check(dec.shape.size() == 2, "decorrelation_filters must have 2 dimensions");
+    const size_t V = brirs.shape[0], L = brirs.shape[1];
+    check(views.shape[0] == V, "views axis 0 is wrong size");
+    check(views.shape[1] == 3, "views axis 1 is wrong size");
+    check(brirs.shape[2] == 2, "brirs axis 2 is wrong size");
+    check(delays.shape[0] == V, "delays axis 0 is wrong size");
+    check(delays.shape[1] == L, "delays axis 1 is wrong size");
+    check(delays.shape[2] == 2, "delays axis 2 is wrong size");
+    check(dec.shape[0] == L, "decorrelation filters axis 0 is wrong size");
+    check(m.has("hoa"), "HOA decoder not present");                                                  // panner.cpp:125
+    tenf::FloatTensor hoa = tf.unpack_f32(m.at("hoa").at("irs"));
+    check(hoa.shape.size() == 3, "HOA decoder must have 3 dimensions");
+    check(hoa.shape[1] == 2, "HOA decoder axis 1 is wrong size");
+    const size_t order = (size_t)std::llround(std::sqrt((double)hoa.shape[0])) - 1;
+    if ((order + 1) * (order + 1) != hoa.shape[0]) throw std::runtime_error("bad number of hoa channels");
+
+    bear_cuda_data d{};
+    d.num_views = (uint32_t)V; d.num_virtual_loudspeakers = (uint32_t)L;
+    d.brir_length = (uint32_t)brirs.shape[3]; d.decorrelator_length = (uint32_t)dec.shape[1];
+    d.num_hoa_decoder_channels = (uint32_t)hoa.shape[0]; d.hoa_ir_length = (uint32_t)hoa.shape[2];
+    d.brirs = brirs.data.data(); d.delays = delays.data.data();
+    d.decorrelation_filters = dec.data.data(); d.hoa_irs = hoa.data.data();
+    d.fs = m.at("fs").num;
+    d.decorrelation_delay = (double)(size_t)m.at("decorrelation_delay").num;                         // panner.cpp:62
+    d.front_loudspeaker = (uint32_t)m.at("front_loudspeaker").num;
+    const tenf::Json *hd = m.at("hoa").find("delay");
+    d.hoa_delay = hd ? hd->num : 0.0;
+    *out = create_impl(*config, d);
+  });
+}
+
+void bear_cuda_destroy(bear_cuda_renderer *r) { delete r; }
+
+const char *bear_cuda_last_error(const bear_cuda_renderer *r) { return r ? r->error.c_str() : g_create_error.c_str(); }
+
+int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *objects, size_t objects_stride,
+                            const float *direct_speakers, size_t direct_speakers_stride, const float *hoa,
+                            size_t hoa_stride, const bear_cuda_block_tables *tables, float *output, size_t out_stride)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    Layout &p = r->lay;
+    if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
+    if (!output) throw InvalidArgument{"output must not be NULL"};
+    const size_t TB = (size_t)T * p.B;
+    auto up_audio = [&](int row0, int rows, const float *host, size_t stride, const char *name) {
+      if (rows == 0) return;
+      if (!host) throw InvalidArgument{std::string(name) + " input must not be NULL"};
+      CK(cudaMemcpy2DAsync(p.xin + (size_t)row0 * p.xs + p.hist, p.xs * sizeof(float), host, stride * sizeof(float),
+                           TB * sizeof(float), rows, cudaMemcpyHostToDevice, r->stream));
+    };
+    up_audio(0, p.N, objects, objects_stride, "objects");
+    up_audio(p.N, p.M, direct_speakers, direct_speakers_stride, "direct_speakers");
+    up_audio(p.N + p.M, p.H, hoa, hoa_stride, "hoa");
+    upload_tables(r, (int)T, tables, false);
+    run_pipeline(r, (int)T);
+    CK(cudaMemcpy2DAsync(output, out_stride * sizeof(float), p.out, p.os * sizeof(float), TB * sizeof(float), 2,
+                         cudaMemcpyDeviceToHost, r->stream));
+    CK(cudaStreamSynchronize(r->stream));
+  });
+}
+
+int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
+                      const float *const *direct_speakers_input, const float *const *hoa_input,
+                      const bear_cuda_block_tables *tables, float *const *output)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    Layout &p = r->lay;
+    if (!output || !output[0] || !output[1]) throw InvalidArgument{"output must not be NULL"};
+    const size_t B = p.B;
+    int row = 0;
+    auto gather = [&](const float *const *ptrs, int count, const char *name) {
+      if (count && !ptrs) throw InvalidArgument{std::string(name) + " input must not be NULL"};
+      for (int i = 0; i < count; i++, row++) {
+        if (!ptrs[i]) throw InvalidArgument{std::string(name) + " channel pointer is NULL"};
+        std::memcpy(r->h_in + (size_t)row * B, ptrs[i], B * sizeof(float));
+      }
+    };
+    gather(objects_input, p.N, "objects");
+    gather(direct_speakers_input, p.M, "direct_speakers");
+    gather(hoa_input, p.H, "hoa");
+    if (row)
+      CK(cudaMemcpy2DAsync(p.xin + p.hist, p.xs * sizeof(float), r->h_in, B * sizeof(float), B * sizeof(float), row,
+                           cudaMemcpyHostToDevice, r->stream));
+    upload_tables(r, 1, tables, true);
+    run_pipeline(r, 1);
+    CK(cudaMemcpy2DAsync(r->h_out, B * sizeof(float), p.out, p.os * sizeof(float), B * sizeof(float), 2,
+                         cudaMemcpyDeviceToHost, r->stream));
+    CK(cudaStreamSynchronize(r->stream));
+    std::memcpy(output[0], r->h_out, B * sizeof(float));
+    std::memcpy(output[1], r->h_out + B, B * sizeof(float));
+  });
+}
+
+int bear_cuda_get_device_io(bear_cuda_renderer *r, bear_cuda_device_io *io)
+{
+  if (!r || !io) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  Layout &p = r->lay;
+  std::memset(io, 0, sizeof(*io));
+  io->audio_in = p.xin; io->audio_stride = p.xs; io->audio_offset = p.hist;
+  io->direct_gains = p.g_dir + (size_t)p.L * p.N;
+  io->diffuse_gains = p.g_dif + (size_t)p.L * p.N;
+  io->direct_delays = p.d_dir + (size_t)2 * p.N;
+  io->direct_speakers_gains = p.g_ds + (size_t)p.L * p.M;
+  io->direct_speakers_delays = p.d_ds + (size_t)2 * p.M;
+  io->static_delays = p.d_stat + (size_t)2 * 2 * p.L;
+  io->brir_index = p.view + 1;
+  io->hoa_gains = p.g_hoa + (size_t)p.A * p.H;
+  io->audio_out = p.out; io->out_stride = p.os;
+  io->stream = r->stream;
+  return BEAR_CUDA_OK;
+}
+
+int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    if (T == 0 || (int)T > r->lay.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
+    run_pipeline(r, (int)T);
+  });
+}
+
+int bear_cuda_synchronize(bear_cuda_renderer *r)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] { CK(cudaStreamSynchronize(r->stream)); });
+}
+
+int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info)
+{
+  if (!r || !info) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  std::memset(info, 0, sizeof(*info));
+  info->num_partitions = r->lay.P;
+  info->object_splits = r->lay.S;
+  info->cmac_splits = r->lay.KS;
+  info->history_samples = r->lay.hist;
+  info->kernels_per_call = r->kernels_per_call;
+  info->device_bytes = r->device_bytes;
+  info->launches_total = r->launches;
+  info->default_direct_delay = r->default_direct_delay;
+  info->default_static_delay = r->default_static_delay;
+  return BEAR_CUDA_OK;
+}
+
+void *bear_cuda_host_alloc(size_t bytes)
+{
+  void *p = nullptr;
+  if (cudaMallocHost(&p, bytes) != cudaSuccess) return nullptr;
+  return p;
+}
+void bear_cuda_host_free(void *p)
+{
+  if (p) cudaFreeHost(p);
+}
+
+}  // extern "C"

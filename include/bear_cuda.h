@@ -1,0 +1,173 @@
+/* bear_cuda.h -- C ABI of the B200-native BEAR render core (libbear_cuda.so).
+ *
+ * The library replaces ONE thing in the reference: the audio DSP graph `bear::DSP`
+ * (visr_bear/src/dsp.cpp:7-236) that `bear::Renderer::process()` runs once per period
+ * (visr_bear/src/api.cpp:138-154).  Its inputs are exactly the Control->DSP parameter ports of
+ * visr_bear/src/top.cpp:34-51 plus the audio; everything above (metadata, libear gain
+ * calculation, listener handling) stays on the host in the reference's own code.
+ *
+ * Conventions: plain pointers and sizes, no C++ types; the caller owns every host buffer for
+ * the duration of a call; the library owns all device state; every function returns
+ * BEAR_CUDA_OK (0) or a negative error code, and bear_cuda_last_error() gives the message.
+ * A renderer is single-threaded like bear::Renderer (visr_bear/src/dynamic_renderer.hpp:14-15).
+ * There is no CPU fallback: creation fails if no CUDA device is usable.
+ */
+#ifndef BEAR_CUDA_H
+#define BEAR_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BEAR_CUDA_OK 0
+#define BEAR_CUDA_ERR_INVALID_ARGUMENT (-1) /* std::invalid_argument in the reference */
+#define BEAR_CUDA_ERR_DATA_FILE (-2)        /* std::runtime_error "BEAR data file error: ..." / tensorfile format_error */
+#define BEAR_CUDA_ERR_CUDA (-3)             /* CUDA runtime failure */
+#define BEAR_CUDA_ERR_UNSUPPORTED (-4)      /* configuration outside what the kernels support */
+
+typedef struct bear_cuda_renderer bear_cuda_renderer;
+
+/* Replaces bear::ConfigImpl (visr_bear/src/config_impl.hpp:6-14) + DSP construction parameters. */
+typedef struct bear_cuda_config {
+  uint32_t num_objects_channels;         /* N */
+  uint32_t num_direct_speakers_channels; /* M */
+  uint32_t num_hoa_channels;             /* H */
+  uint32_t period_size;                  /* B: power of two, 64..4096 */
+  uint32_t sample_rate;                  /* informational; the data file's fs converts delays */
+  uint32_t max_batch_blocks;             /* largest T accepted by the *_batch calls (>=1) */
+  int32_t device;                        /* CUDA device ordinal */
+  uint32_t max_delay_samples;            /* largest table delay in samples (0 -> 256) */
+  uint32_t object_splits;                /* 0 = choose from N and max_batch_blocks */
+  uint32_t cmac_splits;                  /* 0 = choose from B and max_batch_blocks */
+  /* Ramp end-point conventions of the VISR atoms, ramp[n] = (n + offset)/B, offset 0 or 1
+   * (the VISR source is not in the reference tree; see DESIGN.md "Oracle pinning"). */
+  uint32_t gain_ramp_offset;
+  uint32_t delay_ramp_offset;
+  uint32_t xfade_ramp_offset;
+  uint32_t reserved[4];
+} bear_cuda_config;
+
+/* The data-file tables `Panner` hands to the DSP constructor (visr_bear/src/panner.cpp:52-137,
+ * accessors :250-263,:408-412).  Dense, C order, host memory. */
+typedef struct bear_cuda_data {
+  uint32_t num_views;                /* V */
+  uint32_t num_virtual_loudspeakers; /* L (<= 32) */
+  uint32_t brir_length;
+  uint32_t decorrelator_length;      /* <= period_size partitions handled: any length */
+  uint32_t num_hoa_decoder_channels; /* A = (order+1)^2 (<= 64) */
+  uint32_t hoa_ir_length;
+  const float *brirs;                /* [V][L][2][brir_length] */
+  const float *delays;               /* [V][L][2] samples (only used for the default delays) */
+  const float *decorrelation_filters;/* [L][decorrelator_length] */
+  const float *hoa_irs;              /* [A][2][hoa_ir_length] */
+  double fs;
+  double decorrelation_delay;        /* samples */
+  double hoa_delay;                  /* samples */
+  uint32_t front_loudspeaker;
+  uint32_t reserved;
+} bear_cuda_data;
+
+/* Per-block tables = the DSP parameter input ports (visr_bear/src/dsp.cpp:30-53,89-96).
+ * For the batch calls every pointer addresses T consecutive blocks of the stated per-block
+ * shape.  In the single-block call a NULL pointer / negative index means "unchanged since the
+ * last block" (ports that the reference only writes on change). */
+typedef struct bear_cuda_block_tables {
+  const float *direct_gains;           /* [L][N]   direct_gains_in            dsp.cpp:32-34  */
+  const float *diffuse_gains;          /* [L][N]   diffuse_gains_in           dsp.cpp:37-39  */
+  const float *direct_delays;          /* [2N] s   direct_delays_in           dsp.cpp:30-31  */
+  const float *direct_speakers_gains;  /* [L][M]   direct_speakers_gains_in   dsp.cpp:50-53  */
+  const float *direct_speakers_delays; /* [2M] s   direct_speakers_delays_in  dsp.cpp:47-49  */
+  const float *static_delays;          /* [2L] s   static_delays_in           dsp.cpp:91-92  */
+  const int32_t *brir_index;           /* [1]      brir_index_in              dsp.cpp:89     */
+  const float *hoa_gains;              /* [A][H]   hoa_gains_in               dsp.cpp:94-96  */
+} bear_cuda_block_tables;
+
+/* ---- construction: replaces DSP::DSP + Panner table access (dsp.cpp:7-206) ------------------ */
+
+/* Build a renderer from in-memory tables.  Uploads the tables and transforms all V*2L BRIRs,
+ * the decorrelators and the HOA decode filters to partitioned spectra on the device. */
+int bear_cuda_create(const bear_cuda_config *config, const bear_cuda_data *data, bear_cuda_renderer **out);
+
+/* Same, reading a BEAR data file (TENF) with the checks and error strings of Panner::Panner
+ * (panner.cpp:52-137), check_data_file_version (data_file.cpp:16-20) and tensorfile::read
+ * (tensorfile.cpp:187-215).  On failure *out is NULL and bear_cuda_last_error(NULL) has the text. */
+int bear_cuda_create_from_file(const bear_cuda_config *config, const char *data_path, bear_cuda_renderer **out);
+
+void bear_cuda_destroy(bear_cuda_renderer *r);
+
+/* Message of the last failure on this renderer (or, with r == NULL, of the last failed create on
+ * this thread).  Valid until the next call on the same renderer/thread. */
+const char *bear_cuda_last_error(const bear_cuda_renderer *r);
+
+/* ---- per-period processing: replaces what flow.process() does for the DSP atoms -------------- */
+
+/* One period, host buffers, same buffer contract as bear::Renderer::process (api.cpp:253-259,
+ * include/bear/api.hpp:165-177): objects/direct_speakers/hoa are arrays of N/M/H pointers to
+ * period_size floats (the array may be NULL when the count is 0), output is 2 pointers. */
+int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
+                      const float *const *direct_speakers_input, const float *const *hoa_input,
+                      const bear_cuda_block_tables *tables, float *const *output);
+
+/* T consecutive periods in one call (offline rendering: bear-render pushes whole files block by
+ * block, bear/render_cli.py:398-465).  objects/direct_speakers/hoa: [count][T*B] channel-major
+ * host arrays with the given row strides (in floats); tables: T blocks each; output: [2][T*B]
+ * with row stride out_stride.  State carries over between calls exactly as between periods. */
+int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *objects, size_t objects_stride,
+                            const float *direct_speakers, size_t direct_speakers_stride, const float *hoa,
+                            size_t hoa_stride, const bear_cuda_block_tables *tables, float *output,
+                            size_t out_stride);
+
+/* ---- device-resident variant (inputs already in HBM) ---------------------------------------- */
+
+/* Device staging areas owned by the renderer.  A producer that already has audio / tables on
+ * the device writes them here and calls bear_cuda_process_device; nothing crosses PCIe. */
+typedef struct bear_cuda_device_io {
+  float *audio_in;         /* [N+M+H][audio_stride]; block data starts at column audio_offset */
+  size_t audio_stride;
+  size_t audio_offset;
+  float *direct_gains;     /* [T][L][N] */
+  float *diffuse_gains;    /* [T][L][N] */
+  float *direct_delays;    /* [T][2N] */
+  float *direct_speakers_gains;  /* [T][L][M] */
+  float *direct_speakers_delays; /* [T][2M] */
+  float *static_delays;    /* [T][2L] */
+  int32_t *brir_index;     /* [T] */
+  float *hoa_gains;        /* [T][A][H] */
+  float *audio_out;        /* [2][out_stride] */
+  size_t out_stride;
+  void *stream;            /* cudaStream_t all work of this renderer is ordered on */
+} bear_cuda_device_io;
+
+int bear_cuda_get_device_io(bear_cuda_renderer *r, bear_cuda_device_io *io);
+
+/* Render T periods from the staging areas; asynchronous on io.stream. */
+int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T);
+
+/* Block until all work queued on the renderer's stream has finished. */
+int bear_cuda_synchronize(bear_cuda_renderer *r);
+
+/* ---- introspection --------------------------------------------------------------------------- */
+
+typedef struct bear_cuda_info {
+  uint32_t num_partitions;      /* P = ceil(brir_length / B) */
+  uint32_t object_splits, cmac_splits;
+  uint32_t history_samples;
+  uint32_t kernels_per_call;    /* kernel launches one process call issues */
+  uint64_t device_bytes;        /* device memory held by this renderer */
+  uint64_t launches_total;      /* kernels launched since creation */
+  double default_direct_delay, default_static_delay; /* seconds, panner.cpp:172-186 */
+} bear_cuda_info;
+
+int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
+
+/* Pinned host memory helpers for callers that want true asynchronous copies. */
+void *bear_cuda_host_alloc(size_t bytes);
+void bear_cuda_host_free(void *p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BEAR_CUDA_H */
