@@ -125,12 +125,16 @@ __device__ __forceinline__ void lagrange3(float s, float c[4])
   c[2] = -(s * s1 * s3) * 0.5f;
   c[3] = (s * s1 * s2) * (1.0f / 6.0f);
 }
+// Delay at ramp position r, rounded product then rounded sum (no FMA): a delay near 100 samples
+// has an ulp of 7.6e-6 samples, and on white noise one ulp of delay is ~1e-6 of output, so the
+// evaluation order is kept identical to the CPU restatement.
+__device__ __forceinline__ float ramped_delay(float d0, float dd, float r) { return __fadd_rn(d0, __fmul_rn(dd, r)); }
 // y = sum_j c_j(1.5 + mu) x[-i - j] with i = floor(d + .5), mu = d - i: realised delay d + 1.5
 __device__ __forceinline__ float delayed_read(const float *__restrict__ x, float d)
 {
-  float fi = floorf(d + 0.5f);
+  float fi = floorf(__fadd_rn(d, 0.5f));
   float c[4];
-  lagrange3(1.5f + (d - fi), c);
+  lagrange3(__fadd_rn(1.5f, __fsub_rn(d, fi)), c);
   const float *q = x - (int)fi;
   float acc = c[0] * q[0];
   acc = fmaf(c[1], q[-1], acc);
@@ -244,8 +248,8 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
     __syncthreads();
     for (int ii = 0; ii < cnt; ii++) {
       const float *xr = p.xin + (size_t)(cb + ii) * p.xs + p.hist + t;
-      const float xl = delayed_read(xr, fmaf(rd, sd[ii][1], sd[ii][0]));
-      const float xR = delayed_read(xr, fmaf(rd, sd[ii][3], sd[ii][2]));
+      const float xl = delayed_read(xr, ramped_delay(sd[ii][0], sd[ii][1], rd));
+      const float xR = delayed_read(xr, ramped_delay(sd[ii][2], sd[ii][3], rd));
       const float x0 = __ldg(xr);
       const float4 *g0v = reinterpret_cast<const float4 *>(sg[ii]);
       const float4 *dgv = g0v + kMaxSpeakers / 4;
@@ -410,8 +414,8 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nch)
         const int t = 2 * n;            // window sample, both of the pair lie in the same block
         const int h = t >= p.B;
         const int nn = t - h * p.B;
-        v.x += delayed_read(wrow + t, fmaf((float)(nn + p.doff) * invB, dd[h], d0[h]));
-        v.y += delayed_read(wrow + t + 1, fmaf((float)(nn + 1 + p.doff) * invB, dd[h], d0[h]));
+        v.x += delayed_read(wrow + t, ramped_delay(d0[h], dd[h], (float)(nn + p.doff) * invB));
+        v.y += delayed_read(wrow + t + 1, ramped_delay(d0[h], dd[h], (float)(nn + 1 + p.doff) * invB));
       }
       a[n] = v;
     }

@@ -49,6 +49,14 @@ struct bear_cuda_renderer {
   std::string error;
   double default_direct_delay = 0, default_static_delay = 0;
 
+  // optional per-kernel timing: a chain of events, kernel i runs between events i and i+1
+  bool profiling = false;
+  std::vector<cudaEvent_t> ev_free;
+  std::vector<std::vector<cudaEvent_t>> ev_pending;  // one chain per profiled call
+  std::vector<std::vector<int>> ev_kernel;           // kernel id of each link
+  double prof_ms[BEAR_CUDA_NUM_KERNELS] = {0};
+  uint64_t prof_n[BEAR_CUDA_NUM_KERNELS] = {0};
+
   // staging (device) for the T blocks of the current call: slot 1 of each table
   float *audio_out = nullptr;
   // pinned host staging for the single-block API
@@ -72,6 +80,9 @@ struct bear_cuda_renderer {
     cudaSetDevice(device);
     if (stream) cudaStreamSynchronize(stream);
     for (void *p : allocs) cudaFree(p);
+    for (auto &c : ev_pending)
+      for (cudaEvent_t e : c) cudaEventDestroy(e);
+    for (cudaEvent_t e : ev_free) cudaEventDestroy(e);
     if (h_in) cudaFreeHost(h_in);
     if (h_out) cudaFreeHost(h_out);
     if (stream) cudaStreamDestroy(stream);
@@ -246,12 +257,24 @@ void run_pipeline(bear_cuda_renderer *r, int T)
 {
   Layout &p = r->lay;
   cudaStream_t st = r->stream;
-  if (p.N + p.M > 0) launch_mix(p, T, st);
-  if (p.H > 0) launch_hoa_mix(p, T, st);
-  if (p.N > 0) launch_decorrelate(p, T, st);
-  launch_bus_fdl(p, T, st);
-  launch_cmac(p, T, st);
-  launch_ifft_out(p, T, st);
+  std::vector<cudaEvent_t> chain;
+  std::vector<int> ids;
+  auto mark = [&](int kernel_id) {
+    if (!r->profiling) return;
+    cudaEvent_t e;
+    if (r->ev_free.empty()) CK(cudaEventCreate(&e));
+    else { e = r->ev_free.back(); r->ev_free.pop_back(); }
+    CK(cudaEventRecord(e, st));
+    chain.push_back(e);
+    if (kernel_id >= 0) ids.push_back(kernel_id);
+  };
+  if (p.N + p.M > 0) { mark(BEAR_CUDA_KERNEL_MIX); launch_mix(p, T, st); }
+  if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, T, st); }
+  if (p.N > 0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, T, st); }
+  mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, T, st);
+  mark(BEAR_CUDA_KERNEL_CMAC); launch_cmac(p, T, st);
+  mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, T, st);
+  mark(BEAR_CUDA_KERNEL_CARRY);
 
   CarryPlan plan{};
   int n = 0, rows = 0;
@@ -287,6 +310,11 @@ void run_pipeline(bear_cuda_renderer *r, int T)
   plan.n = n;
   plan.row_start[n] = rows;
   launch_carry(plan, st);
+  mark(-1);
+  if (r->profiling) {
+    r->ev_pending.push_back(std::move(chain));
+    r->ev_kernel.push_back(std::move(ids));
+  }
   CK(cudaGetLastError());
   r->launches += r->kernels_per_call;
   p.fdl_head = (p.fdl_head + T) % p.R;
@@ -358,6 +386,57 @@ void upload_tables(bear_cuda_renderer *r, int T, const bear_cuda_block_tables *t
   }
 }
 
+// The tables Panner::Panner unpacks from a data file, with its checks (panner.cpp:52-137).
+struct LoadedData {
+  tenf::File tf;
+  tenf::FloatTensor views, brirs, delays, dec, hoa;
+  bear_cuda_data d{};
+  LoadedData(const char *path, bool need_tables) : tf(path)
+  {
+    (void)need_tables;
+    const tenf::Json &m = tf.metadata();
+    auto check = [](bool ok, const char *msg) {
+      if (!ok) throw std::runtime_error(std::string("BEAR data file error: ") + msg);               // panner.cpp:43-46
+    };
+    if (const tenf::Json *v = m.find("bear_data_version")) {                                         // data_file.cpp:6-20
+      if (v->kind != tenf::Json::Number || !v->is_int) throw std::runtime_error("version must be an integer");
+      if (v->inum > 0)
+        throw std::runtime_error("data file version mismatch: expected 0, got " + std::to_string(v->inum));
+    }
+    views = tf.unpack_f32(m.at("views")); brirs = tf.unpack_f32(m.at("brirs"));
+    delays = tf.unpack_f32(m.at("delays")); dec = tf.unpack_f32(m.at("decorrelation_filters"));
+    check(views.shape.size() == 2, "views must have 2 dimensions");                                  // panner.cpp:67-92
+    check(brirs.shape.size() == 4, "brirs must have 4 dimensions");
+    check(delays.shape.size() == 3, "delays must have 3 dimensions");
+    check(dec.shape.size() == 2, "decorrelation_filters must have 2 dimensions");
+    const size_t V = brirs.shape[0], L = brirs.shape[1];
+    check(views.shape[0] == V, "views axis 0 is wrong size");
+    check(views.shape[1] == 3, "views axis 1 is wrong size");
+    check(brirs.shape[2] == 2, "brirs axis 2 is wrong size");
+    check(delays.shape[0] == V, "delays axis 0 is wrong size");
+    check(delays.shape[1] == L, "delays axis 1 is wrong size");
+    check(delays.shape[2] == 2, "delays axis 2 is wrong size");
+    check(dec.shape[0] == L, "decorrelation filters axis 0 is wrong size");
+    check(m.has("hoa"), "HOA decoder not present");                                                  // panner.cpp:125
+    hoa = tf.unpack_f32(m.at("hoa").at("irs"));
+    check(hoa.shape.size() == 3, "HOA decoder must have 3 dimensions");
+    check(hoa.shape[1] == 2, "HOA decoder axis 1 is wrong size");
+    const size_t order = (size_t)std::llround(std::sqrt((double)hoa.shape[0])) - 1;
+    if ((order + 1) * (order + 1) != hoa.shape[0]) throw std::logic_error("bad number of hoa channels");
+
+    d.num_views = (uint32_t)V; d.num_virtual_loudspeakers = (uint32_t)L;
+    d.brir_length = (uint32_t)brirs.shape[3]; d.decorrelator_length = (uint32_t)dec.shape[1];
+    d.num_hoa_decoder_channels = (uint32_t)hoa.shape[0]; d.hoa_ir_length = (uint32_t)hoa.shape[2];
+    d.brirs = brirs.data.data(); d.delays = delays.data.data();
+    d.decorrelation_filters = dec.data.data(); d.hoa_irs = hoa.data.data();
+    d.fs = m.at("fs").num;
+    d.decorrelation_delay = (double)(size_t)m.at("decorrelation_delay").num;                         // panner.cpp:62
+    d.front_loudspeaker = (uint32_t)m.at("front_loudspeaker").num;
+    const tenf::Json *hd = m.at("hoa").find("delay");
+    d.hoa_delay = hd ? hd->num : 0.0;
+  }
+};
+
 }  // namespace
 
 // ================================================================================================
@@ -379,49 +458,64 @@ int bear_cuda_create_from_file(const bear_cuda_config *config, const char *data_
     if (!config || !out) throw InvalidArgument{"NULL argument"};
     if (config->period_size == 0) throw InvalidArgument{"Config: period size must be set"};          // api.cpp:70
     if (!data_path || !*data_path) throw InvalidArgument{"Config: data path must be set"};           // api.cpp:71
-    tenf::File tf(data_path);
-    const tenf::Json &m = tf.metadata();
-    auto check = [](bool ok, const char *msg) {
-      if (!ok) throw std::runtime_error(std::string("BEAR data file error: ") + msg);               // panner.cpp:43-46
-    };
-    if (const tenf::Json *v = m.find("bear_data_version")) {                                         // data_file.cpp:6-20
-      if (v->kind != tenf::Json::Number || !v->is_int) throw std::runtime_error("version must be an integer");
-      if (v->inum > 0)
-        throw std::runtime_error("data file version mismatch: expected 0, got " + std::to_string(v->inum));
-    }
-    tenf::FloatTensor views = tf.unpack_f32(m.at("views")), brirs = tf.unpack_f32(m.at("brirs")),
-                      delays = tf.unpack_f32(m.at("delays")), dec = tf.unpack_f32(m.at("decorrelation_filters"));
-    check(views.shape.size() == 2, "views must have 2 dimensions");                                  // panner.cpp:67-92
-    check(brirs.shape.size() == 4, "brirs must have 4 dimensions");
-    check(delays.shape.size() == 3, "delays must have 3 dimensions");
-    check(dec.shape.size() == 2, "decorrelation_filters must have 2 dimensions");
-    const size_t V = brirs.shape[0], L = brirs.shape[1];
-    check(views.shape[0] == V, "views axis 0 is wrong size");
-    check(views.shape[1] == 3, "views axis 1 is wrong size");
-    check(brirs.shape[2] == 2, "brirs axis 2 is wrong size");
-    check(delays.shape[0] == V, "delays axis 0 is wrong size");
-    check(delays.shape[1] == L, "delays axis 1 is wrong size");
-    check(delays.shape[2] == 2, "delays axis 2 is wrong size");
-    check(dec.shape[0] == L, "decorrelation filters axis 0 is wrong size");
-    check(m.has("hoa"), "HOA decoder not present");                                                  // panner.cpp:125
-    tenf::FloatTensor hoa = tf.unpack_f32(m.at("hoa").at("irs"));
-    check(hoa.shape.size() == 3, "HOA decoder must have 3 dimensions");
-    check(hoa.shape[1] == 2, "HOA decoder axis 1 is wrong size");
-    const size_t order = (size_t)std::llround(std::sqrt((double)hoa.shape[0])) - 1;
-    if ((order + 1) * (order + 1) != hoa.shape[0]) throw std::runtime_error("bad number of hoa channels");
+    LoadedData ld(data_path, true);
+    *out = create_impl(*config, ld.d);
+  });
+}
 
-    bear_cuda_data d{};
-    d.num_views = (uint32_t)V; d.num_virtual_loudspeakers = (uint32_t)L;
-    d.brir_length = (uint32_t)brirs.shape[3]; d.decorrelator_length = (uint32_t)dec.shape[1];
-    d.num_hoa_decoder_channels = (uint32_t)hoa.shape[0]; d.hoa_ir_length = (uint32_t)hoa.shape[2];
-    d.brirs = brirs.data.data(); d.delays = delays.data.data();
-    d.decorrelation_filters = dec.data.data(); d.hoa_irs = hoa.data.data();
-    d.fs = m.at("fs").num;
-    d.decorrelation_delay = (double)(size_t)m.at("decorrelation_delay").num;                         // panner.cpp:62
-    d.front_loudspeaker = (uint32_t)m.at("front_loudspeaker").num;
-    const tenf::Json *hd = m.at("hoa").find("delay");
-    d.hoa_delay = hd ? hd->num : 0.0;
-    *out = create_impl(*config, d);
+int bear_cuda_read_data_file_info(const char *data_path, bear_cuda_data_file_info *info)
+{
+  return guarded(nullptr, [&] {
+    if (!data_path || !info) throw InvalidArgument{"NULL argument"};
+    std::memset(info, 0, sizeof(*info));
+    LoadedData ld(data_path, false);
+    const bear_cuda_data &d = ld.d;
+    info->num_views = d.num_views; info->num_virtual_loudspeakers = d.num_virtual_loudspeakers;
+    info->brir_length = d.brir_length; info->decorrelator_length = d.decorrelator_length;
+    info->num_hoa_decoder_channels = d.num_hoa_decoder_channels; info->hoa_ir_length = d.hoa_ir_length;
+    info->front_loudspeaker = d.front_loudspeaker;
+    info->fs = d.fs; info->decorrelation_delay = d.decorrelation_delay; info->hoa_delay = d.hoa_delay;
+    // DataFileMetadata::read_from_file, api.cpp:330-353
+    if (const tenf::Json *md = ld.tf.metadata().find("metadata")) {
+      if (md->kind != tenf::Json::Object) throw std::runtime_error("data file metadata should be object");
+      info->has_metadata = 1;
+      const tenf::Json *label = md->find("label");
+      if (!label) throw std::runtime_error("expected label");
+      if (label->kind != tenf::Json::String) throw std::runtime_error("label should be a string");
+      std::snprintf(info->label, sizeof(info->label), "%s", label->str.c_str());
+      if (const tenf::Json *desc = md->find("description")) {
+        if (desc->kind != tenf::Json::String) throw std::runtime_error("description should be a string");
+        std::snprintf(info->description, sizeof(info->description), "%s", desc->str.c_str());
+      }
+      const tenf::Json *rel = md->find("released");
+      if (!rel) throw std::runtime_error("expected released");
+      if (rel->kind != tenf::Json::Bool) throw std::runtime_error("released should be a bool");
+      info->is_released = rel->b;
+    }
+  });
+}
+
+int bear_cuda_tenf_read_f32(const char *path, const char *key, float *out, size_t capacity, size_t *count,
+                            uint32_t *shape, uint32_t *ndim)
+{
+  return guarded(nullptr, [&] {
+    if (!path || !key) throw InvalidArgument{"NULL argument"};
+    tenf::File tf(path);
+    const tenf::Json *node = &tf.metadata();
+    std::string k(key);
+    size_t pos = 0;
+    while (pos <= k.size()) {
+      size_t next = k.find('/', pos);
+      if (next == std::string::npos) next = k.size();
+      if (next > pos) node = &node->at(k.substr(pos, next - pos));
+      pos = next + 1;
+    }
+    tenf::FloatTensor t = tf.unpack_f32(*node);
+    if (count) *count = t.size();
+    if (ndim) *ndim = (uint32_t)t.shape.size();
+    if (shape)
+      for (size_t i = 0; i < t.shape.size() && i < 8; i++) shape[i] = (uint32_t)t.shape[i];
+    if (out && capacity) std::memcpy(out, t.data.data(), std::min(capacity, t.size()) * sizeof(float));
   });
 }
 
@@ -537,6 +631,42 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info)
   info->default_direct_delay = r->default_direct_delay;
   info->default_static_delay = r->default_static_delay;
   return BEAR_CUDA_OK;
+}
+
+int bear_cuda_set_profiling(bear_cuda_renderer *r, int enable)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  r->profiling = enable != 0;
+  return BEAR_CUDA_OK;
+}
+
+int bear_cuda_get_profile(bear_cuda_renderer *r, bear_cuda_kernel_profile *out, int reset)
+{
+  if (!r || !out) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    CK(cudaStreamSynchronize(r->stream));
+    for (size_t c = 0; c < r->ev_pending.size(); c++) {
+      auto &chain = r->ev_pending[c];
+      for (size_t i = 0; i + 1 < chain.size(); i++) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, chain[i], chain[i + 1]));
+        r->prof_ms[r->ev_kernel[c][i]] += ms;
+        r->prof_n[r->ev_kernel[c][i]]++;
+      }
+      for (cudaEvent_t e : chain) r->ev_free.push_back(e);
+    }
+    r->ev_pending.clear();
+    r->ev_kernel.clear();
+    static const char *names[BEAR_CUDA_NUM_KERNELS] = {"mix_kernel", "hoa_mix_kernel", "decorrelate_kernel",
+                                                       "bus_fdl_kernel", "cmac_kernel", "ifft_out_kernel",
+                                                       "carry_kernel"};
+    for (int k = 0; k < BEAR_CUDA_NUM_KERNELS; k++) {
+      std::snprintf(out[k].name, sizeof(out[k].name), "%s", names[k]);
+      out[k].total_ms = r->prof_ms[k];
+      out[k].launches = r->prof_n[k];
+      if (reset) { r->prof_ms[k] = 0; r->prof_n[k] = 0; }
+    }
+  });
 }
 
 void *bear_cuda_host_alloc(size_t bytes)

@@ -72,12 +72,29 @@ class Info(C.Structure):
     ]
 
 
+class DataFileInfo(C.Structure):
+    _fields_ = [
+        ("has_metadata", C.c_int32), ("is_released", C.c_int32), ("label", C.c_char * 256),
+        ("description", C.c_char * 1024),
+        ("num_views", C.c_uint32), ("num_virtual_loudspeakers", C.c_uint32), ("brir_length", C.c_uint32),
+        ("decorrelator_length", C.c_uint32), ("num_hoa_decoder_channels", C.c_uint32),
+        ("hoa_ir_length", C.c_uint32), ("front_loudspeaker", C.c_uint32), ("reserved", C.c_uint32),
+        ("fs", C.c_double), ("decorrelation_delay", C.c_double), ("hoa_delay", C.c_double),
+    ]
+
+
 EXPORTS = (
     "bear_cuda_create", "bear_cuda_create_from_file", "bear_cuda_destroy", "bear_cuda_last_error",
     "bear_cuda_process", "bear_cuda_process_batch", "bear_cuda_get_device_io",
     "bear_cuda_process_device", "bear_cuda_synchronize", "bear_cuda_get_info",
-    "bear_cuda_host_alloc", "bear_cuda_host_free",
+    "bear_cuda_host_alloc", "bear_cuda_host_free", "bear_cuda_read_data_file_info",
+    "bear_cuda_tenf_read_f32", "bear_cuda_set_profiling", "bear_cuda_get_profile",
 )
+NUM_KERNELS = 7
+
+
+class KernelProfile(C.Structure):
+    _fields_ = [("name", C.c_char * 32), ("total_ms", C.c_double), ("launches", C.c_uint64)]
 
 
 def build(force=False):
@@ -114,6 +131,11 @@ def lib():
         l.bear_cuda_host_alloc.restype = vp
         l.bear_cuda_host_free.argtypes = [vp]
         l.bear_cuda_host_free.restype = None
+        l.bear_cuda_read_data_file_info.argtypes = [C.c_char_p, C.POINTER(DataFileInfo)]
+        l.bear_cuda_tenf_read_f32.argtypes = [C.c_char_p, C.c_char_p, vp, sz, C.POINTER(sz),
+                                              C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        l.bear_cuda_set_profiling.argtypes = [vp, C.c_int]
+        l.bear_cuda_get_profile.argtypes = [vp, C.POINTER(KernelProfile), C.c_int]
         _lib = l
     return _lib
 
@@ -129,6 +151,30 @@ def _raise(code, message):
     if code == ERR_INVALID_ARGUMENT:
         raise ValueError(message)
     raise BearCudaError(code, message)
+
+
+def read_data_file_info(path):
+    """bear::DataFileMetadata::read_from_file (api.hpp:261-287) + table dimensions; host only."""
+    info = DataFileInfo()
+    rc = lib().bear_cuda_read_data_file_info(str(path).encode(), C.byref(info))
+    if rc != OK:
+        _raise(rc, lib().bear_cuda_last_error(None).decode())
+    return info
+
+
+def tenf_read_f32(path, key):
+    """Read one array of a TENF file through the C++ reader; host only."""
+    l = lib()
+    count, ndim, shape = C.c_size_t(), C.c_uint32(), (C.c_uint32 * 8)()
+    rc = l.bear_cuda_tenf_read_f32(str(path).encode(), key.encode(), None, 0, C.byref(count), shape, C.byref(ndim))
+    if rc != OK:
+        _raise(rc, l.bear_cuda_last_error(None).decode())
+    out = np.empty(count.value, np.float32)
+    rc = l.bear_cuda_tenf_read_f32(str(path).encode(), key.encode(), C.c_void_p(out.ctypes.data), out.size,
+                                   C.byref(count), shape, C.byref(ndim))
+    if rc != OK:
+        _raise(rc, l.bear_cuda_last_error(None).decode())
+    return out.reshape([shape[i] for i in range(ndim.value)])
 
 
 def pinned_empty(shape, dtype=np.float32):
@@ -299,6 +345,15 @@ class Renderer:
 
     def process_device(self, T):
         self._check(self._l.bear_cuda_process_device(self._h, T))
+
+    def set_profiling(self, enable):
+        self._check(self._l.bear_cuda_set_profiling(self._h, int(enable)))
+
+    def get_profile(self, reset=True):
+        """{kernel name: (total ms, launches)} from CUDA events on the renderer's stream."""
+        arr = (KernelProfile * NUM_KERNELS)()
+        self._check(self._l.bear_cuda_get_profile(self._h, arr, int(reset)))
+        return {e.name.decode(): (e.total_ms, e.launches) for e in arr}
 
     def synchronize(self):
         self._check(self._l.bear_cuda_synchronize(self._h))

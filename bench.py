@@ -1,0 +1,364 @@
+#!/usr/bin/env python
+"""Benchmark of the BEAR render hot path (BASELINE.json metric: object-channels rendered in real
+time at 48 kHz, N x RTF).
+
+A step = one pass of the hot path over T periods of synthetic input of BASELINE.json configs[1]
+("64 moving Objects with per-block metadata changes, block size 512"; the listener yaw steps 2
+degrees per block so every block crossfades to a new BRIR view) per GPU.  With --gpus N each rank
+renders its own group of 64 objects of one 64*N-object scene and the per-step stereo partial mixes
+are summed with an NCCL all-reduce (weak scaling).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+ours:      value = device-resident throughput (audio and tables already in HBM), CUDA events on the
+           renderer's stream; e2e = the same metric through the host-buffer C-ABI call
+           (bear_cuda_process_batch: pinned host -> device -> kernels -> host).
+reference: the CPU implementation of the same path (the oracle port; the reference renderer itself
+           needs VISR + Boost, which are not available) on all host cores, one instance per core.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+FS = 48000
+METRIC = "object-channels rendered real-time at 48 kHz per B200 (N x RTF)"
+UNIT = "object-channels x RTF"
+WORKLOADS = {
+    # name: (scenario, period, objects per GPU)
+    "cfg2_ht": ("cfg2_ht", 512, 64),
+    "cfg4_ht": ("cfg4_ht", 256, 1024),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="cfg2_ht", choices=sorted(WORKLOADS))
+    ap.add_argument("--seconds", type=float, default=10.0, help="audio seconds per step and GPU")
+    ap.add_argument("--cpu-sample-blocks", type=int, default=0, help="blocks of the CPU sample (0 = auto)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------- workload
+def make_workload(workload, T, group=0, num_views=180, seed=0):
+    """Synthetic default-shaped data file + tables + audio for T periods of one object group."""
+    from bear_b200 import control, data_file
+    scen, B, _ = WORKLOADS[workload]
+    data = data_file.from_tree(data_file.synthetic_tree(seed=seed, num_views=num_views))
+    ctl = control.HostControl(data)
+    N, M, H, tb = control.scenario(ctl, scen, T, B, seed=1000 + group)
+    if num_views != 180:  # reduced view table for CPU samples: cycle through the views that exist
+        tb["brir_index"] = (np.arange(T) % num_views).astype(np.int32)
+        tb["static_delays"] = ctl.static_delays(tb["brir_index"]).astype(np.float32)
+    scale = 0.1 if N <= 64 else 0.02
+    audio = control.synth_audio(N, T * B, seed_base=10000 * group, scale=scale)
+    return data, ctl, N, B, tb, audio
+
+
+# ------------------------------------------------------------------------------------------- clocks
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons at 200 ms during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            f = tempfile.NamedTemporaryFile("w", suffix=".csv", delete=False)
+            self.path = f.name
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=f,
+                                         stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        self.proc.wait()
+        sm, smax, reasons = [], None, set()
+        for line in open(self.path):
+            p = [x.strip() for x in line.split(",")]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1])); smax = float(p[2])
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), p[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        os.unlink(self.path)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": smax, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------- CPU legs
+_W = {}
+
+
+def _cpu_worker_init(workload, T, num_views):
+    sys.path.insert(0, str(ROOT))
+    from oracle import bear_ref
+    data, ctl, N, B, tb, audio = make_workload(workload, T, num_views=num_views)
+    _W.update(r=bear_ref.RefRenderer(data, N, 0, 0, B), blocks=tb.blocks(), audio=audio, N=N, B=B, T=T)
+
+
+def _cpu_worker_step(_):
+    t0 = time.perf_counter()
+    _W["r"].render(_W["audio"], None, None, _W["blocks"])
+    return time.perf_counter() - t0
+
+
+def cpu_sample_blocks(args):
+    if args.cpu_sample_blocks:
+        return args.cpu_sample_blocks
+    return 48 if args.workload == "cfg2_ht" else 24
+
+
+def cpu_baseline_single(args):
+    """Oracle port on one host core, bounded sample of the same workload (~10-20 s of CPU work)."""
+    T = cpu_sample_blocks(args)
+    _cpu_worker_init(args.workload, T, num_views=min(180, T))
+    _cpu_worker_step(0)  # warm
+    reps, total = 0, 0.0
+    while total < 10.0 and reps < 64:
+        total += _cpu_worker_step(0)
+        reps += 1
+    N, B = _W["N"], _W["B"]
+    audio_s = reps * T * B / FS
+    return {"value": N * audio_s / total, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "%d x %d periods of %d (%.2f s of audio) of the same workload, oracle/bear_ref f32, 1 thread"
+                      % (reps, T, B, audio_s)}
+
+
+def run_reference(args, rank):
+    """--impl reference: the CPU path on all host cores (one renderer instance per core, each renders
+    the bounded sample; a bear::Renderer is single-threaded, visr_bear/src/dynamic_renderer.hpp:14-15)."""
+    if rank != 0:
+        return
+    import multiprocessing as mp
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
+    T = cpu_sample_blocks(args)
+    scen, B, N = WORKLOADS[args.workload]
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores, initializer=_cpu_worker_init, initargs=(args.workload, T, min(180, T))) as pool:
+        for _ in range(max(1, args.warmup)):
+            pool.map(_cpu_worker_step, range(cores), chunksize=1)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            pool.map(_cpu_worker_step, range(cores), chunksize=1)
+        wall = time.perf_counter() - t0
+    audio_s = T * B / FS
+    value = cores * N * audio_s * args.steps / wall
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, T, cores),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": "%d instances x %d periods of %d per step, oracle/bear_ref f32 (the reference "
+                                   "renderer needs VISR+Boost: unbuildable here)" % (cores, T, B)},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config(args, T, instances=None):
+    scen, B, N = WORKLOADS[args.workload]
+    c = {"workload": "BASELINE configs[1]: 64 moving Objects, per-block metadata, block 512, listener yaw 2 deg/block "
+                     "(view crossfade every block)" if args.workload == "cfg2_ht" else
+                     "BASELINE configs[3] shape: 1024 moving Objects, block 256, view crossfade every block",
+         "objects_per_gpu": N, "period": B, "periods_per_step": T, "audio_seconds_per_step": T * B / FS,
+         "data_file": "synthetic default shape (180 views x 24 x 2 x 2976 taps, 128-tap decorrelators)",
+         "sharding": "object groups, NCCL all-reduce of stereo partial mixes" if args.gpus > 1 else "single GPU",
+         "l2": "inputs larger than L2 (audio + spectra streamed per step >> 126 MB)"}
+    if instances:
+        c["cpu_instances"] = instances
+    return c
+
+
+# ------------------------------------------------------------------------------------------- GPU leg
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+
+    from bear_b200 import device_io
+    from bear_b200.renderer import Renderer, pinned_empty
+
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    scen, B, N = WORKLOADS[args.workload]
+    T = max(8, int(args.seconds * FS / B) // 8 * 8)
+    data, ctl, N, B, tb, audio = make_workload(args.workload, T, group=rank)
+    r = Renderer(data, N, 0, 0, B, max_batch_blocks=T, device=local_rank)
+    io = device_io.DeviceBuffers(r, device_index=local_rank)
+    io.load_audio(audio)
+    io.load_tables(tb)
+    r.synchronize()
+    stream = io.stream
+    out_dev = io.output(T)
+
+    def barrier():
+        r.synchronize()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def step_resident():
+        r.process_device(T)
+        if world > 1:
+            with torch.cuda.stream(stream):
+                dist.all_reduce(out_dev)
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        e1.synchronize()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device="cuda")
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    for _ in range(max(3, args.warmup)):
+        step_resident()
+    clocks = ClockSampler(local_rank)
+    if rank == 0:
+        clocks.start()
+    r.set_profiling(True)
+    r.get_profile(reset=True)
+    launches0 = r.get_info().launches_total
+    ms = timed(step_resident, args.steps)
+    launches = r.get_info().launches_total - launches0
+    prof = r.get_profile(reset=True)
+    r.set_profiling(False)
+
+    # ---- end to end: pinned host buffers through the host-buffer entry point -------------------
+    h_audio = pinned_empty(audio.shape); h_audio[:] = audio
+    h_tb = type(tb)({k: pinned_empty(v.shape, v.dtype) for k, v in tb.items()})
+    for k, v in tb.items():
+        h_tb[k][...] = v
+    h_out = pinned_empty((2, T * B))
+    h2d = audio.nbytes + sum(v.nbytes for v in tb.values())
+    d2h = h_out.nbytes
+
+    def step_e2e():
+        if world == 1:
+            r.process_batch(h_audio, None, None, h_tb, output=h_out)
+        else:
+            io.load_audio(h_audio)
+            io.load_tables(h_tb)
+            r.process_device(T)
+            with torch.cuda.stream(stream):
+                dist.all_reduce(out_dev)
+                torch.from_numpy(h_out).copy_(out_dev, non_blocking=True)
+            stream.synchronize()
+
+    e2e_steps = max(3, min(args.steps, 10))
+    for _ in range(2):
+        step_e2e()
+    ms_e2e = timed(step_e2e, e2e_steps)
+    clk = clocks.stop() if rank == 0 else None
+
+    audio_s = T * B / FS
+    value = world * N * audio_s * args.steps / (ms * 1e-3)
+    e2e_value = world * N * audio_s * e2e_steps / (ms_e2e * 1e-3)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text())
+        except Exception:
+            pass
+        peak, which = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks else \
+            (6650.0, "fallback (B200_PROFILING.md)")
+        info = r.get_info()
+        L, A, P, KS = data.num_virtual_loudspeakers, data.n_hoa_channels, info.num_partitions, info.cmac_splits
+        # cmac_kernel algorithmic bytes per launch (DESIGN.md "Roofline"): per period and ear, 24*P terms of
+        # B packed bins (8 B each): FDL read once, filter spectra read once per rendered view (2 in a
+        # view-change block), partial spectra written once per rendered view.
+        views_rendered = 2.0  # every block of this workload changes view
+        alg = T * 2 * 8 * B * (L * P + L * P * views_rendered + KS * views_rendered)
+        t_cmac, n_cmac = prof["cmac_kernel"]
+        avg_ms = t_cmac / max(n_cmac, 1)
+        achieved = alg / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
+        step_ms_kernels = sum(v[0] for v in prof.values()) / max(args.steps, 1)
+        traffic = None
+        tpath = ROOT / "profiles" / "cmac_traffic.json"
+        if tpath.exists():
+            try:
+                traffic = json.loads(tpath.read_text()).get(args.workload)
+            except Exception:
+                traffic = None
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, T),
+            "rtf_per_gpu": audio_s * args.steps / (ms * 1e-3),
+            "roofline": {"bound": "hbm", "kernel": "cmac_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": achieved / peak, "traffic": traffic, "peak_source": which,
+                         "algorithmic_bytes_per_launch": alg, "avg_launch_ms": avg_ms,
+                         "share_of_step": (t_cmac / max(args.steps, 1)) / step_ms_kernels if step_ms_kernels else None},
+            "kernel_ms_per_step": {k: v[0] / max(args.steps, 1) for k, v in prof.items() if v[1]},
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                    "ms_per_step": ms_e2e / e2e_steps, "steps": e2e_steps,
+                    "api": "bear_cuda_process_batch (pinned host buffers)" if world == 1 else
+                           "pinned host -> staging areas -> bear_cuda_process_device -> NCCL all-reduce -> pinned host"},
+            "gpu_launches": int(launches),
+            "clocks": clk,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_single(args)
+        print(json.dumps(line), flush=True)
+    r.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+    if world != args.gpus:
+        if args.gpus > 1 and world == 1:
+            raise SystemExit("launch with torchrun for --gpus > 1 (see the header of this file)")
+    run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -163,6 +163,49 @@ typedef struct bear_cuda_info {
 
 int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
 
+/* Per-kernel device timing (CUDA events on the renderer's stream, recorded around every kernel
+ * while enabled).  bear_cuda_get_profile synchronises the stream and fills
+ * BEAR_CUDA_NUM_KERNELS entries, indexed by the BEAR_CUDA_KERNEL_* ids. */
+#define BEAR_CUDA_KERNEL_MIX 0
+#define BEAR_CUDA_KERNEL_HOA_MIX 1
+#define BEAR_CUDA_KERNEL_DECORRELATE 2
+#define BEAR_CUDA_KERNEL_BUS_FDL 3
+#define BEAR_CUDA_KERNEL_CMAC 4
+#define BEAR_CUDA_KERNEL_IFFT_OUT 5
+#define BEAR_CUDA_KERNEL_CARRY 6
+#define BEAR_CUDA_NUM_KERNELS 7
+
+typedef struct bear_cuda_kernel_profile {
+  char name[32];
+  double total_ms;
+  uint64_t launches;
+} bear_cuda_kernel_profile;
+
+int bear_cuda_set_profiling(bear_cuda_renderer *r, int enable);
+int bear_cuda_get_profile(bear_cuda_renderer *r, bear_cuda_kernel_profile *out, int reset);
+
+/* ---- data-file access (host only, no GPU needed) ---------------------------------------------- */
+
+/* Replaces bear::DataFileMetadata::read_from_file (include/bear/api.hpp:261-287,
+ * visr_bear/src/api.cpp:330-353) plus the dimensions Panner exposes (panner.hpp:55-57,84-106). */
+typedef struct bear_cuda_data_file_info {
+  int32_t has_metadata, is_released;
+  char label[256];
+  char description[1024];
+  uint32_t num_views, num_virtual_loudspeakers, brir_length, decorrelator_length;
+  uint32_t num_hoa_decoder_channels, hoa_ir_length, front_loudspeaker, reserved;
+  double fs, decorrelation_delay, hoa_delay;
+} bear_cuda_data_file_info;
+
+int bear_cuda_read_data_file_info(const char *data_path, bear_cuda_data_file_info *info);
+
+/* Read one array of a TENF file as float32 in C order (replaces tensorfile::read +
+ * TensorFile::unpack, visr_bear/src/tensorfile.cpp:165-215).  `key` is a '/'-separated path into
+ * the JSON metadata, e.g. "hoa/irs".  shape receives up to 8 extents; *ndim their number; at most
+ * capacity floats are written; *count receives the element count of the array. */
+int bear_cuda_tenf_read_f32(const char *path, const char *key, float *out, size_t capacity, size_t *count,
+                            uint32_t *shape, uint32_t *ndim);
+
 /* Pinned host memory helpers for callers that want true asynchronous copies. */
 void *bear_cuda_host_alloc(size_t bytes);
 void bear_cuda_host_free(void *p);

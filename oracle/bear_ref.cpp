@@ -123,12 +123,14 @@ inline real ramp_value(int n, int steps, int offset) { return (real)(n + offset)
 // ------------------------------------------------------------------------------------------
 struct GainMatrix {
   int n_in = 0, n_out = 0, B = 0, off = 1;
-  std::vector<real> prev, next;
+  std::vector<real> prev, next, ramp;
   void setup(int in, int out, int period, int ramp_offset)
   {
     n_in = in; n_out = out; B = period; off = ramp_offset;
     prev.assign((size_t)in * out, 0);
     next.assign((size_t)in * out, 0);
+    ramp.resize(B);
+    for (int n = 0; n < B; n++) ramp[n] = ramp_value(n, B, off);
   }
   // gains: row-major [n_out][n_in], may be null (no change)
   void process(const float *gains, const real *const *in, real *const *out)
@@ -141,7 +143,8 @@ struct GainMatrix {
       for (int i = 0; i < n_in; i++) {
         real g0 = prev[(size_t)o * n_in + i], dg = next[(size_t)o * n_in + i] - g0;
         const real *x = in[i];
-        for (int n = 0; n < B; n++) y[n] += x[n] * (g0 + dg * ramp_value(n, B, off));
+        const real *rp = ramp.data();
+        for (int n = 0; n < B; n++) y[n] += x[n] * (g0 + dg * rp[n]);
       }
     }
     prev = next;
@@ -166,18 +169,19 @@ inline void lagrange3(real s, real c[4])
 //   i = floor(d + 0.5), mu = d - i in [-0.5, 0.5), y[n] = sum_j c_j(1.5 + mu) x[n - i - j].
 // ------------------------------------------------------------------------------------------
 struct DelayVector {
-  int ch = 0, B = 0, off = 1, ring = 0, pos = 0;
+  int ch = 0, B = 0, off = 1, hist = 0;
   real fs = 48000;
-  std::vector<real> buf, cur, next;
+  std::vector<real> buf, cur, next, ramp;  // buf: per channel [hist past samples | B current samples]
   void setup(int channels, int period, double sample_rate, double initial_seconds, int max_delay_samples,
              int ramp_offset)
   {
     ch = channels; B = period; off = ramp_offset; fs = (real)sample_rate;
-    ring = max_delay_samples + period + 8;
-    buf.assign((size_t)ch * ring, 0);
+    hist = max_delay_samples + 8;
+    buf.assign((size_t)ch * (hist + B), 0);
     cur.assign(ch, (real)initial_seconds * fs);
     next = cur;
-    pos = 0;
+    ramp.resize(B);
+    for (int n = 0; n < B; n++) ramp[n] = ramp_value(n, B, off);
   }
   // delays_seconds: [ch] or null (no change)
   void process(const float *delays_seconds, const real *const *in, real *const *out)
@@ -185,21 +189,20 @@ struct DelayVector {
     if (delays_seconds)
       for (int c = 0; c < ch; c++) next[c] = (real)delays_seconds[c] * fs;
     for (int c = 0; c < ch; c++) {
-      real *rb = &buf[(size_t)c * ring];
-      for (int n = 0; n < B; n++) rb[(pos + n) % ring] = in[c][n];
+      real *rb = &buf[(size_t)c * (hist + B)];
+      std::memmove(rb, rb + B, sizeof(real) * hist);
+      std::memcpy(rb + hist, in[c], sizeof(real) * B);
+      const real *now = rb + hist;
       real d0 = cur[c], dd = next[c] - d0;
       for (int n = 0; n < B; n++) {
-        real d = d0 + dd * ramp_value(n, B, off);
+        real d = d0 + dd * ramp[n];
         real fi = std::floor(d + (real)0.5);
         real coef[4];
         lagrange3((real)1.5 + (d - fi), coef);
-        int base = pos + n - (int)fi + 4 * ring;
-        real acc = 0;
-        for (int j = 0; j < 4; j++) acc += coef[j] * rb[(base - j) % ring];
-        out[c][n] = acc;
+        const real *q = now + n - (int)fi;
+        out[c][n] = coef[0] * q[0] + coef[1] * q[-1] + coef[2] * q[-2] + coef[3] * q[-3];
       }
     }
-    pos = (pos + B) % ring;
     cur = next;
   }
 };

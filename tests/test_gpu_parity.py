@@ -1,0 +1,238 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+Bar (BASELINE.json north_star): max-abs error <= 1e-5 and relative error energy <= -100 dB."""
+import numpy as np
+import pytest
+
+from bear_b200 import control, data_file
+from conftest import GOLDEN, rel_err_db
+
+pytestmark = pytest.mark.gpu
+
+ATOL = 1e-5
+REL_DB = -100.0
+
+
+def check(out, ref, what=""):
+    e = np.abs(out.astype(np.float64) - ref).max()
+    db = rel_err_db(out, ref)
+    assert e <= ATOL and db <= REL_DB, "%s: max-abs %.3e, rel %.1f dB" % (what, e, db)
+
+
+def gpu_render(data, N, M, H, B, tb, obj, ds, hoa, mode, **kw):
+    from bear_b200.renderer import Renderer
+    T = tb.num_blocks
+    if mode == "stream":
+        with Renderer(data, N, M, H, B, max_batch_blocks=1, **kw) as r:
+            out = np.zeros((2, T * B), np.float32)
+            for k in range(T):
+                s = slice(k * B, (k + 1) * B)
+                out[:, s] = r.process(obj[:, s] if N else None, ds[:, s] if M else None,
+                                      hoa[:, s] if H else None, tb.block(k))
+            return out
+    batch = T if mode == "batch" else int(mode[5:])
+    with Renderer(data, N, M, H, B, max_batch_blocks=batch, **kw) as r:
+        return r.render(obj, ds, hoa, tb, batch=batch)
+
+
+def ref_render(oracle, data, N, M, H, B, tb, obj, ds, hoa, **kw):
+    r = oracle.RefRenderer(data, N, M, H, B, **kw)
+    out = r.render(obj, ds, hoa, tb.blocks())
+    r.close()
+    return out
+
+
+def case_tables(ctl, name, T, rng):
+    az1 = rng.uniform(-180, 180, size=(T, 1))
+    az5 = rng.uniform(-180, 180, size=(T, 5))
+    yaw = (30.0 * np.arange(T)) % 360.0
+    eye = np.eye(16, 4, dtype=np.float32)
+    return {
+        "obj_static": (dict(obj_az=np.zeros((T, 1))), 1, 0, 0),
+        "obj_moving": (dict(obj_az=az1), 1, 0, 0),
+        "obj_diffuse": (dict(obj_az=az1, obj_diffuse=1.0), 1, 0, 0),
+        "obj_views": (dict(obj_az=az5, obj_diffuse=[0, .5, 0, 1, .2], yaw_deg=yaw), 5, 0, 0),
+        "ds": (dict(ds_speakers=[2, 5, -1]), 0, 3, 0),
+        "hoa": (dict(hoa_gains=eye, H=4), 0, 0, 4),
+        "all_views": (dict(obj_az=az5, obj_diffuse=[0, .5, 0, 1, .2], ds_speakers=[2, 5, -1], hoa_gains=eye, H=4,
+                           yaw_deg=yaw), 5, 3, 4),
+    }[name]
+
+
+@pytest.mark.parametrize("mode", ["batch", "batch3", "stream"])
+@pytest.mark.parametrize("B", [128, 512, 2048])
+@pytest.mark.parametrize("name", ["obj_static", "obj_moving", "obj_diffuse", "obj_views", "ds", "hoa", "all_views"])
+def test_paths_match_oracle(oracle, small_data, name, B, mode):
+    T = max(6, 3072 // B)
+    ctl = control.HostControl(small_data)
+    kw, N, M, H = case_tables(ctl, name, T, np.random.default_rng(B))
+    tb = ctl.tables(T, **kw)
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((N, 0), (M, 100), (H, 200)))
+    ref = ref_render(oracle, small_data, N, M, H, B, tb, obj, ds, hoa)
+    out = gpu_render(small_data, N, M, H, B, tb, obj, ds, hoa, mode)
+    assert np.abs(ref).max() > 0.05
+    check(out, ref, "%s B=%d %s" % (name, B, mode))
+
+
+@pytest.mark.parametrize("offsets", [(0, 0, 0), (1, 0, 1), (0, 1, 0)])
+def test_ramp_convention_switches_follow_oracle(oracle, small_data, offsets):
+    B, T = 256, 8
+    ctl = control.HostControl(small_data)
+    kw, N, M, H = case_tables(ctl, "all_views", T, np.random.default_rng(1))
+    tb = ctl.tables(T, **kw)
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((N, 0), (M, 100), (H, 200)))
+    ref = ref_render(oracle, small_data, N, M, H, B, tb, obj, ds, hoa, ramp_offsets=offsets)
+    out = gpu_render(small_data, N, M, H, B, tb, obj, ds, hoa, "batch", ramp_offsets=offsets)
+    check(out, ref, str(offsets))
+    other = ref_render(oracle, small_data, N, M, H, B, tb, obj, ds, hoa, ramp_offsets=tuple(1 - o for o in offsets))
+    assert np.abs(out - other).max() > 1e-4   # the switch is not a no-op
+
+
+@pytest.mark.parametrize("splits", [(1, 1), (2, 3), (4, 16)])
+def test_partial_sum_splits(oracle, small_data, splits):
+    """object_splits / cmac_splits only change how partial sums are grouped."""
+    B, T, N = 256, 6, 70
+    ctl = control.HostControl(small_data)
+    rng = np.random.default_rng(2)
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, N)), obj_diffuse=np.where(np.arange(N) % 3 == 0, .4, 0.),
+                    obj_gain=0.3, ds_speakers=[2, 5], yaw_deg=30.0 * np.arange(T))
+    obj, ds = control.synth_audio(N, T * B, 0), control.synth_audio(2, T * B, 500)
+    ref = ref_render(oracle, small_data, N, 2, 0, B, tb, obj, ds, None)
+    out = gpu_render(small_data, N, 2, 0, B, tb, obj, ds, None, "batch", object_splits=splits[0], cmac_splits=splits[1])
+    check(out, ref, str(splits))
+
+
+def test_unity_fixture_path_delays_through_file_loader(oracle, unity_data):
+    """visr_bear/test/test_delays.py:114-136 on the CUDA path, data file read by the C++ loader."""
+    B, T = 512, 10
+    path = str(GOLDEN / "unity_brirs_decorrelators.tf")
+    ctl = control.HostControl(unity_data)
+    x = np.random.default_rng(0).standard_normal((1, T * B)).astype(np.float32)
+    none = np.zeros((0, T * B), np.float32)
+    fl = unity_data.front_loudspeaker
+    tb_ds, tb_obj = ctl.tables(T, ds_speakers=[fl]), ctl.tables(T, obj_az=np.zeros((T, 1)))
+    tb_dif = ctl.tables(T, obj_az=np.zeros((T, 1)), obj_diffuse=1.0)
+    y_ds = gpu_render(path, 0, 1, 0, B, tb_ds, none, x, none, "stream")
+    y_obj = gpu_render(path, 1, 0, 0, B, tb_obj, x, none, none, "stream")
+    y_dif = gpu_render(path, 1, 0, 0, B, tb_dif, x, none, none, "batch")
+    np.testing.assert_allclose(y_ds[:, 2 * B:], y_obj[:, 2 * B:], atol=2e-4)
+    np.testing.assert_allclose(y_ds[:, 2 * B:], y_dif[:, 2 * B:], atol=2e-4)
+    np.testing.assert_allclose(y_ds, ref_render(oracle, unity_data, 0, 1, 0, B, tb_ds, None, x, None), atol=2e-5)
+
+
+def test_single_block_unchanged_ports(oracle, small_data):
+    """Ports the reference only writes on change (static_delays, brir_index, hoa_gains): NULL / -1 in
+    the single-block call means 'unchanged' (static_delay_calc.cpp:19-30, select_brir.cpp:34-53)."""
+    from bear_b200.renderer import Renderer
+    B, T = 256, 6
+    ctl = control.HostControl(small_data)
+    tb = ctl.tables(T, obj_az=np.full((T, 1), 20.0), hoa_gains=np.eye(16, 4, dtype=np.float32), H=4,
+                    yaw_deg=np.array([0, 0, 60, 60, 60, 60.0]))
+    obj, hoa = control.synth_audio(1, T * B, 0), control.synth_audio(4, T * B, 9)
+    ref = ref_render(oracle, small_data, 1, 0, 4, B, tb, obj, None, hoa)
+    out = np.zeros((2, T * B), np.float32)
+    with Renderer(small_data, 1, 0, 4, B) as r:
+        for k in range(T):
+            t = tb.block(k)
+            if k not in (0, 2):   # listener "changes" only in blocks 0 and 2
+                t["static_delays"], t["brir_index"], t["hoa_gains"] = None, None, None
+            s = slice(k * B, (k + 1) * B)
+            out[:, s] = r.process(obj[:, s], None, hoa[:, s], t)
+    check(out, ref)
+
+
+def test_argument_errors(small_data):
+    from bear_b200.renderer import Renderer
+    B = 256
+    ctl = control.HostControl(small_data)
+    tb = ctl.tables(2, obj_az=np.zeros((2, 1)))
+    obj = control.synth_audio(1, 2 * B, 0)
+    with Renderer(small_data, 1, 0, 0, B, max_batch_blocks=1) as r:
+        with pytest.raises(ValueError, match="max_batch_blocks"):
+            r.process_batch(obj, None, None, tb)
+        bad = tb.slice(0, 1)
+        bad["brir_index"] = np.array([small_data.num_views], np.int32)
+        with pytest.raises(ValueError, match="brir_index out of range"):
+            r.process_batch(obj[:, :B], None, None, bad)
+        with pytest.raises(ValueError, match="shape"):
+            r.process(obj[:, :B - 1], None, None, tb.block(0))
+        # still usable after errors
+        r.process(obj[:, :B], None, None, tb.block(0))
+
+
+def test_zero_channel_configs(small_data):
+    from bear_b200.renderer import Renderer
+    B = 128
+    ctl = control.HostControl(small_data)
+    tb = ctl.tables(3)
+    with Renderer(small_data, 0, 0, 0, B, max_batch_blocks=3) as r:   # nothing connected: silence
+        assert not r.process_batch(None, None, None, tb).any()
+        assert not r.process(None, None, None, tb.block(0)).any()     # NULL arrays allowed (test_renderer.cpp:27,57)
+
+
+def test_device_resident_path_matches_host_path(small_data):
+    """bear_cuda_process_device on the staging areas == bear_cuda_process_batch from host buffers."""
+    import torch
+    from bear_b200.renderer import Renderer
+    from bear_b200 import device_io
+    B, T = 512, 5
+    ctl = control.HostControl(small_data)
+    N, M, H, tb = control.scenario(ctl, "cfg5_ht", T, B, seed=3)
+    tb["brir_index"] = (tb["brir_index"] % small_data.num_views).astype(np.int32)
+    audio = [control.synth_audio(c, 2 * T * B, s) for c, s in ((N, 0), (M, 100), (H, 200))]
+    with Renderer(small_data, N, M, H, B, max_batch_blocks=T) as a, Renderer(small_data, N, M, H, B, max_batch_blocks=T) as b:
+        io = device_io.DeviceBuffers(b)
+        for call in range(2):
+            s = slice(call * T * B, (call + 1) * T * B)
+            want = a.process_batch(*[x[:, s] for x in audio], tb)
+            io.load_audio(np.concatenate([x[:, s] for x in audio]))
+            io.load_tables(tb)
+            b.process_device(T)
+            b.synchronize()
+            got = io.read_output(T)
+            np.testing.assert_array_equal(got, want)
+
+
+@pytest.fixture(scope="module")
+def default_shape_data():
+    return data_file.from_tree(data_file.synthetic_tree(seed=0, num_views=24))
+
+
+@pytest.mark.parametrize("name,B,T", [("cfg1", 512, 24), ("cfg2_ht", 512, 24), ("cfg3_ht", 512, 16), ("cfg5_ht", 1024, 8),
+                                      ("cfg4_ht", 256, 16)])
+def test_baseline_configs_default_shape(oracle, default_shape_data, name, B, T):
+    """BASELINE.json configs on a data file of the production shape (BRIR 2976 taps, P = 6/12/3)."""
+    data = default_shape_data
+    ctl = control.HostControl(data)
+    N, M, H, tb = control.scenario(ctl, name, T, B, seed=1)
+    tb["brir_index"] = (tb["brir_index"] % data.num_views).astype(np.int32)
+    tb["static_delays"] = ctl.static_delays(tb["brir_index"]).astype(np.float32)
+    # level the scene so that the rendered mix stays within full scale (the 1e-5 bar is absolute)
+    scale = 0.1 / max(1.0, np.sqrt((N + M + H) / 4.0))
+    obj, ds, hoa = (control.synth_audio(c, T * B, s, scale) for c, s in ((N, 0), (M, 5000), (H, 6000)))
+    ref = ref_render(oracle, data, N, M, H, B, tb, obj, ds, hoa)
+    out = gpu_render(data, N, M, H, B, tb, obj, ds, hoa, "batch8")
+    assert 0.05 < np.abs(ref).max() < 1.5
+    check(out, ref, name)
+
+
+def test_linearity_at_full_size(default_shape_data):
+    """Size-independent property (test_changes.py:341-361): a 1024-object render equals the sum of the
+    renders of its 8 object groups -- the property object-group sharding relies on."""
+    data = default_shape_data
+    B, T, N, G = 256, 24, 1024, 8
+    ctl = control.HostControl(data)
+    _, _, _, tb = control.scenario(ctl, "cfg4_ht", T, B, seed=4)
+    tb["brir_index"] = (tb["brir_index"] % data.num_views).astype(np.int32)
+    tb["static_delays"] = ctl.static_delays(tb["brir_index"]).astype(np.float32)
+    obj = control.synth_audio(N, T * B, 0, 0.1 / np.sqrt(N / 4.0))
+    whole = gpu_render(data, N, 0, 0, B, tb, obj, None, None, "batch")
+    acc = np.zeros_like(whole, dtype=np.float64)
+    per = N // G
+    for g in range(G):
+        s = slice(g * per, (g + 1) * per)
+        part = control.BlockTables({**tb, "direct_gains": tb["direct_gains"][:, :, s],
+                                    "diffuse_gains": tb["diffuse_gains"][:, :, s],
+                                    "direct_delays": tb["direct_delays"][:, 2 * s.start:2 * s.stop]})
+        acc += gpu_render(data, per, 0, 0, B, part, obj[s], None, None, "batch")
+    assert np.abs(whole).max() > 0.05
+    np.testing.assert_allclose(whole, acc, atol=1e-5)
