@@ -629,6 +629,32 @@ void launch_carry(const CarryPlan &plan, cudaStream_t st)
   carry_kernel<<<plan.row_start[plan.n], 256, 0, st>>>(plan);
 }
 
+// ----------------------------------------------------------------------------------------------
+// Library-owned scratch for the partial spectra (see bear_cuda_process_device_static_scratch).
+// One array per GPU that loads this library, held until the process exits.  Host code must not use
+// the symbol itself as a pointer: on the host `g_static_ypart` only stands in for the device array,
+// so the device address is looked up once per device and handed to the kernels as a plain pointer.
+// ----------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_static_ypart[kStaticScratchBytes];
+
+cudaError_t static_scratch_pointer(float2 **out)
+{
+  constexpr int kMaxDevices = 64;
+  static float2 *resolved[kMaxDevices] = {nullptr};
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= kMaxDevices) return cudaErrorInvalidDevice;
+  if (!resolved[dev]) {
+    void *ptr = nullptr;
+    e = cudaGetSymbolAddress(&ptr, g_static_ypart);  // address on the CURRENT device
+    if (e != cudaSuccess) return e;
+    resolved[dev] = static_cast<float2 *>(ptr);
+  }
+  *out = resolved[dev];
+  return cudaSuccess;
+}
+
 cudaError_t configure_kernels(int B)
 {
   const int smem = 2 * B * (int)sizeof(float2);

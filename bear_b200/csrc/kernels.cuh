@@ -79,4 +79,9 @@ void launch_ifft_out(const Layout &p, int T, cudaStream_t st);
 void launch_carry(const CarryPlan &plan, cudaStream_t st);
 cudaError_t configure_kernels(int B);
 
+// Fixed-size device scratch that lives in the library image (no allocation), and its device
+// address for the current device (resolved on first use per device).
+constexpr size_t kStaticScratchBytes = 4u << 20;
+cudaError_t static_scratch_pointer(float2 **out);
+
 }  // namespace bearcuda

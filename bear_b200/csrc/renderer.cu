@@ -611,6 +611,39 @@ int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T)
   });
 }
 
+int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    Layout &p = r->lay;
+    if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
+    const size_t need = (size_t)T * 2 * 2 * p.KS * p.B * sizeof(float2);
+    if (need > kStaticScratchBytes)
+      throw Unsupported{"static scratch too small: " + std::to_string(T) + " periods need " + std::to_string(need) +
+                        " bytes of partial spectra (2 ears x 2 views x " + std::to_string(p.KS) + " splits x " +
+                        std::to_string(p.B) + " bins), the built-in array holds " +
+                        std::to_string(kStaticScratchBytes) + "; use fewer periods per call or bear_cuda_process_device"};
+    float2 *scratch = nullptr;
+    CK(static_scratch_pointer(&scratch));  // first call on a device resolves the symbol address
+    // Same kernels, same state; only the partial spectra go to the built-in array.  Nothing in it has
+    // to start at zero: cmac_kernel writes every partial spectrum that ifft_out_kernel reads in the
+    // same call, so whatever an earlier call (of any renderer) left behind is never read.
+    float2 *own = p.ypart;
+    const bool prof = r->profiling;
+    p.ypart = scratch;
+    r->profiling = false;  // the event pool may grow; this entry point must not create anything
+    try {
+      run_pipeline(r, (int)T);
+    } catch (...) {
+      p.ypart = own;
+      r->profiling = prof;
+      throw;
+    }
+    p.ypart = own;
+    r->profiling = prof;
+  });
+}
+
 int bear_cuda_synchronize(bear_cuda_renderer *r)
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;

@@ -89,7 +89,9 @@ EXPORTS = (
     "bear_cuda_process_device", "bear_cuda_synchronize", "bear_cuda_get_info",
     "bear_cuda_host_alloc", "bear_cuda_host_free", "bear_cuda_read_data_file_info",
     "bear_cuda_tenf_read_f32", "bear_cuda_set_profiling", "bear_cuda_get_profile",
+    "bear_cuda_process_device_static_scratch",
 )
+STATIC_SCRATCH_BYTES = 4 << 20
 NUM_KERNELS = 7
 
 
@@ -125,6 +127,7 @@ def lib():
         l.bear_cuda_process_batch.argtypes = [vp, u32, vp, sz, vp, sz, vp, sz, C.POINTER(Tables), vp, sz]
         l.bear_cuda_get_device_io.argtypes = [vp, C.POINTER(DeviceIO)]
         l.bear_cuda_process_device.argtypes = [vp, u32]
+        l.bear_cuda_process_device_static_scratch.argtypes = [vp, u32]
         l.bear_cuda_synchronize.argtypes = [vp]
         l.bear_cuda_get_info.argtypes = [vp, C.POINTER(Info)]
         l.bear_cuda_host_alloc.argtypes = [sz]
@@ -354,6 +357,11 @@ class Renderer:
         arr = (KernelProfile * NUM_KERNELS)()
         self._check(self._l.bear_cuda_get_profile(self._h, arr, int(reset)))
         return {e.name.decode(): (e.total_ms, e.launches) for e in arr}
+
+    def process_device_static_scratch(self, T):
+        """bear_cuda_process_device without any allocation: partial spectra go to the library's
+        built-in device array (see include/bear_cuda.h for the limit and the sharing rules)."""
+        self._check(self._l.bear_cuda_process_device_static_scratch(self._h, T))
 
     def synchronize(self):
         self._check(self._l.bear_cuda_synchronize(self._h))

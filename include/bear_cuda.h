@@ -146,6 +146,29 @@ int bear_cuda_get_device_io(bear_cuda_renderer *r, bear_cuda_device_io *io);
 /* Render T periods from the staging areas; asynchronous on io.stream. */
 int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T);
 
+/* No counterpart in the reference (its DSP graph owns ordinary heap buffers).
+ *
+ * Same work, inputs, outputs and carried state as bear_cuda_process_device, for hosts that drive
+ * the renderer from a place where nothing may be allocated: the audio callback of a plug-in host or
+ * sound-card driver thread, where a device allocation can take driver-wide locks and stall the
+ * period deadline, or an embedder whose device memory is handed out once at start-up.  This call
+ * performs no cudaMalloc/cudaFree and uses no allocating library routine; the one piece of
+ * per-call scratch the pipeline needs (the partial output spectra between the multiply-accumulate
+ * and the inverse transform) is taken from an array of BEAR_CUDA_STATIC_SCRATCH_BYTES that is part
+ * of the library image on every GPU that loads it, instead of from renderer-owned memory.
+ *
+ *  - Limit: T * 2 ears * 2 views * cmac_splits * period_size * 8 bytes must fit the array
+ *    (bear_cuda_get_info reports cmac_splits); otherwise BEAR_CUDA_ERR_UNSUPPORTED with the numbers
+ *    in bear_cuda_last_error and nothing is launched.
+ *  - The first call on each device looks up the array's device address (a one-off set-up step with
+ *    that device current); make that first call before starting any stream capture.
+ *  - The array is shared by every renderer and every call on the device and keeps whatever the last
+ *    call wrote.  Nothing needs clearing (all that is read was written in the same call), but two
+ *    calls whose kernels overlap on the GPU - different renderers on different streams - would
+ *    overwrite each other's partial spectra: serialise them. */
+#define BEAR_CUDA_STATIC_SCRATCH_BYTES (4u << 20)
+int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T);
+
 /* Block until all work queued on the renderer's stream has finished. */
 int bear_cuda_synchronize(bear_cuda_renderer *r);
 
