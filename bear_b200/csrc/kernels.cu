@@ -40,53 +40,98 @@ __device__ __forceinline__ float2 ldtw(const float2 *__restrict__ tw, int q, int
 }
 
 // ----------------------------------------------------------------------------------------------
-// Complex FFT of length M = 2^logM in shared memory: Stockham autosort, radix 4 with a final
-// radix-2 pass when logM is odd.  Natural order in and out, unnormalised.  `a` holds the input,
-// `b` is scratch of the same size; returns the buffer that holds the result.  All threads of
-// the CTA must call it.
+// Complex FFT of length M = 2^logM in shared memory: Stockham autosort with radix-8 passes held in
+// registers (then one radix-4 or radix-2 pass if log2 M is not a multiple of 3).  Natural order in
+// and out, unnormalised.  Both buffers hold M + M/8 float2: element i lives at padi(i) so that the
+// stride-8 scatter of a radix-8 pass is bank-conflict free.  `a` holds the input, `b` is scratch;
+// returns the buffer that holds the result.  All threads of the CTA must call it.
 // ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ int padi(int i) { return i + (i >> 3); }
+__host__ __device__ constexpr int fft_smem_floats2(int M) { return 2 * (M + (M >> 3)); }
+
+template <bool INV>
+__device__ __forceinline__ void dft4(float2 a0, float2 a1, float2 a2, float2 a3, float2 &x0, float2 &x1, float2 &x2,
+                                     float2 &x3)
+{
+  const float2 s02 = cadd(a0, a2), d02 = csub(a0, a2), s13 = cadd(a1, a3), t = csub(a1, a3);
+  const float2 r = INV ? make_float2(-t.y, t.x) : make_float2(t.y, -t.x);   // -+i (a1 - a3)
+  x0 = cadd(s02, s13); x2 = csub(s02, s13);
+  x1 = cadd(d02, r);   x3 = csub(d02, r);
+}
+// v[r] <- sum_n v[n] exp(-+2 pi i n r / 8)
+template <bool INV>
+__device__ __forceinline__ void dft8(float2 (&v)[8])
+{
+  const float s = 0.70710678118654752440f;
+  const float2 a0 = cadd(v[0], v[4]), a1 = cadd(v[1], v[5]), a2 = cadd(v[2], v[6]), a3 = cadd(v[3], v[7]);
+  const float2 b0 = csub(v[0], v[4]);
+  float2 t = csub(v[1], v[5]);
+  const float2 b1 = INV ? make_float2((t.x - t.y) * s, (t.x + t.y) * s) : make_float2((t.x + t.y) * s, (t.y - t.x) * s);
+  t = csub(v[2], v[6]);
+  const float2 b2 = INV ? make_float2(-t.y, t.x) : make_float2(t.y, -t.x);
+  t = csub(v[3], v[7]);
+  const float2 b3 = INV ? make_float2((-t.x - t.y) * s, (t.x - t.y) * s) : make_float2((t.y - t.x) * s, (-t.x - t.y) * s);
+  dft4<INV>(a0, a1, a2, a3, v[0], v[2], v[4], v[6]);
+  dft4<INV>(b0, b1, b2, b3, v[1], v[3], v[5], v[7]);
+}
+
+template <bool INV>
+__device__ __forceinline__ float2 twid(float2 v, float2 w) { return INV ? cmul_conj(v, w) : cmul(v, w); }
+
 template <bool INV>
 __device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int logM, const float2 *__restrict__ tw)
 {
   const int tid = threadIdx.x, nthr = blockDim.x;
   int ls = 0;
-  for (; ls + 2 <= logM; ls += 2) {
+  for (; ls + 3 <= logM; ls += 3) {
+    const int Ns = 1 << ls, Q = M >> 3;
+    __syncthreads();
+    for (int j = tid; j < Q; j += nthr) {
+      const int k = j & (Ns - 1);
+      float2 v[8];
+#pragma unroll
+      for (int r = 0; r < 8; r++) v[r] = a[padi(j + r * Q)];
+      if (ls > 0) {
+        const int q = k << (logM - 2 - ls);   // exp(-2 pi i k / (8 Ns)) = tw[k M / (4 Ns)]
+        const float2 w1 = __ldg(tw + q), w2 = __ldg(tw + 2 * q), w4 = __ldg(tw + 4 * q);
+        const float2 w3 = cmul(w1, w2), w5 = cmul(w1, w4), w6 = cmul(w2, w4), w7 = cmul(w3, w4);
+        v[1] = twid<INV>(v[1], w1); v[2] = twid<INV>(v[2], w2); v[3] = twid<INV>(v[3], w3);
+        v[4] = twid<INV>(v[4], w4); v[5] = twid<INV>(v[5], w5); v[6] = twid<INV>(v[6], w6);
+        v[7] = twid<INV>(v[7], w7);
+      }
+      dft8<INV>(v);
+      const int j0 = ((j - k) << 3) + k;
+#pragma unroll
+      for (int r = 0; r < 8; r++) b[padi(j0 + r * Ns)] = v[r];
+    }
+    float2 *t = a; a = b; b = t;
+  }
+  if (logM - ls == 2) {
     const int Ns = 1 << ls, Q = M >> 2;
     __syncthreads();
     for (int j = tid; j < Q; j += nthr) {
       const int k = j & (Ns - 1);
-      float2 v0 = a[j], v1 = a[j + Q], v2 = a[j + 2 * Q], v3 = a[j + 3 * Q];
+      float2 v0 = a[padi(j)], v1 = a[padi(j + Q)], v2 = a[padi(j + 2 * Q)], v3 = a[padi(j + 3 * Q)];
       if (ls > 0) {
         const int q = k << (logM - 1 - ls);
-        float2 w1 = ldtw(tw, q, M), w2 = ldtw(tw, 2 * q, M), w3 = ldtw(tw, 3 * q, M);
-        if (INV) {
-          v1 = cmul_conj(v1, w1); v2 = cmul_conj(v2, w2); v3 = cmul_conj(v3, w3);
-        } else {
-          v1 = cmul(v1, w1); v2 = cmul(v2, w2); v3 = cmul(v3, w3);
-        }
+        v1 = twid<INV>(v1, ldtw(tw, q, M)); v2 = twid<INV>(v2, ldtw(tw, 2 * q, M)); v3 = twid<INV>(v3, ldtw(tw, 3 * q, M));
       }
-      float2 s02 = cadd(v0, v2), d02 = csub(v0, v2), s13 = cadd(v1, v3), d13 = csub(v1, v3);
-      // forward: -i*d13, inverse: +i*d13
-      float2 r = INV ? make_float2(-d13.y, d13.x) : make_float2(d13.y, -d13.x);
+      float2 x0, x1, x2, x3;
+      dft4<INV>(v0, v1, v2, v3, x0, x1, x2, x3);
       const int j0 = ((j - k) << 2) + k;
-      b[j0] = cadd(s02, s13);
-      b[j0 + Ns] = cadd(d02, r);
-      b[j0 + 2 * Ns] = csub(s02, s13);
-      b[j0 + 3 * Ns] = csub(d02, r);
+      b[padi(j0)] = x0; b[padi(j0 + Ns)] = x1; b[padi(j0 + 2 * Ns)] = x2; b[padi(j0 + 3 * Ns)] = x3;
     }
     float2 *t = a; a = b; b = t;
-  }
-  if (ls < logM) {
-    const int Ns = 1 << ls, Hh = M >> 1;  // Ns == M/2
+  } else if (logM - ls == 1) {
+    const int Ns = 1 << ls, Hh = M >> 1;
     __syncthreads();
     for (int j = tid; j < Hh; j += nthr) {
       const int k = j & (Ns - 1);
-      float2 v0 = a[j], v1 = a[j + Hh];
-      float2 w = ldtw(tw, k << (logM - ls), M);
-      v1 = INV ? cmul_conj(v1, w) : cmul(v1, w);
+      const float2 v0 = a[padi(j)];
+      const float2 v1 = twid<INV>(a[padi(j + Hh)], ldtw(tw, k << (logM - ls), M));
       const int j0 = ((j - k) << 1) + k;
-      b[j0] = cadd(v0, v1);
-      b[j0 + Ns] = csub(v0, v1);
+      b[padi(j0)] = cadd(v0, v1);
+      b[padi(j0 + Ns)] = csub(v0, v1);
     }
     float2 *t = a; a = b; b = t;
   }
@@ -151,14 +196,14 @@ __global__ void filter_fft_kernel(const float *__restrict__ taps, int taps_len, 
                                   const float2 *__restrict__ tw, float2 *__restrict__ out, float scale)
 {
   extern __shared__ float2 sm[];
-  float2 *a = sm, *b = sm + B;
+  float2 *a = sm, *b = sm + B + (B >> 3);
   const int f = blockIdx.x / P, p = blockIdx.x % P;
   const float *src = taps + (size_t)f * taps_len;
   for (int n = threadIdx.x; n < B; n += blockDim.x) {
     int t0 = p * B + 2 * n;
     float v0 = (2 * n < B && t0 < taps_len) ? src[t0] : 0.0f;
     float v1 = (2 * n + 1 < B && t0 + 1 < taps_len) ? src[t0 + 1] : 0.0f;
-    a[n] = make_float2(v0 * scale, v1 * scale);
+    a[padi(n)] = make_float2(v0 * scale, v1 * scale);
   }
   float2 *z = fft_shared<false>(a, b, B, logB, tw);
   float2 *dst = out + (size_t)blockIdx.x * B;
@@ -167,7 +212,7 @@ __global__ void filter_fft_kernel(const float *__restrict__ taps, int taps_len, 
       dst[0] = make_float2(z[0].x + z[0].y, z[0].x - z[0].y);
     } else {
       float2 xk, xm;
-      rfft_post(z[k], z[B - k], __ldg(tw + k), xk, xm);
+      rfft_post(z[padi(k)], z[padi(B - k)], __ldg(tw + k), xk, xm);
       dst[k] = xk;
       dst[B - k] = xm;
     }
@@ -177,8 +222,8 @@ __global__ void filter_fft_kernel(const float *__restrict__ taps, int taps_len, 
 void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, int logB, int P, const float2 *tw,
                        float2 *out, float scale, cudaStream_t st)
 {
-  int threads = B / 4 < 32 ? 32 : B / 4;
-  filter_fft_kernel<<<n_filters * P, threads, 2 * B * sizeof(float2), st>>>(taps, taps_len, B, logB, P, tw, out, scale);
+  int threads = B / 8 < 32 ? 32 : B / 8;
+  filter_fft_kernel<<<n_filters * P, threads, fft_smem_floats2(B) * sizeof(float2), st>>>(taps, taps_len, B, logB, P, tw, out, scale);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -194,8 +239,8 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
   __shared__ __align__(16) float sg[kMixChunk][4 * kMaxSpeakers + 4];
   __shared__ float sd[kMixChunk][4];
   const int tid = threadIdx.x;
-  const int t = blockIdx.x * kMixTile + tid;
-  const int k = (blockIdx.x * kMixTile) / p.B;
+  const int t = p.k0 * p.B + blockIdx.x * kMixTile + tid;
+  const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
   const int n = t - k * p.B;
   const int s = blockIdx.y;
   const int C = p.N + p.M;
@@ -293,8 +338,8 @@ void launch_mix(const Layout &p, int T, cudaStream_t st)
 // ----------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kMixTile) hoa_mix_kernel(Layout p, int T)
 {
-  const int t = blockIdx.x * kMixTile + threadIdx.x;
-  const int k = (blockIdx.x * kMixTile) / p.B;
+  const int t = p.k0 * p.B + blockIdx.x * kMixTile + threadIdx.x;
+  const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
   const int n = t - k * p.B;
   const float rg = (float)(n + p.goff) / (float)p.B;
   const float *x0 = p.xin + (size_t)(p.N + p.M) * p.xs + p.hist + t;
@@ -333,8 +378,8 @@ __global__ void decorrelate_kernel(Layout p, int T)
 {
   extern __shared__ float2 sm[];
   const int M = p.B;
-  float2 *a = sm, *b = sm + M;
-  const int l = blockIdx.x % p.L, k = blockIdx.x / p.L;
+  float2 *a = sm, *b = sm + M + (M >> 3);
+  const int l = blockIdx.x % p.L, k = p.k0 + blockIdx.x / p.L;
   const int tid = threadIdx.x, nthr = blockDim.x;
   for (int n = tid; n < M; n += nthr) {
     float2 z = make_float2(0.f, 0.f);
@@ -342,7 +387,7 @@ __global__ void decorrelate_kernel(Layout p, int T)
       const float2 v = reinterpret_cast<const float2 *>(p.qdif + ((size_t)s * p.L + l) * p.cs + (size_t)k * p.B)[n];
       z.x += v.x; z.y += v.y;
     }
-    a[n] = z;
+    a[padi(n)] = z;
   }
   float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw);
   float2 *o = (z == a) ? b : a;
@@ -355,23 +400,23 @@ __global__ void decorrelate_kernel(Layout p, int T)
     } else {
       const float2 w = __ldg(p.tw + kk);
       float2 xk, xm, zk, zm;
-      rfft_post(z[kk], z[M - kk], w, xk, xm);
+      rfft_post(z[padi(kk)], z[padi(M - kk)], w, xk, xm);
       xk = cmul(xk, __ldg(h + kk));
       xm = cmul(xm, __ldg(h + M - kk));
       irfft_pre(xk, xm, w, zk, zm);
-      o[kk] = zk;
-      o[M - kk] = zm;
+      o[padi(kk)] = zk;
+      o[padi(M - kk)] = zm;
     }
   }
   float2 *y = fft_shared<true>(o, z, M, p.logB, p.tw);
   float2 *dst = reinterpret_cast<float2 *>(p.w + (size_t)l * p.ws + p.B + p.hist + (size_t)k * p.B);
-  for (int n = tid; n < M / 2; n += nthr) dst[n] = y[M / 2 + n];
+  for (int n = tid; n < M / 2; n += nthr) dst[n] = y[padi(M / 2 + n)];
 }
 
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
 {
-  int threads = p.B / 4 < 32 ? 32 : p.B / 4;
-  decorrelate_kernel<<<T * p.L, threads, 2 * p.B * sizeof(float2), st>>>(p, T);
+  int threads = p.B / 8 < 32 ? 32 : p.B / 8;
+  decorrelate_kernel<<<T * p.L, threads, fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -389,8 +434,8 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nch)
 {
   extern __shared__ float2 sm[];
   const int M = p.B;
-  float2 *a = sm, *b = sm + M;
-  const int ch = blockIdx.x % nch, k = blockIdx.x / nch;
+  float2 *a = sm, *b = sm + M + (M >> 3);
+  const int ch = blockIdx.x % nch, k = p.k0 + blockIdx.x / nch;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const float invB = 1.0f / (float)p.B;
   const int L2 = 2 * p.L;
@@ -417,13 +462,13 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nch)
         v.x += delayed_read(wrow + t, ramped_delay(d0[h], dd[h], (float)(nn + p.doff) * invB));
         v.y += delayed_read(wrow + t + 1, ramped_delay(d0[h], dd[h], (float)(nn + 1 + p.doff) * invB));
       }
-      a[n] = v;
+      a[padi(n)] = v;
     }
   } else {
     const int am = ch - L2;
     const float *arow = p.amb + (size_t)am * p.ws + p.B + p.hist + (size_t)(k - 1) * p.B;
     for (int n = tid; n < M; n += nthr)
-      a[n] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
+      a[padi(n)] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
   }
   float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw);
   const int slot = (p.fdl_head + k) % p.R;
@@ -433,7 +478,7 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nch)
       dst[0] = make_float2(z[0].x + z[0].y, z[0].x - z[0].y);
     } else {
       float2 xk, xm;
-      rfft_post(z[kk], z[M - kk], __ldg(p.tw + kk), xk, xm);
+      rfft_post(z[padi(kk)], z[padi(M - kk)], __ldg(p.tw + kk), xk, xm);
       dst[kk] = xk;
       dst[M - kk] = xm;
     }
@@ -442,32 +487,34 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nch)
 
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
 {
-  int threads = p.B / 4 < 32 ? 32 : p.B / 4;
+  int threads = p.B / 8 < 32 ? 32 : p.B / 8;
   int nch = 2 * p.L + (p.H > 0 ? p.A : 0);
-  bus_fdl_kernel<<<T * nch, threads, 2 * p.B * sizeof(float2), st>>>(p, T, nch);
+  bus_fdl_kernel<<<T * nch, threads, fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T, nch);
 }
 
 // ----------------------------------------------------------------------------------------------
 // cmac_kernel: the partitioned complex multiply-accumulate (the roofline kernel).
 //   Y_w[k][e][bin] = sum_{l<L, part<P} FDL[2l+e][k-part][bin] * H[view_w][2l+e][part][bin]
 //                  + sum_{a<A} FDL[2L+a][k][bin] * Hhoa[a][e][bin]            w in {new, old}
-// Terms are split KS ways over blockIdx.y (partial spectra are summed by ifft_out_kernel).
-// Each thread owns two adjacent bins (one 16-byte load per operand per term), consecutive
-// threads consecutive bin pairs: every warp request is 512 contiguous bytes.
-// grid: (B/(2*threads), KS, 2T); block: min(B/2, 128).
+// View-major: the CTA for period j loads the filter partitions of view(j) ONCE and uses them for
+// both spectra that need them -- the new-view spectrum of period j and, when period j+1 changes
+// view, the old-view spectrum of period j+1.  Walking the partitions in order, the FDL operand of
+// the second accumulation is the first one's operand of the previous step, so each term costs one
+// filter load and one FDL load.  (j = -1 is the view the previous call ended on.)
+// Work is split KS ways by loudspeaker (the HOA decode terms form one more unit); partial spectra
+// are summed by ifft_out_kernel.  Each thread owns two adjacent bins (one 16-byte load per operand
+// per term), consecutive threads consecutive bin pairs: every warp request is 512 contiguous bytes.
+// grid: (B/(2*threads), KS, 2(T+1)); block: min(B/2, 128).
 // ----------------------------------------------------------------------------------------------
-__device__ __forceinline__ void cmac2(float4 &acc, const float4 x, const float4 h)
+__device__ __forceinline__ void cmac2(float4 &acc, const float4 x, const float4 h, const bool packed0)
 {
-  acc.x = fmaf(x.x, h.x, acc.x); acc.x = fmaf(-x.y, h.y, acc.x);
-  acc.y = fmaf(x.x, h.y, acc.y); acc.y = fmaf(x.y, h.x, acc.y);
-  acc.z = fmaf(x.z, h.z, acc.z); acc.z = fmaf(-x.w, h.w, acc.z);
-  acc.w = fmaf(x.z, h.w, acc.w); acc.w = fmaf(x.w, h.z, acc.w);
-}
-// first pair of the packed spectrum: bin 0 holds (DC, Nyquist), both real
-__device__ __forceinline__ void cmac2_packed0(float4 &acc, const float4 x, const float4 h)
-{
+  // bin 0 of the packed spectrum holds (DC, Nyquist), both real: two real products instead of a complex one
   acc.x = fmaf(x.x, h.x, acc.x);
-  acc.y = fmaf(x.y, h.y, acc.y);
+  acc.y = fmaf(x.y, packed0 ? h.y : h.x, acc.y);
+  if (!packed0) {
+    acc.x = fmaf(-x.y, h.y, acc.x);
+    acc.y = fmaf(x.x, h.y, acc.y);
+  }
   acc.z = fmaf(x.z, h.z, acc.z); acc.z = fmaf(-x.w, h.w, acc.z);
   acc.w = fmaf(x.z, h.w, acc.w); acc.w = fmaf(x.w, h.z, acc.w);
 }
@@ -479,41 +526,44 @@ __device__ __forceinline__ float4 ldg_stream(const float4 *p)
   return v;
 }
 
-template <bool XFADE>
-__device__ __forceinline__ void cmac_body(const Layout &p, int k, int e, int ks, int pair, float4 &accn, float4 &acco)
+template <bool DO_A, bool DO_B>
+__device__ __forceinline__ void cmac_body(const Layout &p, int j, int e, int ks, int pair, int v, float4 &accA,
+                                          float4 &accB)
 {
-  const int B = p.B, P = p.P, L = p.L;
-  const int vnew = p.view[k + 1], vold = p.view[k];
-  const int nb = L * P;
-  const int nterms = nb + (p.H > 0 ? p.A : 0);
-  const int per = (nterms + p.KS - 1) / p.KS;
-  const int t0 = ks * per, t1 = min(nterms, t0 + per);
-  const bool first = pair == 0;
-  const size_t vstride = (size_t)2 * L * P * B;  // float2 per view
-  const int base_slot = p.fdl_head + k + p.R;    // + R keeps the modulo argument positive
-#pragma unroll 4
-  for (int t = t0; t < t1; t++) {
-    const float4 *xp, *hn, *ho;
-    if (t < nb) {
-      const int l = t / P, part = t - l * P;
-      const int ch = 2 * l + e;
-      const int slot = (base_slot - part) % p.R;
-      xp = reinterpret_cast<const float4 *>(p.fdl + ((size_t)ch * p.R + slot) * B) + pair;
-      const size_t ho_ = ((size_t)ch * P + part) * B;
-      hn = reinterpret_cast<const float4 *>(p.h_brir + vnew * vstride + ho_) + pair;
-      ho = reinterpret_cast<const float4 *>(p.h_brir + vold * vstride + ho_) + pair;
+  const int B = p.B, P = p.P, L = p.L, R = p.R;
+  const int nunits = L + (p.H > 0 ? 1 : 0);
+  const int per = (nunits + p.KS - 1) / p.KS;
+  const int u0 = ks * per, u1 = min(nunits, u0 + per);
+  const bool packed0 = pair == 0;
+  const int hB = B >> 1;                                   // float4 per spectrum
+  int slotA = p.fdl_head + j;                              // ring slot of period j (j >= -1)
+  slotA = slotA < 0 ? slotA + R : (slotA >= R ? slotA - R : slotA);
+  const int slotB = slotA + 1 == R ? 0 : slotA + 1;        // period j+1
+  const float4 *fdl4 = reinterpret_cast<const float4 *>(p.fdl) + pair;
+  for (int u = u0; u < u1; u++) {
+    if (u < L) {
+      const int ch = 2 * u + e;
+      const float4 *x = fdl4 + (size_t)ch * R * hB;
+      const float4 *h = reinterpret_cast<const float4 *>(p.h_brir) + ((size_t)(v * 2 * L + ch) * P) * hB + pair;
+      float4 xb = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (DO_B) xb = __ldg(x + (size_t)slotB * hB);
+      int slot = slotA;
+#pragma unroll 3
+      for (int part = 0; part < P; part++) {
+        const float4 xa = __ldg(x + (size_t)slot * hB);
+        const float4 hv = ldg_stream(h + (size_t)part * hB);
+        if (DO_A) cmac2(accA, xa, hv, packed0);
+        if (DO_B) cmac2(accB, xb, hv, packed0);
+        xb = xa;
+        slot = slot == 0 ? R - 1 : slot - 1;
+      }
     } else {
-      const int am = t - nb;
-      const int slot = base_slot % p.R;
-      xp = reinterpret_cast<const float4 *>(p.fdl + ((size_t)(2 * L + am) * p.R + slot) * B) + pair;
-      hn = ho = reinterpret_cast<const float4 *>(p.h_hoa + ((size_t)am * 2 + e) * B) + pair;
-    }
-    const float4 x = __ldg(xp);
-    const float4 h = ldg_stream(hn);
-    if (first) cmac2_packed0(accn, x, h); else cmac2(accn, x, h);
-    if (XFADE) {
-      const float4 h2 = __ldg(ho);
-      if (first) cmac2_packed0(acco, x, h2); else cmac2(acco, x, h2);
+      for (int am = 0; am < p.A; am++) {
+        const float4 *x = fdl4 + (size_t)(2 * L + am) * R * hB;
+        const float4 hv = __ldg(reinterpret_cast<const float4 *>(p.h_hoa) + ((size_t)am * 2 + e) * hB + pair);
+        if (DO_A) cmac2(accA, __ldg(x + (size_t)slotA * hB), hv, packed0);
+        if (DO_B) cmac2(accB, __ldg(x + (size_t)slotB * hB), hv, packed0);
+      }
     }
   }
 }
@@ -522,23 +572,25 @@ __global__ void __launch_bounds__(128) cmac_kernel(Layout p, int T)
 {
   const int pair = blockIdx.x * blockDim.x + threadIdx.x;  // bins 2*pair, 2*pair+1
   const int ks = blockIdx.y;
-  const int k = blockIdx.z >> 1, e = blockIdx.z & 1;
-  const bool xf = p.view[k + 1] != p.view[k];
-  float4 accn = make_float4(0.f, 0.f, 0.f, 0.f), acco = accn;
-  if (xf) cmac_body<true>(p, k, e, ks, pair, accn, acco);
-  else cmac_body<false>(p, k, e, ks, pair, accn, acco);
-  float4 *yn = reinterpret_cast<float4 *>(p.ypart + ((((size_t)k * 2 + e) * 2 + 0) * p.KS + ks) * p.B) + pair;
-  *yn = accn;
-  if (xf) {
-    float4 *yo = reinterpret_cast<float4 *>(p.ypart + ((((size_t)k * 2 + e) * 2 + 1) * p.KS + ks) * p.B) + pair;
-    *yo = acco;
-  }
+  const int j = p.k0 + (int)(blockIdx.z >> 1) - 1, e = blockIdx.z & 1;
+  const int v = p.view[j + 1];                              // view of period j (slot 0: previous call)
+  const bool doA = j >= p.k0;                               // earlier chunks already did their periods
+  const bool doB = j + 1 < p.k0 + T && p.view[j + 2] != v;   // period j+1 must be in this launch
+  if (!doA && !doB) return;
+  float4 accA = make_float4(0.f, 0.f, 0.f, 0.f), accB = accA;
+  if (doA && doB) cmac_body<true, true>(p, j, e, ks, pair, v, accA, accB);
+  else if (doA) cmac_body<true, false>(p, j, e, ks, pair, v, accA, accB);
+  else cmac_body<false, true>(p, j, e, ks, pair, v, accA, accB);
+  const size_t hB = p.B >> 1;
+  float4 *y = reinterpret_cast<float4 *>(p.ypart) + pair;
+  if (doA) y[((((size_t)j * 2 + e) * 2 + 0) * p.KS + ks) * hB] = accA;
+  if (doB) y[((((size_t)(j + 1) * 2 + e) * 2 + 1) * p.KS + ks) * hB] = accB;
 }
 
 void launch_cmac(const Layout &p, int T, cudaStream_t st)
 {
   int threads = p.B / 2 < 128 ? p.B / 2 : 128;
-  dim3 grid(p.B / 2 / threads, p.KS, 2 * T);
+  dim3 grid(p.B / 2 / threads, p.KS, 2 * (T + 1));
   cmac_kernel<<<grid, threads, 0, st>>>(p, T);
 }
 
@@ -552,8 +604,8 @@ __global__ void ifft_out_kernel(Layout p, int T)
 {
   extern __shared__ float2 sm[];
   const int M = p.B;
-  float2 *a = sm, *b = sm + M;
-  const int k = blockIdx.x >> 1, e = blockIdx.x & 1;
+  float2 *a = sm, *b = sm + M + (M >> 3);
+  const int k = p.k0 + (blockIdx.x >> 1), e = blockIdx.x & 1;
   const int tid = threadIdx.x, nthr = blockDim.x;
   const bool xf = p.view[k + 1] != p.view[k];
   const float invB = 1.0f / (float)p.B;
@@ -576,13 +628,13 @@ __global__ void ifft_out_kernel(Layout p, int T)
       } else {
         float2 zk, zm;
         irfft_pre(xk, xm, __ldg(p.tw + kk), zk, zm);
-        a[kk] = zk;
-        a[M - kk] = zm;
+        a[padi(kk)] = zk;
+        a[padi(M - kk)] = zm;
       }
     }
     float2 *z = fft_shared<true>(a, b, M, p.logB, p.tw);
     for (int n = tid; n < M / 2; n += nthr) {
-      float2 v = z[M / 2 + n];
+      float2 v = z[padi(M / 2 + n)];
       if (xf) {
         const float r0 = (float)(2 * n + p.xoff) * invB, r1 = (float)(2 * n + 1 + p.xoff) * invB;
         if (pass == 1) {
@@ -599,8 +651,8 @@ __global__ void ifft_out_kernel(Layout p, int T)
 
 void launch_ifft_out(const Layout &p, int T, cudaStream_t st)
 {
-  int threads = p.B / 4 < 32 ? 32 : p.B / 4;
-  ifft_out_kernel<<<2 * T, threads, 2 * p.B * sizeof(float2), st>>>(p, T);
+  int threads = p.B / 8 < 32 ? 32 : p.B / 8;
+  ifft_out_kernel<<<2 * T, threads, fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -657,7 +709,7 @@ cudaError_t static_scratch_pointer(float2 **out)
 
 cudaError_t configure_kernels(int B)
 {
-  const int smem = 2 * B * (int)sizeof(float2);
+  const int smem = fft_smem_floats2(B) * (int)sizeof(float2);
   if (smem > 48 * 1024) {
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(filter_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;

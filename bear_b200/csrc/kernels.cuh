@@ -52,6 +52,7 @@ struct Layout {
   // out
   float *out;  size_t os;    // [2][os]
   int fdl_head;              // ring slot of block 0 of this call
+  int k0;                    // first period of this launch (a call may be issued in chunks)
 };
 
 struct CarryRow {

@@ -42,6 +42,10 @@ struct bear_cuda_renderer {
   Layout lay{};
   int device = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t copy_stream = nullptr;      // host->device uploads of the host-buffer path
+  std::vector<cudaEvent_t> h2d_events;     // one per upload chunk
+  int chunk = 0;                           // periods per launch group (0 = whole call)
+  int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
   uint64_t device_bytes = 0;
   uint64_t launches = 0;
@@ -85,6 +89,8 @@ struct bear_cuda_renderer {
     for (cudaEvent_t e : ev_free) cudaEventDestroy(e);
     if (h_in) cudaFreeHost(h_in);
     if (h_out) cudaFreeHost(h_out);
+    for (cudaEvent_t e : h2d_events) cudaEventDestroy(e);
+    if (copy_stream) cudaStreamDestroy(copy_stream);
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -135,6 +141,7 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   r->device = cfg.device;
   CK(cudaSetDevice(r->device));
   CK(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
   CK(configure_kernels((int)B));
 
   Layout &p = r->lay;
@@ -161,14 +168,20 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
     p.S = std::max(1, std::min(std::min(S, maxS), 16));
   }
   {
-    const int nterms = p.L * p.P + (p.H > 0 ? p.A : 0);
+    // cMAC work units: one per loudspeaker (P partition terms each) + one for the HOA decode terms
+    const int nunits = p.L + (p.H > 0 ? 1 : 0);
     const int threads = std::min(p.B / 2, 128);
-    const int base = (p.B / 2 / threads) * 2 * p.Tmax;
+    const int base = (p.B / 2 / threads) * 2 * (p.Tmax + 1);
     int KS = cfg.cmac_splits;
     if (KS == 0) KS = (4 * 148 + base - 1) / base;
-    p.KS = std::max(1, std::min(std::min(KS, std::max(1, nterms / 8)), 32));
+    p.KS = std::max(1, std::min(KS, nunits));
   }
   p.R = p.Tmax + p.P - 1;
+  r->chunk = (int)cfg.chunk_blocks;
+  // host-buffer path: upload in ~12 chunks (at least 16 periods each) so copies overlap the kernels
+  r->h2d_chunk = cfg.chunk_blocks ? (int)cfg.chunk_blocks : std::max(16, (p.Tmax + 11) / 12);
+  r->h2d_events.resize((p.Tmax + r->h2d_chunk - 1) / r->h2d_chunk);
+  for (cudaEvent_t &e : r->h2d_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 
   // ---- allocations -----------------------------------------------------------------------
   const size_t TB = (size_t)p.Tmax * p.B;
@@ -253,7 +266,12 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
 }
 
 // Queue the kernels for T blocks whose audio and tables are already in the staging areas.
-void run_pipeline(bear_cuda_renderer *r, int T)
+// A call may be issued in chunks of `chunk` periods (all kernels of chunk c, then chunk c+1, ...):
+// every intermediate buffer is indexed by the period number within the call, so later chunks just
+// read earlier columns.  `before_chunk(c, k0, n)` runs on the host before chunk c is queued (the
+// host-buffer path uses it to make the stream wait for that chunk's upload).
+template <class Hook>
+void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Hook &&before_chunk)
 {
   Layout &p = r->lay;
   cudaStream_t st = r->stream;
@@ -268,12 +286,20 @@ void run_pipeline(bear_cuda_renderer *r, int T)
     chain.push_back(e);
     if (kernel_id >= 0) ids.push_back(kernel_id);
   };
-  if (p.N + p.M > 0) { mark(BEAR_CUDA_KERNEL_MIX); launch_mix(p, T, st); }
-  if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, T, st); }
-  if (p.N > 0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, T, st); }
-  mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, T, st);
-  mark(BEAR_CUDA_KERNEL_CMAC); launch_cmac(p, T, st);
-  mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, T, st);
+  if (chunk <= 0 || chunk > T) chunk = T;
+  int nchunks = 0;
+  for (int k0 = 0; k0 < T; k0 += chunk, nchunks++) {
+    const int n = std::min(chunk, T - k0);
+    before_chunk(nchunks, k0, n);
+    p.k0 = k0;
+    if (p.N + p.M > 0) { mark(BEAR_CUDA_KERNEL_MIX); launch_mix(p, n, st); }
+    if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, n, st); }
+    if (p.N > 0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, st); }
+    mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, st);
+    mark(BEAR_CUDA_KERNEL_CMAC); launch_cmac(p, n, st);
+    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, st);
+  }
+  p.k0 = 0;
   mark(BEAR_CUDA_KERNEL_CARRY);
 
   CarryPlan plan{};
@@ -316,8 +342,13 @@ void run_pipeline(bear_cuda_renderer *r, int T)
     r->ev_kernel.push_back(std::move(ids));
   }
   CK(cudaGetLastError());
-  r->launches += r->kernels_per_call;
+  r->launches += (uint64_t)(r->kernels_per_call - 1) * nchunks + 1;
   p.fdl_head = (p.fdl_head + T) % p.R;
+}
+
+void run_pipeline(bear_cuda_renderer *r, int T)
+{
+  run_pipeline(r, T, r->chunk, [](int, int, int) {});
 }
 
 template <class F>
@@ -346,10 +377,10 @@ int guarded(bear_cuda_renderer *r, F &&f)
   }
 }
 
-void upload_tables(bear_cuda_renderer *r, int T, const bear_cuda_block_tables *t, bool allow_unchanged)
+void upload_tables(bear_cuda_renderer *r, int T, const bear_cuda_block_tables *t, bool allow_unchanged,
+                   cudaStream_t st)
 {
   Layout &p = r->lay;
-  cudaStream_t st = r->stream;
   auto up = [&](float *dev, size_t per_block, size_t slot0_blocks, const float *host, const char *name) {
     if (per_block == 0) return;
     float *dst = dev + slot0_blocks * per_block;
@@ -533,17 +564,27 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
     if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
     if (!output) throw InvalidArgument{"output must not be NULL"};
     const size_t TB = (size_t)T * p.B;
-    auto up_audio = [&](int row0, int rows, const float *host, size_t stride, const char *name) {
-      if (rows == 0) return;
-      if (!host) throw InvalidArgument{std::string(name) + " input must not be NULL"};
-      CK(cudaMemcpy2DAsync(p.xin + (size_t)row0 * p.xs + p.hist, p.xs * sizeof(float), host, stride * sizeof(float),
-                           TB * sizeof(float), rows, cudaMemcpyHostToDevice, r->stream));
-    };
-    up_audio(0, p.N, objects, objects_stride, "objects");
-    up_audio(p.N, p.M, direct_speakers, direct_speakers_stride, "direct_speakers");
-    up_audio(p.N + p.M, p.H, hoa, hoa_stride, "hoa");
-    upload_tables(r, (int)T, tables, false);
-    run_pipeline(r, (int)T);
+    if (p.N && !objects) throw InvalidArgument{"objects input must not be NULL"};
+    if (p.M && !direct_speakers) throw InvalidArgument{"direct_speakers input must not be NULL"};
+    if (p.H && !hoa) throw InvalidArgument{"hoa input must not be NULL"};
+    // Uploads go to their own stream in chunks of h2d_chunk periods, the render stream waits for
+    // chunk c before it queues the kernels of chunk c: copies of later chunks overlap the kernels.
+    cudaStream_t cs = r->copy_stream;
+    upload_tables(r, (int)T, tables, false, cs);
+    const int hc = r->h2d_chunk;
+    for (int k0 = 0, c = 0; k0 < (int)T; k0 += hc, c++) {
+      const size_t col = (size_t)k0 * p.B, width = (size_t)std::min(hc, (int)T - k0) * p.B * sizeof(float);
+      auto up_audio = [&](int row0, int rows, const float *host, size_t stride) {
+        if (rows)
+          CK(cudaMemcpy2DAsync(p.xin + (size_t)row0 * p.xs + p.hist + col, p.xs * sizeof(float), host + col,
+                               stride * sizeof(float), width, rows, cudaMemcpyHostToDevice, cs));
+      };
+      up_audio(0, p.N, objects, objects_stride);
+      up_audio(p.N, p.M, direct_speakers, direct_speakers_stride);
+      up_audio(p.N + p.M, p.H, hoa, hoa_stride);
+      CK(cudaEventRecord(r->h2d_events[c], cs));
+    }
+    run_pipeline(r, (int)T, hc, [&](int c, int, int) { CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0)); });
     CK(cudaMemcpy2DAsync(output, out_stride * sizeof(float), p.out, p.os * sizeof(float), TB * sizeof(float), 2,
                          cudaMemcpyDeviceToHost, r->stream));
     CK(cudaStreamSynchronize(r->stream));
@@ -573,7 +614,7 @@ int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
     if (row)
       CK(cudaMemcpy2DAsync(p.xin + p.hist, p.xs * sizeof(float), r->h_in, B * sizeof(float), B * sizeof(float), row,
                            cudaMemcpyHostToDevice, r->stream));
-    upload_tables(r, 1, tables, true);
+    upload_tables(r, 1, tables, true, r->stream);
     run_pipeline(r, 1);
     CK(cudaMemcpy2DAsync(r->h_out, B * sizeof(float), p.out, p.os * sizeof(float), B * sizeof(float), 2,
                          cudaMemcpyDeviceToHost, r->stream));

@@ -30,7 +30,7 @@ class Config(C.Structure):
         ("max_batch_blocks", C.c_uint32), ("device", C.c_int32), ("max_delay_samples", C.c_uint32),
         ("object_splits", C.c_uint32), ("cmac_splits", C.c_uint32),
         ("gain_ramp_offset", C.c_uint32), ("delay_ramp_offset", C.c_uint32),
-        ("xfade_ramp_offset", C.c_uint32), ("reserved", C.c_uint32 * 4),
+        ("xfade_ramp_offset", C.c_uint32), ("chunk_blocks", C.c_uint32), ("reserved", C.c_uint32 * 3),
     ]
 
 
@@ -204,7 +204,7 @@ class Renderer:
 
     def __init__(self, data, num_objects=0, num_direct_speakers=0, num_hoa=0, period=0, max_batch_blocks=1,
                  device=0, max_delay_samples=0, object_splits=0, cmac_splits=0, ramp_offsets=(1, 1, 1),
-                 sample_rate=48000):
+                 sample_rate=48000, chunk_blocks=0):
         """`data`: path to a BEAR data file, or a bear_b200.data_file.DataFile."""
         self._l = lib()
         self._h = C.c_void_p()
@@ -212,7 +212,7 @@ class Renderer:
         cfg.num_objects_channels, cfg.num_direct_speakers_channels = num_objects, num_direct_speakers
         cfg.num_hoa_channels, cfg.period_size, cfg.sample_rate = num_hoa, period, sample_rate
         cfg.max_batch_blocks, cfg.device, cfg.max_delay_samples = max_batch_blocks, device, max_delay_samples
-        cfg.object_splits, cfg.cmac_splits = object_splits, cmac_splits
+        cfg.object_splits, cfg.cmac_splits, cfg.chunk_blocks = object_splits, cmac_splits, chunk_blocks
         cfg.gain_ramp_offset, cfg.delay_ramp_offset, cfg.xfade_ramp_offset = ramp_offsets
         if isinstance(data, (str, os.PathLike)):
             rc = self._l.bear_cuda_create_from_file(C.byref(cfg), str(data).encode(), C.byref(self._h))

@@ -51,6 +51,7 @@ def parse_args():
     ap.add_argument("--seconds", type=float, default=10.0, help="audio seconds per step and GPU")
     ap.add_argument("--cpu-sample-blocks", type=int, default=0, help="blocks of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunk-blocks", type=int, default=0, help="periods per launch group (0 = library default)")
     return ap.parse_args()
 
 
@@ -184,7 +185,7 @@ def run_reference(args, rank):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def workload_config(args, T, instances=None):
@@ -215,7 +216,7 @@ def run_ours(args, rank, world, local_rank):
     scen, B, N = WORKLOADS[args.workload]
     T = max(8, int(args.seconds * FS / B) // 8 * 8)
     data, ctl, N, B, tb, audio = make_workload(args.workload, T, group=rank)
-    r = Renderer(data, N, 0, 0, B, max_batch_blocks=T, device=local_rank)
+    r = Renderer(data, N, 0, 0, B, max_batch_blocks=T, device=local_rank, chunk_blocks=args.chunk_blocks)
     io = device_io.DeviceBuffers(r, device_index=local_rank)
     io.load_audio(audio)
     io.load_tables(tb)
@@ -339,14 +340,32 @@ def run_ours(args, rank, world, local_rank):
         }
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_single(args)
-        print(json.dumps(line), flush=True)
+        emit(line)
     r.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line, on the real stdout (fd 1 is pointed at stderr while the run is going so that
+    library banners such as NCCL's version line cannot land in front of it)."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, data)
+    else:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -35,7 +35,7 @@ typedef struct bear_cuda_config {
   uint32_t num_objects_channels;         /* N */
   uint32_t num_direct_speakers_channels; /* M */
   uint32_t num_hoa_channels;             /* H */
-  uint32_t period_size;                  /* B: power of two, 64..4096 */
+  uint32_t period_size;                  /* B: power of two, 128..4096 */
   uint32_t sample_rate;                  /* informational; the data file's fs converts delays */
   uint32_t max_batch_blocks;             /* largest T accepted by the *_batch calls (>=1) */
   int32_t device;                        /* CUDA device ordinal */
@@ -47,7 +47,8 @@ typedef struct bear_cuda_config {
   uint32_t gain_ramp_offset;
   uint32_t delay_ramp_offset;
   uint32_t xfade_ramp_offset;
-  uint32_t reserved[4];
+  uint32_t chunk_blocks;                 /* periods per launch group / upload chunk (0 = automatic) */
+  uint32_t reserved[3];
 } bear_cuda_config;
 
 /* The data-file tables `Panner` hands to the DSP constructor (visr_bear/src/panner.cpp:52-137,

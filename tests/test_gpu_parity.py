@@ -101,6 +101,24 @@ def test_partial_sum_splits(oracle, small_data, splits):
     check(out, ref, str(splits))
 
 
+@pytest.mark.parametrize("chunk", [1, 2, 5])
+def test_chunked_launch_and_overlapped_upload(oracle, small_data, chunk):
+    """A call issued in chunks of periods (uploads of later chunks overlap the kernels of earlier
+    ones) gives the same result as the one-launch form."""
+    B, T = 256, 11
+    ctl = control.HostControl(small_data)
+    kw, N, M, H = case_tables(ctl, "all_views", T, np.random.default_rng(7))
+    tb = ctl.tables(T, **kw)
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((N, 0), (M, 100), (H, 200)))
+    ref = ref_render(oracle, small_data, N, M, H, B, tb, obj, ds, hoa)
+    whole = gpu_render(small_data, N, M, H, B, tb, obj, ds, hoa, "batch")
+    out = gpu_render(small_data, N, M, H, B, tb, obj, ds, hoa, "batch", chunk_blocks=chunk)
+    check(out, ref, "chunk %d" % chunk)
+    np.testing.assert_array_equal(out, whole)
+    out2 = gpu_render(small_data, N, M, H, B, tb, obj, ds, hoa, "batch6", chunk_blocks=chunk)   # 6 + 5 periods
+    check(out2, ref, "chunk %d, two calls" % chunk)
+
+
 def test_unity_fixture_path_delays_through_file_loader(oracle, unity_data):
     """visr_bear/test/test_delays.py:114-136 on the CUDA path, data file read by the C++ loader."""
     B, T = 512, 10
