@@ -238,6 +238,15 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
   // stores (consecutive channels, same speaker) spread over 8 banks instead of 1
   __shared__ __align__(16) float sg[kMixChunk][4 * kMaxSpeakers + 4];
   __shared__ float sd[kMixChunk][4];
+  // bit g of smask[ii][0/1]: some direct / diffuse gain of speakers 4g..4g+3 is non-zero in this
+  // period.  Panning gains are sparse (a point source feeds <= 3 of 24 loudspeakers), all-zero
+  // groups are skipped with a CTA-uniform branch; skipped terms would have added exact zeros.
+  __shared__ unsigned smask[kMixChunk][2];
+  // input rows of the staged channels: [hist history samples | kMixTile samples of this tile],
+  // filled with 16-byte cp.async copies so that the per-ear fractional-delay reads are shared-memory
+  // reads (the reads themselves are unaligned 4-tap gathers, which made the kernel wait on L2)
+  extern __shared__ __align__(16) float xt[];
+  const int XW = p.hist + kMixTile;
   const int tid = threadIdx.x;
   const int t = p.k0 * p.B + blockIdx.x * kMixTile + tid;
   const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
@@ -258,6 +267,19 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
   for (int cb = c0; cb < c1; cb += kMixChunk) {
     const int cnt = min(kMixChunk, c1 - cb);
     __syncthreads();
+    if (tid < 2 * kMixChunk) smask[tid >> 1][tid & 1] = 0u;
+    {
+      const int vec_per_row = XW >> 2;
+      const float *src0 = p.xin + (size_t)cb * p.xs + (t - tid);   // column (hist + t0) - hist
+      for (int idx = tid; idx < cnt * vec_per_row; idx += kMixTile) {
+        const int row = idx / vec_per_row, v = idx - row * vec_per_row;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(xt + row * XW + 4 * v);
+        const float *src = src0 + (size_t)row * p.xs + 4 * v;
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
+      }
+      asm volatile("cp.async.commit_group;");
+    }
+    __syncthreads();
     for (int idx = tid; idx < cnt * kMaxSpeakers; idx += kMixTile) {
       const int l = idx / cnt, ii = idx - l * cnt, c = cb + ii;
       float g0 = 0.f, g1 = 0.f, q0 = 0.f, q1 = 0.f;
@@ -275,6 +297,8 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
       }
       sg[ii][l] = g0; sg[ii][kMaxSpeakers + l] = g1 - g0;
       sg[ii][2 * kMaxSpeakers + l] = q0; sg[ii][3 * kMaxSpeakers + l] = q1 - q0;
+      if (g0 != 0.f || g1 != 0.f) atomicOr(&smask[ii][0], 1u << (l >> 2));
+      if (q0 != 0.f || q1 != 0.f) atomicOr(&smask[ii][1], 1u << (l >> 2));
     }
     for (int idx = tid; idx < cnt * 2; idx += kMixTile) {
       const int ii = idx >> 1, e = idx & 1, c = cb + ii;
@@ -290,28 +314,44 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
       d0 *= p.fs; d1 *= p.fs;
       sd[ii][2 * e] = d0; sd[ii][2 * e + 1] = d1 - d0;
     }
+    asm volatile("cp.async.wait_group 0;");
     __syncthreads();
+    const float dmax = (float)(p.hist - 4);
     for (int ii = 0; ii < cnt; ii++) {
-      const float *xr = p.xin + (size_t)(cb + ii) * p.xs + p.hist + t;
-      const float xl = delayed_read(xr, ramped_delay(sd[ii][0], sd[ii][1], rd));
-      const float xR = delayed_read(xr, ramped_delay(sd[ii][2], sd[ii][3], rd));
-      const float x0 = __ldg(xr);
+      const float *xr = xt + ii * XW + p.hist + tid;
+      const unsigned md = smask[ii][0], mq = smask[ii][1];
+      if ((md | mq) == 0u) continue;   // silent channel in this period
       const float4 *g0v = reinterpret_cast<const float4 *>(sg[ii]);
       const float4 *dgv = g0v + kMaxSpeakers / 4;
       const float4 *q0v = g0v + 2 * kMaxSpeakers / 4;
       const float4 *dqv = g0v + 3 * kMaxSpeakers / 4;
+      if (md) {
+        const float xl = delayed_read(xr, fminf(ramped_delay(sd[ii][0], sd[ii][1], rd), dmax));
+        const float xR = delayed_read(xr, fminf(ramped_delay(sd[ii][2], sd[ii][3], rd), dmax));
 #pragma unroll
-      for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
-        float4 g0 = g0v[l4], dg = dgv[l4], q0 = q0v[l4], dq = dqv[l4];
-        float g;
-        g = fmaf(rg, dg.x, g0.x); accL[4 * l4 + 0] = fmaf(g, xl, accL[4 * l4 + 0]); accR[4 * l4 + 0] = fmaf(g, xR, accR[4 * l4 + 0]);
-        g = fmaf(rg, dg.y, g0.y); accL[4 * l4 + 1] = fmaf(g, xl, accL[4 * l4 + 1]); accR[4 * l4 + 1] = fmaf(g, xR, accR[4 * l4 + 1]);
-        g = fmaf(rg, dg.z, g0.z); accL[4 * l4 + 2] = fmaf(g, xl, accL[4 * l4 + 2]); accR[4 * l4 + 2] = fmaf(g, xR, accR[4 * l4 + 2]);
-        g = fmaf(rg, dg.w, g0.w); accL[4 * l4 + 3] = fmaf(g, xl, accL[4 * l4 + 3]); accR[4 * l4 + 3] = fmaf(g, xR, accR[4 * l4 + 3]);
-        accQ[4 * l4 + 0] = fmaf(fmaf(rg, dq.x, q0.x), x0, accQ[4 * l4 + 0]);
-        accQ[4 * l4 + 1] = fmaf(fmaf(rg, dq.y, q0.y), x0, accQ[4 * l4 + 1]);
-        accQ[4 * l4 + 2] = fmaf(fmaf(rg, dq.z, q0.z), x0, accQ[4 * l4 + 2]);
-        accQ[4 * l4 + 3] = fmaf(fmaf(rg, dq.w, q0.w), x0, accQ[4 * l4 + 3]);
+        for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
+          if (md & (1u << l4)) {
+            const float4 g0 = g0v[l4], dg = dgv[l4];
+            float g;
+            g = fmaf(rg, dg.x, g0.x); accL[4 * l4 + 0] = fmaf(g, xl, accL[4 * l4 + 0]); accR[4 * l4 + 0] = fmaf(g, xR, accR[4 * l4 + 0]);
+            g = fmaf(rg, dg.y, g0.y); accL[4 * l4 + 1] = fmaf(g, xl, accL[4 * l4 + 1]); accR[4 * l4 + 1] = fmaf(g, xR, accR[4 * l4 + 1]);
+            g = fmaf(rg, dg.z, g0.z); accL[4 * l4 + 2] = fmaf(g, xl, accL[4 * l4 + 2]); accR[4 * l4 + 2] = fmaf(g, xR, accR[4 * l4 + 2]);
+            g = fmaf(rg, dg.w, g0.w); accL[4 * l4 + 3] = fmaf(g, xl, accL[4 * l4 + 3]); accR[4 * l4 + 3] = fmaf(g, xR, accR[4 * l4 + 3]);
+          }
+        }
+      }
+      if (mq) {
+        const float x0 = xr[0];
+#pragma unroll
+        for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
+          if (mq & (1u << l4)) {
+            const float4 q0 = q0v[l4], dq = dqv[l4];
+            accQ[4 * l4 + 0] = fmaf(fmaf(rg, dq.x, q0.x), x0, accQ[4 * l4 + 0]);
+            accQ[4 * l4 + 1] = fmaf(fmaf(rg, dq.y, q0.y), x0, accQ[4 * l4 + 1]);
+            accQ[4 * l4 + 2] = fmaf(fmaf(rg, dq.z, q0.z), x0, accQ[4 * l4 + 2]);
+            accQ[4 * l4 + 3] = fmaf(fmaf(rg, dq.w, q0.w), x0, accQ[4 * l4 + 3]);
+          }
+        }
       }
     }
   }
@@ -326,10 +366,11 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
   }
 }
 
+size_t mix_smem_bytes(int hist);
 void launch_mix(const Layout &p, int T, cudaStream_t st)
 {
   dim3 grid(T * p.B / kMixTile, p.S);
-  mix_kernel<<<grid, kMixTile, 0, st>>>(p, T);
+  mix_kernel<<<grid, kMixTile, mix_smem_bytes(p.hist), st>>>(p, T);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -705,6 +746,13 @@ cudaError_t static_scratch_pointer(float2 **out)
   }
   *out = resolved[dev];
   return cudaSuccess;
+}
+
+size_t mix_smem_bytes(int hist) { return (size_t)kMixChunk * (hist + kMixTile) * sizeof(float); }
+
+cudaError_t configure_mix(int hist)
+{
+  return cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
 }
 
 cudaError_t configure_kernels(int B)

@@ -34,6 +34,7 @@ struct InvalidArgument { std::string msg; };
 struct Unsupported { std::string msg; };
 
 size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
+bool mix_hist_too_large(int hist) { return (size_t)kMixChunk * (hist + kMixTile) * sizeof(float) > 160 * 1024; }
 
 }  // namespace
 
@@ -152,8 +153,17 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   p.CH = 2 * p.L + p.A;
   p.V = d.num_views;
   p.Tmax = cfg.max_batch_blocks ? cfg.max_batch_blocks : 1;
-  const uint32_t max_delay = cfg.max_delay_samples ? cfg.max_delay_samples : 256;
+  // Longest table delay the data file can produce (panner.cpp:189-235): the largest loudspeaker delay
+  // plus the decorrelation delay, or the HOA delay.  max_delay_samples == 0 derives it from the file.
+  uint32_t max_delay = cfg.max_delay_samples;
+  if (max_delay == 0) {
+    float dm = 0.f;
+    for (size_t i = 0; i < (size_t)d.num_views * d.num_virtual_loudspeakers * 2; i++) dm = std::max(dm, d.delays[i]);
+    max_delay = (uint32_t)std::ceil(std::max((double)dm + d.decorrelation_delay, d.hoa_delay)) + 4;
+  }
   p.hist = (int)round_up(max_delay + 8, 4);
+  if (mix_hist_too_large(p.hist)) throw Unsupported{"max_delay_samples too large for the mix kernel's shared-memory tile"};
+  CK(configure_mix(p.hist));
   p.goff = cfg.gain_ramp_offset; p.doff = cfg.delay_ramp_offset; p.xoff = cfg.xfade_ramp_offset;
   p.fs = (float)d.fs;
   p.hoa_delay = (float)d.hoa_delay;

@@ -250,11 +250,17 @@ def run_ours(args, rank, world, local_rank):
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         return float(ms.item())
 
-    for _ in range(max(3, args.warmup)):
-        step_resident()
+    # clocks are sampled from the warm-up through both timed regions (the timed regions alone last
+    # only tens of milliseconds); a short pre-roll keeps the GPU under load while the sampler starts
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
+    t_pre = time.perf_counter()
+    while time.perf_counter() - t_pre < 0.6:
+        step_resident()
+        r.synchronize()
+    for _ in range(max(3, args.warmup)):
+        step_resident()
     r.set_profiling(True)
     r.get_profile(reset=True)
     launches0 = r.get_info().launches_total
