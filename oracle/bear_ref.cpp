@@ -15,9 +15,12 @@
 //   * partitioned convolution (steady state): cross-checked against the reference's in-tree
 //     libear BlockConvolver (oracle/_ref) and a naive time-domain convolution;
 //   * path-delay equalities of visr_bear/test/test_delays.py:114-136 hold on the in-tree fixture;
-//   * ramp end-point conventions (gain / delay / crossfade) and the Lagrange tap alignment are
-//     VISR-internal: see oracle/identify_conventions.py for what the golden vectors pin;
-//     anything that script cannot pin is "parity unpinned" and is a runtime switch here.
+//   * gain ramp (n+1)/B, delay ramp (n+1)/B, centred Lagrange-3 with method delay 1.5, initial state:
+//     PINNED on the reference's golden vectors (oracle/identify_conventions.py ->
+//     tests/golden/pinned_conventions.json), and the three static no-head-track goldens are replayed
+//     end to end at 2e-5 (tests/test_golden_reference.py);
+//   * view-crossfade ramp (n+1)/B and the diffuse path: "parity unpinned" (no golden that can be
+//     replayed without default.tf exercises them); the ramp offsets are runtime switches.
 //
 // Build: see oracle/Makefile (REAL=float -> libbear_ref_f32.so, REAL=double -> libbear_ref_f64.so).
 #include <algorithm>
