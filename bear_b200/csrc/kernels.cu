@@ -76,12 +76,17 @@ __device__ __forceinline__ void dft8(float2 (&v)[8])
 }
 
 template <bool INV>
-__device__ __forceinline__ float2 twid(float2 v, float2 w) { return INV ? cmul_conj(v, w) : cmul(v, w); }
+__device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int logM, const float2 *__restrict__ tw);
 
 template <bool INV>
-__device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int logM, const float2 *__restrict__ tw)
+__device__ __forceinline__ float2 twid(float2 v, float2 w) { return INV ? cmul_conj(v, w) : cmul(v, w); }
+
+// (tid, nthr): the calling thread's index within, and the size of, the thread group that works on this
+// transform; several groups of one CTA may transform different buffers in lockstep.
+template <bool INV>
+__device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int logM, const float2 *__restrict__ tw,
+                                              int tid, int nthr)
 {
-  const int tid = threadIdx.x, nthr = blockDim.x;
   int ls = 0;
   for (; ls + 3 <= logM; ls += 3) {
     const int Ns = 1 << ls, Q = M >> 3;
@@ -137,6 +142,12 @@ __device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int l
   }
   __syncthreads();
   return a;
+}
+
+template <bool INV>
+__device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int logM, const float2 *__restrict__ tw)
+{
+  return fft_shared<INV>(a, b, M, logM, tw, threadIdx.x, blockDim.x);
 }
 
 // real-FFT split: Z = FFT_M(x[2n] + i x[2n+1]);  X[k], X[M-k] of the length-2M real transform
@@ -461,57 +472,86 @@ void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
 }
 
 // ----------------------------------------------------------------------------------------------
-// bus_fdl_kernel: assemble the 2B-sample window [block k-1, block k] of one convolver input and
-// write its packed spectrum into the frequency-domain delay line.
+// bus_fdl_kernel: assemble the 2B-sample window [block k-1, block k] of the convolver inputs and
+// write their packed spectra into the frequency-domain delay line.
 //   bus channel 2l+e : sum of the direct partials + decorrelator output l read through the
 //                      static delay line 2l+e (dsp.cpp:137-158), ramped when the view changed
 //   HOA channel a    : ambisonic bus a read through the fixed HOA delay.  The reference delays
 //                      the decoder OUTPUT (dsp.cpp:190-197); delay and decode filter are both
 //                      LTI, so the delay is commuted in front and the HOA terms join the same
 //                      frequency-domain accumulation as the BRIR terms.
-// grid: T*CH (channel fastest); block: B/4.
+// A CTA transforms two channels with two thread groups in lockstep: both ears of one loudspeaker
+// (they read the same decorrelator row through different delays) or two HOA channels.  The rows the
+// fractional-delay gathers read are first staged in shared memory with 16-byte cp.async copies.
+// grid: T * (L + ceil(A/2)) (unit fastest); block: 2 * B/8.
 // ----------------------------------------------------------------------------------------------
-__global__ void bus_fdl_kernel(Layout p, int T, int nch)
+__global__ void bus_fdl_kernel(Layout p, int T, int nunits)
 {
-  extern __shared__ float2 sm[];
+  extern __shared__ __align__(16) float2 sm[];
   const int M = p.B;
-  float2 *a = sm, *b = sm + M + (M >> 3);
-  const int ch = blockIdx.x % nch, k = p.k0 + blockIdx.x / nch;
-  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int unit = blockIdx.x % nunits, k = p.k0 + blockIdx.x / nunits;
+  const int nthr = blockDim.x >> 1;
+  const int g = threadIdx.x >= nthr, tid = threadIdx.x - g * nthr;   // group 0 / 1
+  const int FB = M + (M >> 3);                                       // padded FFT buffer, float2
+  float2 *a = sm + (size_t)g * 2 * FB, *b = a + FB;
+  const int RW = p.hist + 2 * M;                                     // staged row: history + window
+  float *rows = reinterpret_cast<float *>(sm + 4 * FB);              // [2][RW]
   const float invB = 1.0f / (float)p.B;
   const int L2 = 2 * p.L;
-  if (ch < L2) {
-    const int l = ch >> 1;
-    const float *wrow = p.w + (size_t)l * p.ws + p.B + p.hist + (size_t)(k - 1) * p.B;
-    const bool dif = p.N > 0;
-    float d0[2], dd[2];
-    for (int h = 0; h < 2; h++) {  // h = 0: block k-1, h = 1: block k
-      const float t0 = p.d_stat[(size_t)(k + h) * L2 + ch] * p.fs;
-      const float t1 = p.d_stat[(size_t)(k + h + 1) * L2 + ch] * p.fs;
-      d0[h] = t0; dd[h] = t1 - t0;
+  const bool bus = unit < p.L;
+  const int ch = bus ? 2 * unit + g : L2 + 2 * (unit - p.L) + g;
+  const bool active = bus || ch < L2 + p.A;                          // odd A: last group idles
+
+  // stage the source rows: columns [k*B, k*B + hist + 2B) of the (B + hist)-prefixed row
+  if (!bus || p.N > 0) {
+    const int nrows = bus ? 1 : 2;
+    const int vec = RW >> 2;
+    for (int idx = threadIdx.x; idx < nrows * vec; idx += blockDim.x) {
+      const int r = idx / vec, v = idx - r * vec;
+      const int am = 2 * (unit - p.L) + r;
+      if (!bus && am >= p.A) continue;
+      const float *src = (bus ? p.w + (size_t)unit * p.ws : p.amb + (size_t)am * p.ws) + (size_t)k * p.B + 4 * v;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(rows + r * RW + 4 * v);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
     }
-    for (int n = tid; n < M; n += nthr) {
-      float2 v = make_float2(0.f, 0.f);
-      for (int s = 0; s < p.S; s++) {
-        const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
-        v.x += c.x; v.y += c.y;
-      }
-      if (dif) {
-        const int t = 2 * n;            // window sample, both of the pair lie in the same block
-        const int h = t >= p.B;
-        const int nn = t - h * p.B;
-        v.x += delayed_read(wrow + t, ramped_delay(d0[h], dd[h], (float)(nn + p.doff) * invB));
-        v.y += delayed_read(wrow + t + 1, ramped_delay(d0[h], dd[h], (float)(nn + 1 + p.doff) * invB));
-      }
-      a[padi(n)] = v;
-    }
-  } else {
-    const int am = ch - L2;
-    const float *arow = p.amb + (size_t)am * p.ws + p.B + p.hist + (size_t)(k - 1) * p.B;
-    for (int n = tid; n < M; n += nthr)
-      a[padi(n)] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
+    asm volatile("cp.async.commit_group;");
+    asm volatile("cp.async.wait_group 0;");
   }
-  float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw);
+  __syncthreads();
+
+  if (active) {
+    if (bus) {
+      const float *wrow = rows + p.hist;    // window sample 0
+      const bool dif = p.N > 0;
+      float d0[2], dd[2];
+      for (int h = 0; h < 2; h++) {  // h = 0: block k-1, h = 1: block k
+        const float t0 = p.d_stat[(size_t)(k + h) * L2 + ch] * p.fs;
+        const float t1 = p.d_stat[(size_t)(k + h + 1) * L2 + ch] * p.fs;
+        d0[h] = t0; dd[h] = t1 - t0;
+      }
+      for (int n = tid; n < M; n += nthr) {
+        float2 v = make_float2(0.f, 0.f);
+        for (int s = 0; s < p.S; s++) {
+          const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
+          v.x += c.x; v.y += c.y;
+        }
+        if (dif) {
+          const int t = 2 * n;            // window sample, both of the pair lie in the same block
+          const int h = t >= p.B;
+          const int nn = t - h * p.B;
+          v.x += delayed_read(wrow + t, ramped_delay(d0[h], dd[h], (float)(nn + p.doff) * invB));
+          v.y += delayed_read(wrow + t + 1, ramped_delay(d0[h], dd[h], (float)(nn + 1 + p.doff) * invB));
+        }
+        a[padi(n)] = v;
+      }
+    } else {
+      const float *arow = rows + g * RW + p.hist;
+      for (int n = tid; n < M; n += nthr)
+        a[padi(n)] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
+    }
+  }
+  float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw, tid, nthr);
+  if (!active) return;
   const int slot = (p.fdl_head + k) % p.R;
   float2 *dst = p.fdl + ((size_t)ch * p.R + slot) * M;
   for (int kk = tid; kk <= M / 2; kk += nthr) {
@@ -526,11 +566,16 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nch)
   }
 }
 
+static size_t bus_fdl_smem_bytes(int B, int hist)
+{
+  return (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float);
+}
+
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
 {
-  int threads = p.B / 8 < 32 ? 32 : p.B / 8;
-  int nch = 2 * p.L + (p.H > 0 ? p.A : 0);
-  bus_fdl_kernel<<<T * nch, threads, fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T, nch);
+  int threads = 2 * (p.B / 8 < 32 ? 32 : p.B / 8);
+  int nunits = p.L + (p.H > 0 ? (p.A + 1) / 2 : 0);
+  bus_fdl_kernel<<<T * nunits, threads, bus_fdl_smem_bytes(p.B, p.hist), st>>>(p, T, nunits);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -750,9 +795,12 @@ cudaError_t static_scratch_pointer(float2 **out)
 
 size_t mix_smem_bytes(int hist) { return (size_t)kMixChunk * (hist + kMixTile) * sizeof(float); }
 
-cudaError_t configure_mix(int hist)
+cudaError_t configure_mix(int hist, int B)
 {
-  return cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
+  cudaError_t e = cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
+  if (e != cudaSuccess) return e;
+  return cudaFuncSetAttribute(bus_fdl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                              (int)bus_fdl_smem_bytes(B, hist));
 }
 
 cudaError_t configure_kernels(int B)
@@ -762,7 +810,6 @@ cudaError_t configure_kernels(int B)
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(filter_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
     if ((e = cudaFuncSetAttribute(decorrelate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
-    if ((e = cudaFuncSetAttribute(bus_fdl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
     if ((e = cudaFuncSetAttribute(ifft_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
   }
   return cudaSuccess;

@@ -79,7 +79,7 @@ void launch_cmac(const Layout &p, int T, cudaStream_t st);
 void launch_ifft_out(const Layout &p, int T, cudaStream_t st);
 void launch_carry(const CarryPlan &plan, cudaStream_t st);
 cudaError_t configure_kernels(int B);
-cudaError_t configure_mix(int hist);
+cudaError_t configure_mix(int hist, int B);
 
 // Fixed-size device scratch that lives in the library image (no allocation), and its device
 // address for the current device (resolved on first use per device).

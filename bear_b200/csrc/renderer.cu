@@ -163,7 +163,7 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   }
   p.hist = (int)round_up(max_delay + 8, 4);
   if (mix_hist_too_large(p.hist)) throw Unsupported{"max_delay_samples too large for the mix kernel's shared-memory tile"};
-  CK(configure_mix(p.hist));
+  CK(configure_mix(p.hist, p.B));
   p.goff = cfg.gain_ramp_offset; p.doff = cfg.delay_ramp_offset; p.xoff = cfg.xfade_ramp_offset;
   p.fs = (float)d.fs;
   p.hoa_delay = (float)d.hoa_delay;
