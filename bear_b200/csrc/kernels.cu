@@ -634,7 +634,7 @@ __device__ __forceinline__ void cmac_body(const Layout &p, int j, int e, int ks,
       float4 xb = make_float4(0.f, 0.f, 0.f, 0.f);
       if (DO_B) xb = __ldg(x + (size_t)slotB * hB);
       int slot = slotA;
-#pragma unroll 3
+#pragma unroll 6
       for (int part = 0; part < P; part++) {
         const float4 xa = __ldg(x + (size_t)slot * hB);
         const float4 hv = ldg_stream(h + (size_t)part * hB);

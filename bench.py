@@ -296,6 +296,20 @@ def run_ours(args, rank, world, local_rank):
     ms_e2e = timed(step_e2e, e2e_steps)
     clk = clocks.stop() if rank == 0 else None
 
+    # ---- real-time use: one period per call through bear_cuda_process (host pointers), wall clock ----
+    stream_ms = None
+    if rank == 0:
+        with Renderer(data, N, 0, 0, B, max_batch_blocks=1, device=local_rank) as rs:
+            blk = [tb.block(k) for k in range(8)]
+            xin = [np.ascontiguousarray(audio[:, k * B:(k + 1) * B]) for k in range(8)]
+            out1 = np.empty((2, B), np.float32)
+            for k in range(16):
+                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
+            t0 = time.perf_counter()
+            for k in range(200):
+                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
+            stream_ms = (time.perf_counter() - t0) / 200 * 1e3
+
     audio_s = T * B / FS
     value = world * N * audio_s * args.steps / (ms * 1e-3)
     e2e_value = world * N * audio_s * e2e_steps / (ms_e2e * 1e-3)
@@ -310,11 +324,15 @@ def run_ours(args, rank, world, local_rank):
             (6650.0, "fallback (B200_PROFILING.md)")
         info = r.get_info()
         L, A, P, KS = data.num_virtual_loudspeakers, data.n_hoa_channels, info.num_partitions, info.cmac_splits
-        # cmac_kernel algorithmic bytes per launch (DESIGN.md "Roofline"): per period and ear, 24*P terms of
-        # B packed bins (8 B each): FDL read once, filter spectra read once per rendered view (2 in a
-        # view-change block), partial spectra written once per rendered view.
-        views_rendered = 2.0  # every block of this workload changes view
-        alg = T * 2 * 8 * B * (L * P + L * P * views_rendered + KS * views_rendered)
+        # cmac_kernel algorithmic bytes per launch.  Minimum HBM traffic of a
+        # T-period launch: every period renders a view that was not rendered in the period before
+        # (its 2L*P filter partitions are read once and serve both this period's new-view spectrum and
+        # the next period's old-view spectrum), every FDL spectrum of the 2L bus channels is read once,
+        # and the partial spectra (2 ears x 2 views x KS splits) are written once; B packed bins x 8 B.
+        alg = T * 8 * B * (2 * L * P + 2 * L + 2 * 2 * KS)
+        # SURVEY 8(d)'s single-period streaming figure for the same work: FDL partitions re-read by each
+        # of the P periods that use them, filters of old and new view both read in a view-change period
+        alg_survey = T * 2 * 8 * B * (L * P + L * P * 2.0 + KS * 2.0)
         t_cmac, n_cmac = prof["cmac_kernel"]
         avg_ms = t_cmac / max(n_cmac, 1)
         achieved = alg / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0
@@ -335,6 +353,10 @@ def run_ours(args, rank, world, local_rank):
             "roofline": {"bound": "hbm", "kernel": "cmac_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": achieved / peak, "traffic": traffic, "peak_source": which,
                          "algorithmic_bytes_per_launch": alg, "avg_launch_ms": avg_ms,
+                         "traffic_source": "profiles/ (ncu --set full of the same command, dram read+write per launch)",
+                         "survey_8d_streaming_bytes_per_launch": alg_survey,
+                         "achieved_survey_8d": alg_survey / (avg_ms * 1e-3) / 1e9 if avg_ms > 0 else 0.0,
+                         "achieved_dram": (traffic / (avg_ms * 1e-3) / 1e9) if (traffic and avg_ms > 0) else None,
                          "share_of_step": (t_cmac / max(args.steps, 1)) / step_ms_kernels if step_ms_kernels else None},
             "kernel_ms_per_step": {k: v[0] / max(args.steps, 1) for k, v in prof.items() if v[1]},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -342,6 +364,8 @@ def run_ours(args, rank, world, local_rank):
                     "api": "bear_cuda_process_batch (pinned host buffers)" if world == 1 else
                            "pinned host -> staging areas -> bear_cuda_process_device -> NCCL all-reduce -> pinned host"},
             "gpu_launches": int(launches),
+            "stream": {"ms_per_period_call": stream_ms, "period_ms": 1e3 * B / FS,
+                       "note": "bear_cuda_process, one period per call incl. host<->device copies and sync (real-time use)"},
             "clocks": clk,
         }
         if world == 1 and not args.no_cpu_baseline:
