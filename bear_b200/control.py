@@ -91,6 +91,18 @@ class HostControl:
         np.put_along_axis(g_hi, self.ring_idx[hi][..., None], np.sin(f * np.pi / 2)[..., None], -1)
         return g + g_hi
 
+    def raw_object_gains(self, obj_az, obj_diffuse=None, obj_gain=None):
+        """What GainCalcObjects would emit for T periods: [T, 2L, N] float32, rows 0..L-1 direct,
+        L..2L-1 diffuse (synthetic panner; no normalisation, no delays)."""
+        obj_az = np.asarray(obj_az, dtype=np.float64)
+        T, N = obj_az.shape
+        g = self.pan(obj_az)
+        if obj_gain is not None:
+            g = g * np.broadcast_to(np.asarray(obj_gain, dtype=np.float64), (T, N))[..., None]
+        dif = np.zeros((T, N)) if obj_diffuse is None else np.broadcast_to(np.asarray(obj_diffuse, dtype=np.float64), (T, N))
+        both = np.concatenate([g * np.sqrt(1.0 - dif)[..., None], g * np.sqrt(dif)[..., None]], -1)   # [T,N,2L]
+        return np.ascontiguousarray(both.transpose(0, 2, 1), dtype=np.float32)
+
     # ---- reference formulas ------------------------------------------------------------
     def select_view(self, yaw_deg):
         """Listener yaw (degrees, anticlockwise seen from above) -> view index; the look vector is

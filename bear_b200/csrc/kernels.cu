@@ -768,6 +768,133 @@ void launch_carry(const CarryPlan &plan, cudaStream_t st)
 }
 
 // ----------------------------------------------------------------------------------------------
+// control_kernel: the Control graph's table producers between the gain calculators and the DSP
+// ports, one warp per (period, channel); all arithmetic in double like the reference, float at the
+// ports.  References: Panner::get_delays panner.cpp:189-208, compensation_gain :277-316,:332-346,
+// :364-380, compensation_gain_direct :318-330,:348-362,:391-404, GainNorm::process gain_norm.cpp:26-44,
+// DirectDiffuseSplit direct_diffuse_split.cpp:24-32, StaticDelayCalc static_delay_calc.cpp:19-30.
+// Lane j holds gain j (and j+32): direct gains 0..L-1, diffuse gains L..2L-1.  The quadratic form of
+// the gain-normalisation table is evaluated only over the non-zero gains (panning gains are sparse).
+// grid: (ceil((N+M+1)/4), T); block: 128 (4 warps).
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__global__ void __launch_bounds__(128) control_kernel(Layout p, int T)
+{
+  const int lane = threadIdx.x & 31;
+  const int c = blockIdx.x * 4 + (threadIdx.x >> 5);     // channel: objects, DirectSpeakers, then "static delays"
+  const int t = blockIdx.y;
+  const int L = p.L, G = 2 * L, N = p.N, M = p.M;
+  if (c > N + M) return;
+  const int v = p.view[t + 1];
+  const float *dl = p.delays_tab + (size_t)v * L * 2;
+  if (c == N + M) {  // StaticDelayCalc
+    for (int i = lane; i < G; i += 32) p.d_stat[(size_t)(t + 2) * G + i] = (float)((double)dl[i] / p.fs_d);
+    return;
+  }
+  const bool obj = c < N;
+  // gains of this channel: g0 = entry `lane`, g1 = entry `lane + 32`
+  float f0 = 0.f, f1 = 0.f;
+  if (obj) {
+    const float *raw = p.raw_obj + (size_t)t * G * N + c;
+    if (lane < G) f0 = raw[(size_t)lane * N];
+    if (lane + 32 < G) f1 = raw[(size_t)(lane + 32) * N];
+  } else {
+    const float *raw = p.raw_ds + (size_t)t * L * M + (c - N);
+    if (lane < L) f0 = raw[(size_t)lane * M];
+  }
+  const double g0 = (double)f0, g1 = (double)f1;
+  // ---- delays: gain-weighted mean of the loudspeaker delays (direct + diffuse gains for objects) ----
+  // total gain of loudspeaker l = g[l] + g[L + l]; entry L + l lives in lane (L + l) & 31, slot (L + l) >> 5
+  const int jd = L + lane;                               // index of this loudspeaker's diffuse gain
+  const double a_ = __shfl_sync(0xffffffffu, g0, jd & 31), b_ = __shfl_sync(0xffffffffu, g1, jd & 31);
+  double tot = 0.0;
+  if (lane < L) {
+    tot = g0;
+    if (obj) tot += (jd < 32) ? a_ : b_;
+  }
+  const double dL = lane < L ? (double)dl[2 * lane] : 0.0, dR = lane < L ? (double)dl[2 * lane + 1] : 0.0;
+  const double total = warp_sum(tot), sl = warp_sum(dL * tot), sr = warp_sum(dR * tot);
+  double ml, mr;
+  if (total > 1e-6) { ml = sl / total; mr = sr / total; }
+  else { ml = (double)dl[2 * p.front]; mr = (double)dl[2 * p.front + 1]; }
+  const float del[2] = {(float)((ml + p.dec_delay_d) / p.fs_d), (float)((mr + p.dec_delay_d) / p.fs_d)};
+  // ---- compensation gain ----
+  double comp = 1.0;
+  if (p.gn_factors) {
+    const int Gq = obj ? G : L;                      // size of the quadratic form
+    const size_t GG = (size_t)G * G * 2;             // floats per (sample, view)
+    const float *F0 = p.gn_factors + (size_t)v * GG;  // sample 0
+    const size_t sample_stride = (size_t)p.V * GG;
+    double e_acc = 0.0;
+    if (lane < Gq) e_acc += g0 * g0 * ((double)F0[((size_t)lane * G + lane) * 2] + (double)F0[((size_t)lane * G + lane) * 2 + 1]);
+    if (lane + 32 < Gq) {
+      const int j = lane + 32;
+      e_acc += g1 * g1 * ((double)F0[((size_t)j * G + j) * 2] + (double)F0[((size_t)j * G + j) * 2 + 1]);
+    }
+    const double expected = sqrt(warp_sum(e_acc));
+    const unsigned nz0 = __ballot_sync(0xffffffffu, f0 != 0.f), nz1 = __ballot_sync(0xffffffffu, f1 != 0.f);
+    double r_acc = 0.0;
+    for (int e = 0; e < 2; e++) {
+      int s_lo = 0, ns = 1;
+      double pw[2] = {1.0, 0.0};
+      if (obj) {
+        const double unclamped = (double)del[e] * p.fs_d - p.dec_delay_d;
+        const double d = fmin(fmax(0.0, unclamped), (double)p.gnS - 1.0);
+        s_lo = min((int)floor(d), p.gnS - 2);
+        ns = 2;
+        pw[0] = 1.0 - fabs(d - (double)s_lo);
+        pw[1] = 1.0 - fabs(d - (double)(s_lo + 1));
+      }
+      for (int si = 0; si < ns; si++) {
+        const float *Fs = F0 + (size_t)(s_lo + si) * sample_stride + e;
+        for (int half = 0; half < 2; half++) {
+          unsigned m = half ? nz1 : nz0;
+          while (m) {
+            const int b = __ffs(m) - 1;
+            m &= m - 1;
+            const int i = b + 32 * half;
+            if (i >= Gq) continue;
+            const double gi = half ? __shfl_sync(0xffffffffu, g1, b) : __shfl_sync(0xffffffffu, g0, b);
+            const float *row = Fs + (size_t)i * G * 2;
+            double part = 0.0;
+            if (lane < Gq) part += g0 * (double)row[(size_t)lane * 2];
+            if (lane + 32 < Gq) part += g1 * (double)row[(size_t)(lane + 32) * 2];
+            r_acc += pw[si] * gi * part;
+          }
+        }
+      }
+    }
+    const double real = sqrt(warp_sum(r_acc));
+    comp = fabs(real) < 1e-6 ? 1.0 : expected / real;
+  }
+  // ---- write the tables of period t (slot t + 1) ----
+  if (obj) {
+    if (lane < 2) p.d_dir[(size_t)(t + 1) * 2 * N + 2 * c + lane] = del[lane];
+    if (lane < G) {
+      float *dst = lane < L ? p.g_dir + ((size_t)(t + 1) * L + lane) * N : p.g_dif + ((size_t)(t + 1) * L + lane - L) * N;
+      dst[c] = (float)(comp * g0);
+    }
+    if (lane + 32 < G) p.g_dif[((size_t)(t + 1) * L + lane + 32 - L) * N + c] = (float)(comp * g1);
+  } else {
+    const int j = c - N;
+    if (lane < 2) p.d_ds[(size_t)(t + 1) * 2 * M + 2 * j + lane] = del[lane];
+    if (lane < L) p.g_ds[((size_t)(t + 1) * L + lane) * M + j] = (float)(comp * g0);
+  }
+}
+
+void launch_control(const Layout &p, int T, cudaStream_t st)
+{
+  dim3 grid((p.N + p.M + 1 + 3) / 4, T);
+  control_kernel<<<grid, 128, 0, st>>>(p, T);
+}
+
+// ----------------------------------------------------------------------------------------------
 // Library-owned scratch for the partial spectra (see bear_cuda_process_device_static_scratch).
 // One array per GPU that loads this library, held until the process exits.  Host code must not use
 // the symbol itself as a pointer: on the host `g_static_ypart` only stands in for the device array,

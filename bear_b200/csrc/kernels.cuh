@@ -51,6 +51,14 @@ struct Layout {
   const float2 *tw;          // [B] exp(-i pi q / B)
   // out
   float *out;  size_t os;    // [2][os]
+  // control tail (optional): data-file delay table, gain-normalisation factors, raw gains of this call
+  const float *delays_tab;   // [V][L][2] samples
+  const float *gn_factors;   // [gnS][V][2L][2L][2] or null
+  int gnS;
+  float *raw_obj;            // [Tmax][2L][N]
+  float *raw_ds;             // [Tmax][L][M]
+  double fs_d, dec_delay_d;
+  int front;
   int fdl_head;              // ring slot of block 0 of this call
   int k0;                    // first period of this launch (a call may be issued in chunks)
 };
@@ -78,6 +86,7 @@ void launch_bus_fdl(const Layout &p, int T, cudaStream_t st);
 void launch_cmac(const Layout &p, int T, cudaStream_t st);
 void launch_ifft_out(const Layout &p, int T, cudaStream_t st);
 void launch_carry(const CarryPlan &plan, cudaStream_t st);
+void launch_control(const Layout &p, int T, cudaStream_t st);
 cudaError_t configure_kernels(int B);
 cudaError_t configure_mix(int hist, int B);
 

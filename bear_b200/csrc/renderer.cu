@@ -45,6 +45,7 @@ struct bear_cuda_renderer {
   cudaStream_t stream = nullptr;
   cudaStream_t copy_stream = nullptr;      // host->device uploads of the host-buffer path
   std::vector<cudaEvent_t> h2d_events;     // one per upload chunk
+  bool tables_on_device = false;           // bear_cuda_control_tables filled the staging tables
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -217,6 +218,30 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   p.os = round_up(TB, 4);
   p.out = r->dalloc<float>(2 * p.os);
   r->audio_out = p.out;
+
+  // control tail: data-file delay table, optional gain-normalisation factors, raw-gain staging
+  {
+    const size_t nd = (size_t)p.V * p.L * 2;
+    float *dt = r->dalloc<float>(nd, false);
+    CK(cudaMemcpyAsync(dt, d.delays, nd * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+    p.delays_tab = dt;
+    p.gn_factors = nullptr;
+    p.gnS = 0;
+    if (d.gain_norm_factors && d.num_gain_norm_delays) {
+      if (d.num_gain_norm_delays < 2) throw InvalidArgument{"gain_norm factors need at least 2 delay samples"};
+      const size_t nf = (size_t)d.num_gain_norm_delays * p.V * 4 * p.L * p.L * 2;
+      float *gf = r->dalloc<float>(nf, false);
+      CK(cudaMemcpyAsync(gf, d.gain_norm_factors, nf * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+      p.gn_factors = gf;
+      p.gnS = (int)d.num_gain_norm_delays;
+    }
+    p.raw_obj = r->dalloc<float>((size_t)p.Tmax * 2 * p.L * std::max(1, p.N));
+    p.raw_ds = r->dalloc<float>((size_t)p.Tmax * p.L * std::max(1, p.M));
+    p.fs_d = d.fs;
+    p.dec_delay_d = d.decorrelation_delay;
+    p.front = (int)d.front_loudspeaker;
+    CK(cudaStreamSynchronize(r->stream));
+  }
 
   // twiddles exp(-i pi q / B), computed in double
   {
@@ -402,7 +427,11 @@ void upload_tables(bear_cuda_renderer *r, int T, const bear_cuda_block_tables *t
       throw InvalidArgument{std::string("table must not be NULL: ") + name};
     }
   };
-  if (!t) throw InvalidArgument{"tables must not be NULL"};
+  if (!t) {  // tables of this call were prepared on the device by bear_cuda_control_tables
+    if (!r->tables_on_device) throw InvalidArgument{"tables must not be NULL (no bear_cuda_control_tables call pending)"};
+    r->tables_on_device = false;
+    return;
+  }
   up(p.g_dir, (size_t)p.L * p.N, 1, t->direct_gains, "direct_gains");
   up(p.g_dif, (size_t)p.L * p.N, 1, t->diffuse_gains, "diffuse_gains");
   up(p.d_dir, (size_t)2 * p.N, 1, t->direct_delays, "direct_delays");
@@ -430,7 +459,7 @@ void upload_tables(bear_cuda_renderer *r, int T, const bear_cuda_block_tables *t
 // The tables Panner::Panner unpacks from a data file, with its checks (panner.cpp:52-137).
 struct LoadedData {
   tenf::File tf;
-  tenf::FloatTensor views, brirs, delays, dec, hoa;
+  tenf::FloatTensor views, brirs, delays, dec, hoa, gn;
   bear_cuda_data d{};
   LoadedData(const char *path, bool need_tables) : tf(path)
   {
@@ -458,6 +487,16 @@ struct LoadedData {
     check(delays.shape[1] == L, "delays axis 1 is wrong size");
     check(delays.shape[2] == 2, "delays axis 2 is wrong size");
     check(dec.shape[0] == L, "decorrelation filters axis 0 is wrong size");
+    if (const tenf::Json *q = m.find("gain_norm_quick")) {                                           // panner.cpp:113-123
+      gn = tf.unpack_f32(q->at("factors"));
+      check(gn.shape.size() == 5, "gain comp factors must have 5 dimensions");
+      check(gn.shape[1] == V, "gain comp factors axis 1 is wrong size");
+      check(gn.shape[2] == L * 2, "gain comp factors axis 2 is wrong size");
+      check(gn.shape[3] == L * 2, "gain comp factors axis 3 is wrong size");
+      check(gn.shape[4] == 2, "gain comp factors axis 4 is wrong size");
+      d.gain_norm_factors = gn.data.data();
+      d.num_gain_norm_delays = (uint32_t)gn.shape[0];
+    }
     check(m.has("hoa"), "HOA decoder not present");                                                  // panner.cpp:125
     hoa = tf.unpack_f32(m.at("hoa").at("irs"));
     check(hoa.shape.size() == 3, "HOA decoder must have 3 dimensions");
@@ -634,6 +673,46 @@ int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
   });
 }
 
+int bear_cuda_control_tables(bear_cuda_renderer *r, uint32_t T, const float *object_gains,
+                             const float *direct_speakers_gains, const int32_t *brir_index, const float *hoa_gains)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    Layout &p = r->lay;
+    cudaStream_t st = r->stream;
+    if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
+    if (p.N && !object_gains) throw InvalidArgument{"object_gains must not be NULL"};
+    if (p.M && !direct_speakers_gains) throw InvalidArgument{"direct_speakers_gains must not be NULL"};
+    if (!brir_index) throw InvalidArgument{"brir_index must not be NULL"};
+    if (p.H && !hoa_gains) throw InvalidArgument{"hoa_gains must not be NULL"};
+    for (uint32_t k = 0; k < T; k++)
+      if (brir_index[k] < 0 || brir_index[k] >= p.V) throw InvalidArgument{"brir_index out of range"};
+    CK(cudaMemcpyAsync(p.view + 1, brir_index, (size_t)T * sizeof(int32_t), cudaMemcpyHostToDevice, st));
+    if (p.N)
+      CK(cudaMemcpyAsync(p.raw_obj, object_gains, (size_t)T * 2 * p.L * p.N * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (p.M)
+      CK(cudaMemcpyAsync(p.raw_ds, direct_speakers_gains, (size_t)T * p.L * p.M * sizeof(float), cudaMemcpyHostToDevice, st));
+    if (p.H)
+      CK(cudaMemcpyAsync(p.g_hoa + (size_t)p.A * p.H, hoa_gains, (size_t)T * p.A * p.H * sizeof(float),
+                         cudaMemcpyHostToDevice, st));
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (r->profiling) {
+      auto get = [&]() { cudaEvent_t e; if (r->ev_free.empty()) CK(cudaEventCreate(&e)); else { e = r->ev_free.back(); r->ev_free.pop_back(); } return e; };
+      e0 = get(); e1 = get();
+      CK(cudaEventRecord(e0, st));
+    }
+    launch_control(p, (int)T, st);
+    CK(cudaGetLastError());
+    if (r->profiling) {
+      CK(cudaEventRecord(e1, st));
+      r->ev_pending.push_back({e0, e1});
+      r->ev_kernel.push_back({BEAR_CUDA_KERNEL_CONTROL});
+    }
+    r->launches++;
+    r->tables_on_device = true;
+  });
+}
+
 int bear_cuda_get_device_io(bear_cuda_renderer *r, bear_cuda_device_io *io)
 {
   if (!r || !io) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
@@ -743,7 +822,7 @@ int bear_cuda_get_profile(bear_cuda_renderer *r, bear_cuda_kernel_profile *out, 
     r->ev_kernel.clear();
     static const char *names[BEAR_CUDA_NUM_KERNELS] = {"mix_kernel", "hoa_mix_kernel", "decorrelate_kernel",
                                                        "bus_fdl_kernel", "cmac_kernel", "ifft_out_kernel",
-                                                       "carry_kernel"};
+                                                       "carry_kernel", "control_kernel"};
     for (int k = 0; k < BEAR_CUDA_NUM_KERNELS; k++) {
       std::snprintf(out[k].name, sizeof(out[k].name), "%s", names[k]);
       out[k].total_ms = r->prof_ms[k];

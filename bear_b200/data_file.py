@@ -41,6 +41,7 @@ class DataFile:
     decorrelation_delay: float
     front_loudspeaker: int
     hoa_delay: float = 0.0
+    gain_norm_factors: object = None   # [S,V,2L,2L,2] f32 ("gain_norm_quick"/"factors", panner.cpp:113-123) or None
     layout: object = None
     extra: dict = field(default_factory=dict)
 
@@ -100,13 +101,21 @@ def from_tree(tree):
     order = int(round(np.sqrt(hoa.shape[0]))) - 1
     if (order + 1) ** 2 != hoa.shape[0]:
         raise DataFileError("bad number of hoa channels")
+    gn = None
+    if "gain_norm_quick" in tree:
+        gn = f32(tree["gain_norm_quick"]["factors"])
+        _check(gn.ndim == 5, "gain comp factors must have 5 dimensions")
+        _check(gn.shape[1] == V, "gain comp factors axis 1 is wrong size")
+        _check(gn.shape[2] == L * 2, "gain comp factors axis 2 is wrong size")
+        _check(gn.shape[3] == L * 2, "gain comp factors axis 3 is wrong size")
+        _check(gn.shape[4] == 2, "gain comp factors axis 4 is wrong size")
     known = {"views", "brirs", "delays", "decorrelation_filters", "hoa", "fs",
-             "decorrelation_delay", "front_loudspeaker", "layout"}
+             "decorrelation_delay", "front_loudspeaker", "layout", "gain_norm_quick"}
     return DataFile(
         views=views, brirs=brirs, delays=delays, decorrelation_filters=dec, hoa_irs=hoa,
         fs=float(tree["fs"]), decorrelation_delay=float(int(tree["decorrelation_delay"])),
         front_loudspeaker=int(tree["front_loudspeaker"]),
-        hoa_delay=float(tree["hoa"].get("delay", 0.0)), layout=tree.get("layout"),
+        hoa_delay=float(tree["hoa"].get("delay", 0.0)), gain_norm_factors=gn, layout=tree.get("layout"),
         extra={k: v for k, v in tree.items() if k not in known},
     )
 
@@ -115,8 +124,34 @@ def load(path):
     return from_tree(tensorfile.read(path))
 
 
+def gain_norm_factors(brirs, decorrelation_filters, delays, dec_delay):
+    """The "gain_norm_quick" factor table of a data file, by the recipe of the reference's authoring
+    tool (bear/process_irs/finalise.py:210-257): inner products between all pairs of the delayed
+    direct-path BRIRs and the decorrelated, delay-rounded diffuse-path BRIRs, per integer direct
+    delay 0..max_delay-1, view and ear.  O(S V (2L)^2 T): only for small synthetic files."""
+    V, L, _, T = brirs.shape
+    b = brirs.astype(np.float64)
+    rd = np.round(delays).astype(int)
+    S = int(np.max(np.ceil(delays))) + 2
+    dl = decorrelation_filters.shape[1]
+    ir_len = max(T + dl - 1 + rd.max(), T + int(dec_delay) + S - 1)
+    out = np.zeros((S, V, 2 * L, 2 * L, 2), np.float32)
+    for v in range(V):
+        dif = np.zeros((L, 2, ir_len))
+        for l in range(L):
+            for e in range(2):
+                c = np.convolve(b[v, l, e], decorrelation_filters[l].astype(np.float64))
+                dif[l, e, rd[v, l, e]:rd[v, l, e] + len(c)] = c
+        for s in range(S):
+            direct = np.zeros((L, 2, ir_len))
+            direct[:, :, s + int(dec_delay):s + int(dec_delay) + T] = b[v]
+            allb = np.concatenate([direct, dif], 0)
+            out[s, v] = np.einsum("les,mes->lme", allb, allb)
+    return out
+
+
 def synthetic_tree(seed=0, num_views=180, brir_length=2976, decorrelator_length=128,
-                   hoa_ir_length=128, decay=600.0):
+                   hoa_ir_length=128, decay=600.0, gain_norm=False):
     """Synthetic data-file tree of the default.tf shape (SURVEY.md §8d recipe).
 
     Views are unit yaw vectors every 360/V degrees (as the in-tree fixture); delays,
@@ -141,7 +176,12 @@ def synthetic_tree(seed=0, num_views=180, brir_length=2976, decorrelator_length=
     dec = rng.standard_normal((L, decorrelator_length))
     dec /= np.sqrt(np.sum(dec ** 2, axis=1, keepdims=True))
     hoa = 0.1 * rng.standard_normal((16, 2, hoa_ir_length))
+    extra = {}
+    if gain_norm:
+        extra["gain_norm_quick"] = {"factors": gain_norm_factors(brirs.astype(np.float32), dec.astype(np.float32),
+                                                                 delays, int(tpl["decorrelation_delay"]))}
     return {
+        **extra,
         "views": views,
         "brirs": brirs.astype(np.float32),
         "delays": delays,

@@ -41,7 +41,8 @@ class Data(C.Structure):
         ("hoa_ir_length", C.c_uint32),
         ("brirs", _f32p), ("delays", _f32p), ("decorrelation_filters", _f32p), ("hoa_irs", _f32p),
         ("fs", C.c_double), ("decorrelation_delay", C.c_double), ("hoa_delay", C.c_double),
-        ("front_loudspeaker", C.c_uint32), ("reserved", C.c_uint32),
+        ("front_loudspeaker", C.c_uint32), ("num_gain_norm_delays", C.c_uint32),
+        ("gain_norm_factors", _f32p),
     ]
 
 
@@ -89,10 +90,10 @@ EXPORTS = (
     "bear_cuda_process_device", "bear_cuda_synchronize", "bear_cuda_get_info",
     "bear_cuda_host_alloc", "bear_cuda_host_free", "bear_cuda_read_data_file_info",
     "bear_cuda_tenf_read_f32", "bear_cuda_set_profiling", "bear_cuda_get_profile",
-    "bear_cuda_process_device_static_scratch",
+    "bear_cuda_process_device_static_scratch", "bear_cuda_control_tables",
 )
 STATIC_SCRATCH_BYTES = 4 << 20
-NUM_KERNELS = 7
+NUM_KERNELS = 8
 
 
 class KernelProfile(C.Structure):
@@ -137,6 +138,7 @@ def lib():
         l.bear_cuda_read_data_file_info.argtypes = [C.c_char_p, C.POINTER(DataFileInfo)]
         l.bear_cuda_tenf_read_f32.argtypes = [C.c_char_p, C.c_char_p, vp, sz, C.POINTER(sz),
                                               C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+        l.bear_cuda_control_tables.argtypes = [vp, u32, vp, vp, vp, vp]
         l.bear_cuda_set_profiling.argtypes = [vp, C.c_int]
         l.bear_cuda_get_profile.argtypes = [vp, C.POINTER(KernelProfile), C.c_int]
         _lib = l
@@ -226,6 +228,11 @@ class Renderer:
             d.brirs, d.delays, d.decorrelation_filters, d.hoa_irs = (a.ctypes.data_as(_f32p) for a in keep)
             d.fs, d.decorrelation_delay, d.hoa_delay = data.fs, data.decorrelation_delay, data.hoa_delay
             d.front_loudspeaker = data.front_loudspeaker
+            gn = getattr(data, "gain_norm_factors", None)
+            if gn is not None:
+                keep.append(_as_f32(gn))
+                d.gain_norm_factors = keep[-1].ctypes.data_as(_f32p)
+                d.num_gain_norm_delays = gn.shape[0]
             rc = self._l.bear_cuda_create(C.byref(cfg), C.byref(d), C.byref(self._h))
         if rc != OK:
             _raise(rc, self._l.bear_cuda_last_error(None).decode())
@@ -302,11 +309,24 @@ class Renderer:
                                               C.byref(t), C.cast(outp, C.c_void_p)))
         return out
 
+    def control_tables(self, object_gains, direct_speakers_gains, brir_index, hoa_gains=None):
+        """bear_cuda_control_tables: raw gain-calculator outputs of T periods -> the renderer's device
+        tables (delays, gain normalisation, direct/diffuse split, static delays).  object_gains
+        [T,2L,N], direct_speakers_gains [T,L,M], brir_index [T], hoa_gains [T,A,H]."""
+        bi = np.ascontiguousarray(brir_index, dtype=np.int32)
+        og = None if object_gains is None or self.N == 0 else _as_f32(object_gains)
+        dg = None if direct_speakers_gains is None or self.M == 0 else _as_f32(direct_speakers_gains)
+        hg = None if hoa_gains is None or self.H == 0 else _as_f32(hoa_gains)
+        p = lambda a: None if a is None else C.c_void_p(a.ctypes.data)
+        self._check(self._l.bear_cuda_control_tables(self._h, len(bi), p(og), p(dg), p(bi), p(hg)))
+        self._pending_T = len(bi)
+
     def process_batch(self, objects, direct_speakers, hoa, tables, output=None):
         """T periods in one call: objects [N,T*B], direct_speakers [M,T*B], hoa [H,T*B]
-        (row-contiguous float32, row stride free), tables: BlockTables with T blocks."""
+        (row-contiguous float32, row stride free), tables: BlockTables with T blocks, or None to
+        use the tables prepared by the preceding control_tables() call."""
         keep = []
-        T = int(np.asarray(tables["brir_index"]).shape[0])
+        T = self._pending_T if tables is None else int(np.asarray(tables["brir_index"]).shape[0])
         TB = T * self.B
 
         def arr(x, count):
@@ -324,7 +344,8 @@ class Renderer:
         d, ds_ = arr(direct_speakers, self.M)
         h, hs_ = arr(hoa, self.H)
         t = self._tables_struct(tables, keep)
-        self._check(self._l.bear_cuda_process_batch(self._h, T, o, os_, d, ds_, h, hs_, C.byref(t),
+        self._check(self._l.bear_cuda_process_batch(self._h, T, o, os_, d, ds_, h, hs_,
+                                                    None if tables is None else C.byref(t),
                                                     C.c_void_p(out.ctypes.data), out.strides[0] // 4))
         return out
 

@@ -310,6 +310,26 @@ def run_ours(args, rank, world, local_rank):
                 rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
             stream_ms = (time.perf_counter() - t0) / 200 * 1e3
 
+    # ---- control tail on the device (delays + gain normalisation + split), kernel time only ----
+    control_ms = None
+    if rank == 0:
+        import copy
+        d2 = copy.copy(data)
+        S = 40   # default.tf: max loudspeaker delay 38 + 2 (finalise.py:214-215)
+        d2.gain_norm_factors = np.random.default_rng(0).random((S, data.num_views, 2 * ctl.L, 2 * ctl.L, 2),
+                                                               dtype=np.float32)
+        Tc = min(T, 128)
+        with Renderer(d2, N, 0, 0, B, max_batch_blocks=Tc, device=local_rank) as rc:
+            raw = np.concatenate([tb["direct_gains"][:Tc], tb["diffuse_gains"][:Tc]], axis=1)
+            rc.set_profiling(True)
+            for _ in range(4):
+                rc.control_tables(raw, None, tb["brir_index"][:Tc])
+            t_ctl, n_ctl = rc.get_profile()["control_kernel"]
+            control_ms = {"ms_per_launch": t_ctl / max(n_ctl, 1), "periods_per_launch": Tc, "objects": N,
+                          "ms_per_10s_audio": t_ctl / max(n_ctl, 1) * T / Tc,
+                          "note": "control_kernel (DirectDelayCalc + GainNorm + DirectDiffuseSplit + StaticDelayCalc on the "
+                                  "device), gain-norm table of default.tf shape with random values"}
+
     audio_s = T * B / FS
     value = world * N * audio_s * args.steps / (ms * 1e-3)
     e2e_value = world * N * audio_s * e2e_steps / (ms_e2e * 1e-3)
@@ -364,6 +384,7 @@ def run_ours(args, rank, world, local_rank):
                     "api": "bear_cuda_process_batch (pinned host buffers)" if world == 1 else
                            "pinned host -> staging areas -> bear_cuda_process_device -> NCCL all-reduce -> pinned host"},
             "gpu_launches": int(launches),
+            "control_tail": control_ms,
             "stream": {"ms_per_period_call": stream_ms, "period_ms": 1e3 * B / FS,
                        "note": "bear_cuda_process, one period per call incl. host<->device copies and sync (real-time use)"},
             "clocks": clk,

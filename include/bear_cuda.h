@@ -68,7 +68,8 @@ typedef struct bear_cuda_data {
   double decorrelation_delay;        /* samples */
   double hoa_delay;                  /* samples */
   uint32_t front_loudspeaker;
-  uint32_t reserved;
+  uint32_t num_gain_norm_delays;     /* S, 0 = the file has no "gain_norm_quick" table */
+  const float *gain_norm_factors;    /* [S][V][2L][2L][2] (panner.cpp:113-123) or NULL */
 } bear_cuda_data;
 
 /* Per-block tables = the DSP parameter input ports (visr_bear/src/dsp.cpp:30-53,89-96).
@@ -120,6 +121,22 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
                             const float *direct_speakers, size_t direct_speakers_stride, const float *hoa,
                             size_t hoa_stride, const bear_cuda_block_tables *tables, float *output,
                             size_t out_stride);
+
+/* ---- control tail on the device ----------------------------------------
+
+ * Replaces, for T periods at once, the table producers that sit between the gain calculators and
+ * the DSP ports in the reference's Control graph (visr_bear/src/control.cpp:56-85):
+ *   DirectDelayCalc (direct_delay_calc.cpp:25-42), GainNorm (gain_norm.cpp:26-44 ->
+ *   Panner::compensation_gain, panner.cpp:277-404), DirectDiffuseSplit (direct_diffuse_split.cpp:24-32),
+ *   DirectSpeakersDelayCalc, DirectSpeakersGainNorm, StaticDelayCalc (static_delay_calc.cpp:19-30).
+ * Inputs are what the gain calculators emit: object gains [2L][N] per period (rows 0..L-1 direct,
+ * L..2L-1 diffuse; GainCalcObjects gains_out), DirectSpeakers gains [L][M], the selected view, and
+ * the HOA matrix (passed through).  The kernel writes the direct/diffuse gain, delay and static-delay
+ * tables of the T periods straight into the renderer's device staging areas; follow with
+ * bear_cuda_process_device, or bear_cuda_process_batch / bear_cuda_process with tables == NULL.
+ * With a data file that has no gain_norm_quick table the compensation gain is 1 (panner.cpp:368-369). */
+int bear_cuda_control_tables(bear_cuda_renderer *r, uint32_t T, const float *object_gains,
+                             const float *direct_speakers_gains, const int32_t *brir_index, const float *hoa_gains);
 
 /* ---- device-resident variant (inputs already in HBM) ---------------------------------------- */
 
@@ -197,7 +214,8 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
 #define BEAR_CUDA_KERNEL_CMAC 4
 #define BEAR_CUDA_KERNEL_IFFT_OUT 5
 #define BEAR_CUDA_KERNEL_CARRY 6
-#define BEAR_CUDA_NUM_KERNELS 7
+#define BEAR_CUDA_KERNEL_CONTROL 7
+#define BEAR_CUDA_NUM_KERNELS 8
 
 typedef struct bear_cuda_kernel_profile {
   char name[32];

@@ -573,3 +573,131 @@ void bear_ref_rfft(const float *x, int n, real *out_interleaved)
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// Control tail: the table producers between the gain calculators and the DSP ports, restated from
+// the in-tree reference source (all control math in double, float at the ports):
+//   DirectDelayCalc::process          direct_delay_calc.cpp:25-42   -> Panner::get_delays panner.cpp:189-208
+//   GainNorm::process                 gain_norm.cpp:26-44           -> Panner::compensation_gain :277-316,:332-346,:364-380
+//   DirectDiffuseSplit::process       direct_diffuse_split.cpp:24-32
+//   DirectSpeakersDelayCalc::process  direct_speakers_delay_calc.cpp:24-40
+//   DirectSpeakersGainNorm::process   direct_speakers_gain_norm.cpp:19-32 -> compensation_gain_direct :318-330,:348-362,:391-404
+//   StaticDelayCalc::process          static_delay_calc.cpp:19-30   -> Panner::get_diffuse_delays :224-235
+// ================================================================================================
+namespace {
+struct ControlTables {
+  int L, V, S;
+  double fs, dec_delay;
+  int front;
+  const float *delays;   // [V][L][2]
+  const float *factors;  // [S][V][2L][2L][2] or null
+  double delay(int v, int l, int e) const { return (double)delays[((size_t)v * L + l) * 2 + e]; }
+  double factor(int s, int v, int i, int j, int e) const
+  {
+    const size_t G = 2 * (size_t)L;
+    return (double)factors[((((size_t)s * V + v) * G + i) * G + j) * 2 + e];
+  }
+  // Panner::get_delays
+  void mean_delays(const double *g, int v, double out[2]) const
+  {
+    double total = 0;
+    for (int l = 0; l < L; l++) total += g[l];
+    double m[2];
+    if (total > 1e-6) {
+      double tl = 0, tr = 0;
+      for (int l = 0; l < L; l++) {
+        tl += delay(v, l, 0) * g[l];
+        tr += delay(v, l, 1) * g[l];
+      }
+      m[0] = tl / total; m[1] = tr / total;
+    } else {
+      m[0] = delay(v, front, 0); m[1] = delay(v, front, 1);
+    }
+    out[0] = (m[0] + dec_delay) / fs;
+    out[1] = (m[1] + dec_delay) / fs;
+  }
+  // Panner::compensation_gain (gains: 2L values, direct then diffuse; delays in seconds)
+  double compensation_gain(const double *g, const double dly[2], int v) const
+  {
+    if (!factors) return 1.0;
+    const int G = 2 * L;
+    double expected = 0;
+    for (int e = 0; e < 2; e++)
+      for (int j = 0; j < G; j++) expected += g[j] * g[j] * factor(0, v, j, j, e);
+    expected = std::sqrt(expected);
+    double sum = 0;
+    for (int e = 0; e < 2; e++) {
+      double unclamped = dly[e] * fs - dec_delay;
+      double d = std::min(std::max(0.0, unclamped), (double)S - 1);
+      size_t di = std::min((size_t)std::floor(d), (size_t)S - 2);
+      for (size_t si = 0; si < 2; si++) {
+        size_t s = di + si;
+        double p = 1 - std::abs(d - (double)s);
+        for (int i = 0; i < G; i++) {
+          double i_sum = 0;
+          for (int j = 0; j < G; j++) i_sum += g[j] * factor((int)s, v, i, j, e);
+          sum += p * g[i] * i_sum;
+        }
+      }
+    }
+    double real = std::sqrt(sum);
+    if (std::abs(real) < 1e-6) return 1.0;
+    return expected / real;
+  }
+  // Panner::compensation_gain_direct (gains: L values)
+  double compensation_gain_direct(const double *g, int v) const
+  {
+    if (!factors) return 1.0;
+    double expected = 0, sum = 0;
+    for (int e = 0; e < 2; e++)
+      for (int j = 0; j < L; j++) expected += g[j] * g[j] * factor(0, v, j, j, e);
+    for (int e = 0; e < 2; e++)
+      for (int i = 0; i < L; i++) {
+        double i_sum = 0;
+        for (int j = 0; j < L; j++) i_sum += g[j] * factor(0, v, i, j, e);
+        sum += g[i] * i_sum;
+      }
+    double real = std::sqrt(sum);
+    if (std::abs(real) < 1e-6) return 1.0;
+    return std::sqrt(expected) / real;
+  }
+};
+}  // namespace
+
+extern "C" void bear_ref_control(int L, int V, int S, double fs, double decorrelation_delay, int front_loudspeaker,
+                                 const float *delays, const float *factors, int view, int N, const float *gains /*[2L][N]*/,
+                                 int M, const float *ds_gains /*[L][M]*/, float *direct_gains /*[L][N]*/,
+                                 float *diffuse_gains /*[L][N]*/, float *direct_delays /*[2N]*/,
+                                 float *ds_gains_out /*[L][M]*/, float *ds_delays /*[2M]*/, float *static_delays /*[2L]*/)
+{
+  ControlTables c{L, V, S, fs, decorrelation_delay, front_loudspeaker, delays, S > 0 ? factors : nullptr};
+  std::vector<double> g(2 * L), tot(L);
+  for (int i = 0; i < N; i++) {
+    for (int l = 0; l < 2 * L; l++) g[l] = (double)gains[(size_t)l * N + i];
+    for (int l = 0; l < L; l++) tot[l] = g[l] + g[L + l];
+    double d[2];
+    c.mean_delays(tot.data(), view, d);
+    direct_delays[2 * i] = (float)d[0];
+    direct_delays[2 * i + 1] = (float)d[1];
+    // GainNorm reads the delays back from the float port (gain_norm.cpp:36-37)
+    double df[2] = {(double)direct_delays[2 * i], (double)direct_delays[2 * i + 1]};
+    double comp = c.compensation_gain(g.data(), df, view);
+    for (int l = 0; l < L; l++) {
+      float gd = (float)(comp * (double)gains[(size_t)l * N + i]);
+      float gq = (float)(comp * (double)gains[(size_t)(L + l) * N + i]);
+      direct_gains[(size_t)l * N + i] = gd;
+      diffuse_gains[(size_t)l * N + i] = gq;
+    }
+  }
+  for (int j = 0; j < M; j++) {
+    for (int l = 0; l < L; l++) g[l] = (double)ds_gains[(size_t)l * M + j];
+    double d[2];
+    c.mean_delays(g.data(), view, d);
+    ds_delays[2 * j] = (float)d[0];
+    ds_delays[2 * j + 1] = (float)d[1];
+    double comp = c.compensation_gain_direct(g.data(), view);
+    for (int l = 0; l < L; l++) ds_gains_out[(size_t)l * M + j] = (float)(comp * (double)ds_gains[(size_t)l * M + j]);
+  }
+  for (int l = 0; l < L; l++)
+    for (int e = 0; e < 2; e++) static_delays[2 * l + e] = (float)(c.delay(view, l, e) / fs);
+}

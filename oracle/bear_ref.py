@@ -47,6 +47,8 @@ def lib(precision="f32"):
         l.bear_ref_delay.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_double, C.c_double,
                                      C.c_int, C.c_int, C.c_void_p]
         l.bear_ref_rfft.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        l.bear_ref_control.argtypes = [C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p,
+                                       C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p] + [C.c_void_p] * 6
         _libs[precision] = l
     return _libs[precision]
 
@@ -151,3 +153,24 @@ def ear_block_convolve(x, taps, period):
     y = np.zeros(len(x), dtype=np.float32)
     l.ear_block_convolve(_ptr(x), len(x), _ptr(taps), len(taps), period, _ptr(y))
     return y
+
+
+def control(data, view, gains, ds_gains=None):
+    """The Control graph's table producers for one period (oracle restatement, bear_ref_control):
+    gains [2L,N] raw object gains (direct rows, then diffuse rows), ds_gains [L,M] -> dict of the DSP
+    port tables of that period."""
+    L, V = data.num_virtual_loudspeakers, data.num_views
+    g = _f32(gains) if gains is not None else np.zeros((2 * L, 0), np.float32)
+    dg = _f32(ds_gains) if ds_gains is not None else np.zeros((L, 0), np.float32)
+    N, M = g.shape[1], dg.shape[1]
+    gn = getattr(data, "gain_norm_factors", None)
+    gn = None if gn is None else _f32(gn)
+    delays = _f32(data.delays)
+    out = {"direct_gains": np.zeros((L, N), np.float32), "diffuse_gains": np.zeros((L, N), np.float32),
+           "direct_delays": np.zeros(2 * N, np.float32), "direct_speakers_gains": np.zeros((L, M), np.float32),
+           "direct_speakers_delays": np.zeros(2 * M, np.float32), "static_delays": np.zeros(2 * L, np.float32)}
+    lib("f32").bear_ref_control(L, V, 0 if gn is None else gn.shape[0], data.fs, data.decorrelation_delay,
+                                data.front_loudspeaker, _ptr(delays), _ptr(gn), int(view), N, _ptr(g), M, _ptr(dg),
+                                *[_ptr(out[k]) for k in ("direct_gains", "diffuse_gains", "direct_delays",
+                                                         "direct_speakers_gains", "direct_speakers_delays", "static_delays")])
+    return out

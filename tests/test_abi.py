@@ -26,7 +26,7 @@ def test_exports_match_header():
 
 def test_struct_sizes():
     assert ctypes.sizeof(renderer.Config) == 17 * 4
-    assert ctypes.sizeof(renderer.Data) == 6 * 4 + 4 * 8 + 3 * 8 + 8
+    assert ctypes.sizeof(renderer.Data) == 6 * 4 + 4 * 8 + 3 * 8 + 8 + 8
     assert ctypes.sizeof(renderer.Tables) == 8 * 8
     assert ctypes.sizeof(renderer.DeviceIO) == 14 * 8
 
