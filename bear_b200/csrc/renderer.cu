@@ -49,6 +49,7 @@ struct bear_cuda_renderer {
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
+  std::vector<std::pair<void *, size_t>> state_allocs;
   uint64_t device_bytes = 0;
   uint64_t launches = 0;
   uint32_t kernels_per_call = 0;
@@ -77,7 +78,10 @@ struct bear_cuda_renderer {
     CK(cudaMalloc(&p, bytes));
     allocs.push_back(p);
     device_bytes += bytes;
-    if (zero) CK(cudaMemsetAsync(p, 0, bytes, stream));
+    if (zero) {
+      CK(cudaMemsetAsync(p, 0, bytes, stream));
+      state_allocs.emplace_back(p, bytes);   // render state: cleared again by bear_cuda_reset
+    }
     return static_cast<T *>(p);
   }
 
@@ -111,6 +115,19 @@ void fill_device(bear_cuda_renderer *r, float *dst, size_t count, float value)
   std::vector<float> h(count, value);
   CK(cudaMemcpyAsync(dst, h.data(), count * sizeof(float), cudaMemcpyHostToDevice, r->stream));
   CK(cudaStreamSynchronize(r->stream));
+}
+
+// Initial state of the DSP graph (dsp.cpp:24-29,41-46,137-144; panner.cpp:172-186): gains 0 (buffers are
+// zeroed), object / DirectSpeakers delays = default direct delay, static delays = default static delay,
+// view 0.
+void set_initial_state(bear_cuda_renderer *r)
+{
+  Layout &p = r->lay;
+  if (p.N) fill_device(r, p.d_dir, 2 * p.N, (float)r->default_direct_delay);
+  if (p.M) fill_device(r, p.d_ds, 2 * p.M, (float)r->default_direct_delay);
+  fill_device(r, p.d_stat, 2 * 2 * p.L, (float)r->default_static_delay);
+  p.fdl_head = 0;
+  r->tables_on_device = false;
 }
 
 bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_data &d)
@@ -287,9 +304,7 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   r->default_static_delay = front / d.fs;
   r->default_direct_delay = (front + d.decorrelation_delay) / d.fs;
   if (front + d.decorrelation_delay + 4 > p.hist) throw Unsupported{"default delay exceeds max_delay_samples"};
-  if (p.N) fill_device(r.get(), p.d_dir, 2 * p.N, (float)r->default_direct_delay);
-  if (p.M) fill_device(r.get(), p.d_ds, 2 * p.M, (float)r->default_direct_delay);
-  fill_device(r.get(), p.d_stat, 2 * 2 * p.L, (float)r->default_static_delay);
+  set_initial_state(r.get());
 
   r->h_in_floats = (size_t)std::max(1, p.N + p.M + p.H) * p.B;
   CK(cudaMallocHost(&r->h_in, r->h_in_floats * sizeof(float)));
@@ -771,6 +786,17 @@ int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T)
     }
     p.ypart = own;
     r->profiling = prof;
+  });
+}
+
+int bear_cuda_reset(bear_cuda_renderer *r)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    CK(cudaStreamSynchronize(r->stream));
+    for (auto &a : r->state_allocs) CK(cudaMemsetAsync(a.first, 0, a.second, r->stream));
+    set_initial_state(r);
+    CK(cudaStreamSynchronize(r->stream));
   });
 }
 

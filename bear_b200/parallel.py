@@ -78,3 +78,16 @@ class ShardedScene:
         partial = self.renderer.render(obj[sl] if n else None, ds if m else None, hoa if h else None, tb)
         partial = np.ascontiguousarray(partial, dtype=np.float32)
         return reduce_partial_mix(partial, self.group)
+
+
+def render_file_batch(renderer, files, rank=0, world=1):
+    """Batch-of-files render (BASELINE configs[4]): rank `rank` renders files rank, rank+world, ... one
+    after the other on ONE renderer instance, resetting its state between files (`Renderer.reset`),
+    so the BRIR spectra are transformed once per process instead of once per file.  `files`: sequence
+    of (objects, direct_speakers, hoa, tables).  Returns {file index: [2, T*B] render}."""
+    out = {}
+    for idx in file_shard(rank, world, len(files)):
+        obj, ds, hoa, tb = files[idx]
+        renderer.reset()
+        out[idx] = renderer.render(obj, ds, hoa, tb)
+    return out

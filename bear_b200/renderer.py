@@ -90,7 +90,7 @@ EXPORTS = (
     "bear_cuda_process_device", "bear_cuda_synchronize", "bear_cuda_get_info",
     "bear_cuda_host_alloc", "bear_cuda_host_free", "bear_cuda_read_data_file_info",
     "bear_cuda_tenf_read_f32", "bear_cuda_set_profiling", "bear_cuda_get_profile",
-    "bear_cuda_process_device_static_scratch", "bear_cuda_control_tables",
+    "bear_cuda_process_device_static_scratch", "bear_cuda_control_tables", "bear_cuda_reset",
 )
 STATIC_SCRATCH_BYTES = 4 << 20
 NUM_KERNELS = 8
@@ -130,6 +130,7 @@ def lib():
         l.bear_cuda_process_device.argtypes = [vp, u32]
         l.bear_cuda_process_device_static_scratch.argtypes = [vp, u32]
         l.bear_cuda_synchronize.argtypes = [vp]
+        l.bear_cuda_reset.argtypes = [vp]
         l.bear_cuda_get_info.argtypes = [vp, C.POINTER(Info)]
         l.bear_cuda_host_alloc.argtypes = [sz]
         l.bear_cuda_host_alloc.restype = vp
@@ -383,6 +384,10 @@ class Renderer:
         """bear_cuda_process_device without any allocation: partial spectra go to the library's
         built-in device array (see include/bear_cuda.h for the limit and the sharing rules)."""
         self._check(self._l.bear_cuda_process_device_static_scratch(self._h, T))
+
+    def reset(self):
+        """Back to the freshly constructed state (bear_cuda_reset): next file of a batch."""
+        self._check(self._l.bear_cuda_reset(self._h))
 
     def synchronize(self):
         self._check(self._l.bear_cuda_synchronize(self._h))

@@ -100,6 +100,12 @@ int bear_cuda_create_from_file(const bear_cuda_config *config, const char *data_
 
 void bear_cuda_destroy(bear_cuda_renderer *r);
 
+/* Put the renderer back into the state of a freshly constructed one (all histories, the frequency-
+ * domain delay line and the carried tables cleared; filter spectra kept), so that one instance can
+ * render a batch of independent files one after the other.  The reference builds a new
+ * bear::Renderer per file (bear/render_cli.py:503-512), which re-transforms all BRIRs each time. */
+int bear_cuda_reset(bear_cuda_renderer *r);
+
 /* Message of the last failure on this renderer (or, with r == NULL, of the last failed create on
  * this thread).  Valid until the next call on the same renderer/thread. */
 const char *bear_cuda_last_error(const bear_cuda_renderer *r);

@@ -158,6 +158,31 @@ def test_single_block_unchanged_ports(oracle, small_data):
     check(out, ref)
 
 
+def test_reset_makes_one_instance_render_a_batch_of_files(oracle, small_data):
+    """BASELINE configs[4] (batch of mixed files): one renderer + reset between files == a fresh
+    renderer per file (what the reference does, bear/render_cli.py:503-512) == the oracle."""
+    from bear_b200 import parallel
+    from bear_b200.renderer import Renderer
+    B, T = 512, 6
+    ctl = control.HostControl(small_data)
+    files = []
+    for f in range(3):
+        N, M, H, tb = control.scenario(ctl, "cfg5_ht", T, B, seed=20 + f)
+        tb["brir_index"] = ((tb["brir_index"] + 5 * f) % small_data.num_views).astype(np.int32)
+        tb["static_delays"] = ctl.static_delays(tb["brir_index"]).astype(np.float32)
+        audio = [control.synth_audio(c, T * B, 1000 * f + s, 0.05) for c, s in ((N, 0), (M, 100), (H, 200))]
+        files.append((*audio, tb))
+    with Renderer(small_data, N, M, H, B, max_batch_blocks=T) as r:
+        got = {}
+        for rank in range(2):                       # two "ranks" share the instance here; files 0,2 then 1
+            got.update(parallel.render_file_batch(r, files, rank, 2))
+    assert sorted(got) == [0, 1, 2]
+    for f, (obj, ds, hoa, tb) in enumerate(files):
+        check(got[f], ref_render(oracle, small_data, N, M, H, B, tb, obj, ds, hoa), "file %d" % f)
+        fresh = gpu_render(small_data, N, M, H, B, tb, obj, ds, hoa, "batch")
+        np.testing.assert_array_equal(got[f], fresh)
+
+
 def test_argument_errors(small_data):
     from bear_b200.renderer import Renderer
     B = 256
