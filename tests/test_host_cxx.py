@@ -11,14 +11,38 @@ from bear_b200 import control, data_file, tensorfile
 from conftest import ROOT
 
 
-@pytest.fixture(scope="module")
-def test_host(tmp_path_factory):
-    exe = tmp_path_factory.mktemp("cxx") / "test_host"
+def _compile(tmp_path_factory, name):
+    exe = tmp_path_factory.mktemp("cxx") / name
     lib_dir = ROOT / "bear_b200"
-    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-I", str(ROOT / "include"),
-                           str(ROOT / "tests" / "cxx" / "test_host.cpp"), "-o", str(exe), "-L", str(lib_dir),
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-Wall", "-Wextra", "-Werror", "-pthread", "-I", str(ROOT / "include"),
+                           str(ROOT / "tests" / "cxx" / (name + ".cpp")), "-o", str(exe), "-L", str(lib_dir),
                            "-lbear_cuda", "-Wl,-rpath," + str(lib_dir)])
     return str(exe)
+
+
+@pytest.fixture(scope="module")
+def test_host(tmp_path_factory):
+    return _compile(tmp_path_factory, "test_host")
+
+
+@pytest.fixture(scope="module")
+def test_dynamic(tmp_path_factory):
+    return _compile(tmp_path_factory, "test_dynamic")
+
+
+def test_wrappers_without_gpu(test_dynamic):
+    """VariableBlockSizeAdapter, BackgroundBuilder, DynamicRenderer (include/bear_b200/dynamic.hpp) around a
+    fake renderer: one-period delay, metadata queueing, builder start/swap/error, fade sequence."""
+    r = subprocess.run([test_dynamic], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip().endswith("OK (0 failures)"), r.stdout + r.stderr
+
+
+@pytest.mark.gpu
+def test_wrappers_on_gpu(test_dynamic, scene_file):
+    """the same wrappers around bear_b200::Renderer: every dynamic period is the static render times n/B,
+    times 1-n/B, zero or unchanged, in a legal order (test_dynamic_renderer.py:253-291)."""
+    r = subprocess.run([test_dynamic, "gpu", scene_file[0]], capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "OK (0 failures)" in r.stdout, r.stdout + r.stderr
 
 
 def test_host_layer_without_gpu(test_host):
