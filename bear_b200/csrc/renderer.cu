@@ -38,7 +38,38 @@ bool mix_hist_too_large(int hist) { return (size_t)kMixChunk * (hist + kMixTile)
 
 }  // namespace
 
+// Everything derived from the data file for one (device, period size): filter spectra, twiddles, the
+// delay and gain-normalisation tables.  Immutable after construction and shared (reference counted)
+// between renderers created with bear_cuda_create_shared, so N instances cost one 212 MB table.
+struct FilterBank {
+  int device = 0, B = 0, logB = 0, V = 0, L = 0, A = 0, P = 0, gnS = 0, front = 0;
+  uint32_t auto_max_delay = 0;
+  double fs = 48000, dec_delay = 0, hoa_delay = 0, default_direct_delay = 0, default_static_delay = 0;
+  const float2 *h_brir = nullptr, *h_dec = nullptr, *h_hoa = nullptr, *tw = nullptr;
+  const float *delays_tab = nullptr, *gn_factors = nullptr;
+  std::vector<void *> allocs;
+  uint64_t bytes = 0;
+  uint64_t launches = 0;
+  template <class T>
+  T *alloc(size_t count)
+  {
+    void *p = nullptr;
+    size_t n = (count * sizeof(T) + 16 + 255) / 256 * 256;
+    cudaError_t e = cudaMalloc(&p, n);
+    if (e != cudaSuccess) throw CudaFail{std::string("cudaMalloc: ") + cudaGetErrorString(e)};
+    allocs.push_back(p);
+    bytes += n;
+    return static_cast<T *>(p);
+  }
+  ~FilterBank()
+  {
+    cudaSetDevice(device);
+    for (void *p : allocs) cudaFree(p);
+  }
+};
+
 struct bear_cuda_renderer {
+  std::shared_ptr<FilterBank> bank;
   bear_cuda_config cfg{};
   Layout lay{};
   int device = 0;
@@ -130,7 +161,7 @@ void set_initial_state(bear_cuda_renderer *r)
   r->tables_on_device = false;
 }
 
-bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_data &d)
+std::shared_ptr<FilterBank> build_bank(const bear_cuda_config &cfg, const bear_cuda_data &d)
 {
   const uint32_t B = cfg.period_size;
   if (B == 0) throw InvalidArgument{"Config: period size must be set"};  // api.cpp:70
@@ -145,8 +176,6 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   if (d.num_views == 0 || d.brir_length == 0) throw InvalidArgument{"empty BRIR table"};
   if (d.front_loudspeaker >= d.num_virtual_loudspeakers)
     throw InvalidArgument{"front_loudspeaker out of range"};
-  if (cfg.gain_ramp_offset > 1 || cfg.delay_ramp_offset > 1 || cfg.xfade_ramp_offset > 1)
-    throw InvalidArgument{"ramp offsets must be 0 or 1"};
 
   int ndev = 0;
   cudaError_t e = cudaGetDeviceCount(&ndev);
@@ -155,37 +184,115 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
                    "); this library has no CPU fallback"};
   if (cfg.device < 0 || cfg.device >= ndev) throw InvalidArgument{"device ordinal out of range"};
 
+  auto bank = std::make_shared<FilterBank>();
+  FilterBank &k = *bank;
+  k.device = cfg.device;
+  CK(cudaSetDevice(k.device));
+  CK(configure_kernels((int)B));
+  k.B = (int)B; k.logB = ilog2(B);
+  k.P = (int)((d.brir_length + B - 1) / B);
+  k.L = (int)d.num_virtual_loudspeakers; k.A = (int)d.num_hoa_decoder_channels; k.V = (int)d.num_views;
+  k.fs = d.fs; k.dec_delay = d.decorrelation_delay; k.hoa_delay = d.hoa_delay; k.front = (int)d.front_loudspeaker;
+  // Longest table delay the data file can produce (panner.cpp:189-235): the largest loudspeaker delay
+  // plus the decorrelation delay, or the HOA delay.
+  float dm = 0.f;
+  for (size_t i = 0; i < (size_t)d.num_views * d.num_virtual_loudspeakers * 2; i++) dm = std::max(dm, d.delays[i]);
+  k.auto_max_delay = (uint32_t)std::ceil(std::max((double)dm + d.decorrelation_delay, d.hoa_delay)) + 4;
+  // initial delays (panner.cpp:172-186)
+  const double front = ((double)d.delays[(0 * k.L + d.front_loudspeaker) * 2 + 0] +
+                        (double)d.delays[(0 * k.L + d.front_loudspeaker) * 2 + 1]) / 2.0;
+  k.default_static_delay = front / d.fs;
+  k.default_direct_delay = (front + d.decorrelation_delay) / d.fs;
+
+  cudaStream_t st = nullptr;
+  CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+  struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } guard{st};
+  {  // twiddles exp(-i pi q / B), computed in double
+    std::vector<float2> tw(B);
+    const double pi = 3.14159265358979323846264338327950288;
+    for (uint32_t q = 0; q < B; q++) tw[q] = make_float2((float)std::cos(pi * q / B), (float)-std::sin(pi * q / B));
+    float2 *dtw = k.alloc<float2>(B);
+    CK(cudaMemcpyAsync(dtw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice, st));
+    CK(cudaStreamSynchronize(st));
+    k.tw = dtw;
+  }
+  {  // data-file delay table and optional gain-normalisation factors (control tail)
+    const size_t nd = (size_t)k.V * k.L * 2;
+    float *dt = k.alloc<float>(nd);
+    CK(cudaMemcpyAsync(dt, d.delays, nd * sizeof(float), cudaMemcpyHostToDevice, st));
+    k.delays_tab = dt;
+    if (d.gain_norm_factors && d.num_gain_norm_delays) {
+      if (d.num_gain_norm_delays < 2) throw InvalidArgument{"gain_norm factors need at least 2 delay samples"};
+      const size_t nf = (size_t)d.num_gain_norm_delays * k.V * 4 * k.L * k.L * 2;
+      float *gf = k.alloc<float>(nf);
+      CK(cudaMemcpyAsync(gf, d.gain_norm_factors, nf * sizeof(float), cudaMemcpyHostToDevice, st));
+      k.gn_factors = gf;
+      k.gnS = (int)d.num_gain_norm_delays;
+    }
+    CK(cudaStreamSynchronize(st));
+  }
+  {  // filter spectra, pre-scaled by 1/(2B)
+    const float scale = 1.0f / (float)(2 * B);
+    auto transform = [&](const float *host, size_t n_filters, int len, int parts) {
+      float *tmp = nullptr;
+      const size_t bytes = n_filters * len * sizeof(float);
+      CK(cudaMalloc(&tmp, bytes));
+      CK(cudaMemcpyAsync(tmp, host, bytes, cudaMemcpyHostToDevice, st));
+      float2 *spec = k.alloc<float2>(n_filters * parts * B);
+      const size_t slice = 16384;   // launch in slices to keep grid sizes moderate
+      for (size_t f0 = 0; f0 < n_filters; f0 += slice) {
+        size_t nf = std::min(slice, n_filters - f0);
+        launch_filter_fft(tmp + f0 * len, (int)nf, len, (int)B, k.logB, parts, k.tw, spec + f0 * parts * B, scale, st);
+        k.launches++;
+      }
+      cudaError_t le = cudaGetLastError();
+      cudaError_t se = cudaStreamSynchronize(st);
+      cudaFree(tmp);
+      CK(le);
+      CK(se);
+      return spec;
+    };
+    k.h_brir = transform(d.brirs, (size_t)k.V * 2 * k.L, (int)d.brir_length, k.P);
+    k.h_dec = transform(d.decorrelation_filters, (size_t)k.L, (int)d.decorrelator_length, 1);
+    k.h_hoa = transform(d.hoa_irs, (size_t)std::max(1, k.A) * 2, (int)d.hoa_ir_length, 1);
+  }
+  return bank;
+}
+
+bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_ptr<FilterBank> bank)
+{
+  const FilterBank &k = *bank;
+  const uint32_t B = cfg.period_size;
+  if ((int)B != k.B) throw InvalidArgument{"period size differs from the shared filter bank's"};
+  if (cfg.device != k.device) throw InvalidArgument{"device differs from the shared filter bank's"};
+  if (cfg.gain_ramp_offset > 1 || cfg.delay_ramp_offset > 1 || cfg.xfade_ramp_offset > 1)
+    throw InvalidArgument{"ramp offsets must be 0 or 1"};
+
   std::unique_ptr<bear_cuda_renderer> r(new bear_cuda_renderer);
+  r->bank = bank;
   r->cfg = cfg;
   r->device = cfg.device;
   CK(cudaSetDevice(r->device));
   CK(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
-  CK(configure_kernels((int)B));
 
   Layout &p = r->lay;
   p.N = cfg.num_objects_channels; p.M = cfg.num_direct_speakers_channels; p.H = cfg.num_hoa_channels;
   p.B = B; p.logB = ilog2(B);
-  p.P = (d.brir_length + B - 1) / B;
-  p.L = d.num_virtual_loudspeakers; p.A = d.num_hoa_decoder_channels;
+  p.P = k.P;
+  p.L = k.L; p.A = k.A;
   p.CH = 2 * p.L + p.A;
-  p.V = d.num_views;
+  p.V = k.V;
   p.Tmax = cfg.max_batch_blocks ? cfg.max_batch_blocks : 1;
-  // Longest table delay the data file can produce (panner.cpp:189-235): the largest loudspeaker delay
-  // plus the decorrelation delay, or the HOA delay.  max_delay_samples == 0 derives it from the file.
-  uint32_t max_delay = cfg.max_delay_samples;
-  if (max_delay == 0) {
-    float dm = 0.f;
-    for (size_t i = 0; i < (size_t)d.num_views * d.num_virtual_loudspeakers * 2; i++) dm = std::max(dm, d.delays[i]);
-    max_delay = (uint32_t)std::ceil(std::max((double)dm + d.decorrelation_delay, d.hoa_delay)) + 4;
-  }
+  // max_delay_samples == 0: the longest table delay the data file can produce
+  const uint32_t max_delay = cfg.max_delay_samples ? cfg.max_delay_samples : k.auto_max_delay;
   p.hist = (int)round_up(max_delay + 8, 4);
   if (mix_hist_too_large(p.hist)) throw Unsupported{"max_delay_samples too large for the mix kernel's shared-memory tile"};
   CK(configure_mix(p.hist, p.B));
   p.goff = cfg.gain_ramp_offset; p.doff = cfg.delay_ramp_offset; p.xoff = cfg.xfade_ramp_offset;
-  p.fs = (float)d.fs;
-  p.hoa_delay = (float)d.hoa_delay;
-  if (d.hoa_delay + 4 > p.hist) throw Unsupported{"hoa delay exceeds max_delay_samples"};
+  p.fs = (float)k.fs;
+  p.hoa_delay = (float)k.hoa_delay;
+  if (k.hoa_delay + 4 > p.hist) throw Unsupported{"hoa delay exceeds max_delay_samples"};
 
   const int C = p.N + p.M;
   {
@@ -236,74 +343,23 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   p.out = r->dalloc<float>(2 * p.os);
   r->audio_out = p.out;
 
-  // control tail: data-file delay table, optional gain-normalisation factors, raw-gain staging
-  {
-    const size_t nd = (size_t)p.V * p.L * 2;
-    float *dt = r->dalloc<float>(nd, false);
-    CK(cudaMemcpyAsync(dt, d.delays, nd * sizeof(float), cudaMemcpyHostToDevice, r->stream));
-    p.delays_tab = dt;
-    p.gn_factors = nullptr;
-    p.gnS = 0;
-    if (d.gain_norm_factors && d.num_gain_norm_delays) {
-      if (d.num_gain_norm_delays < 2) throw InvalidArgument{"gain_norm factors need at least 2 delay samples"};
-      const size_t nf = (size_t)d.num_gain_norm_delays * p.V * 4 * p.L * p.L * 2;
-      float *gf = r->dalloc<float>(nf, false);
-      CK(cudaMemcpyAsync(gf, d.gain_norm_factors, nf * sizeof(float), cudaMemcpyHostToDevice, r->stream));
-      p.gn_factors = gf;
-      p.gnS = (int)d.num_gain_norm_delays;
-    }
-    p.raw_obj = r->dalloc<float>((size_t)p.Tmax * 2 * p.L * std::max(1, p.N));
-    p.raw_ds = r->dalloc<float>((size_t)p.Tmax * p.L * std::max(1, p.M));
-    p.fs_d = d.fs;
-    p.dec_delay_d = d.decorrelation_delay;
-    p.front = (int)d.front_loudspeaker;
-    CK(cudaStreamSynchronize(r->stream));
-  }
+  // control tail: shared tables + this renderer's raw-gain staging
+  p.delays_tab = k.delays_tab;
+  p.gn_factors = k.gn_factors;
+  p.gnS = k.gnS;
+  p.raw_obj = r->dalloc<float>((size_t)p.Tmax * 2 * p.L * std::max(1, p.N));
+  p.raw_ds = r->dalloc<float>((size_t)p.Tmax * p.L * std::max(1, p.M));
+  p.fs_d = k.fs;
+  p.dec_delay_d = k.dec_delay;
+  p.front = k.front;
+  p.tw = k.tw;
+  p.h_brir = k.h_brir;
+  p.h_dec = k.h_dec;
+  p.h_hoa = k.h_hoa;
 
-  // twiddles exp(-i pi q / B), computed in double
-  {
-    std::vector<float2> tw(p.B);
-    const double pi = 3.14159265358979323846264338327950288;
-    for (int q = 0; q < p.B; q++) tw[q] = make_float2((float)std::cos(pi * q / p.B), (float)-std::sin(pi * q / p.B));
-    float2 *dtw = r->dalloc<float2>(p.B, false);
-    CK(cudaMemcpyAsync(dtw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice, r->stream));
-    CK(cudaStreamSynchronize(r->stream));
-    p.tw = dtw;
-  }
-
-  // ---- filter spectra ------------------------------------------------------------------------
-  {
-    const float scale = 1.0f / (float)(2 * p.B);
-    auto transform = [&](const float *host, size_t n_filters, int len, int parts) {
-      float *tmp = nullptr;
-      const size_t bytes = n_filters * len * sizeof(float);
-      CK(cudaMalloc(&tmp, bytes));
-      CK(cudaMemcpyAsync(tmp, host, bytes, cudaMemcpyHostToDevice, r->stream));
-      float2 *spec = r->dalloc<float2>(n_filters * parts * p.B, false);
-      // launch in slices to keep grid sizes moderate
-      const size_t slice = 16384;
-      for (size_t f0 = 0; f0 < n_filters; f0 += slice) {
-        size_t nf = std::min(slice, n_filters - f0);
-        launch_filter_fft(tmp + f0 * len, (int)nf, len, p.B, p.logB, parts, p.tw, spec + f0 * parts * p.B, scale,
-                          r->stream);
-        r->launches++;
-      }
-      CK(cudaGetLastError());
-      CK(cudaStreamSynchronize(r->stream));
-      CK(cudaFree(tmp));
-      return spec;
-    };
-    p.h_brir = transform(d.brirs, (size_t)p.V * 2 * p.L, d.brir_length, p.P);
-    p.h_dec = transform(d.decorrelation_filters, p.L, d.decorrelator_length, 1);
-    p.h_hoa = transform(d.hoa_irs, (size_t)std::max(1, p.A) * 2, d.hoa_ir_length, 1);
-  }
-
-  // ---- initial state (dsp.cpp:24-29,41-46,137-144; panner.cpp:172-186) -------------------------
-  const double front = ((double)d.delays[(0 * p.L + d.front_loudspeaker) * 2 + 0] +
-                        (double)d.delays[(0 * p.L + d.front_loudspeaker) * 2 + 1]) / 2.0;
-  r->default_static_delay = front / d.fs;
-  r->default_direct_delay = (front + d.decorrelation_delay) / d.fs;
-  if (front + d.decorrelation_delay + 4 > p.hist) throw Unsupported{"default delay exceeds max_delay_samples"};
+  r->default_static_delay = k.default_static_delay;
+  r->default_direct_delay = k.default_direct_delay;
+  if (k.default_direct_delay * k.fs + 4 > p.hist) throw Unsupported{"default delay exceeds max_delay_samples"};
   set_initial_state(r.get());
 
   r->h_in_floats = (size_t)std::max(1, p.N + p.M + p.H) * p.B;
@@ -313,6 +369,11 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
 
   r->kernels_per_call = (C > 0) + (p.H > 0) + (p.N > 0) + 4;
   return r.release();
+}
+
+bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_data &d)
+{
+  return create_with_bank(cfg, build_bank(cfg, d));
 }
 
 // Queue the kernels for T blocks whose audio and tables are already in the staging areas.
@@ -543,6 +604,15 @@ int bear_cuda_create(const bear_cuda_config *config, const bear_cuda_data *data,
   return guarded(nullptr, [&] {
     if (!config || !data || !out) throw InvalidArgument{"NULL argument"};
     *out = create_impl(*config, *data);
+  });
+}
+
+int bear_cuda_create_shared(const bear_cuda_config *config, const bear_cuda_renderer *share_with, bear_cuda_renderer **out)
+{
+  if (out) *out = nullptr;
+  return guarded(nullptr, [&] {
+    if (!config || !share_with || !out) throw InvalidArgument{"NULL argument"};
+    *out = create_with_bank(*config, share_with->bank);
   });
 }
 
@@ -816,6 +886,7 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info)
   info->history_samples = r->lay.hist;
   info->kernels_per_call = r->kernels_per_call;
   info->device_bytes = r->device_bytes;
+  info->shared_bytes = r->bank ? r->bank->bytes : 0;
   info->launches_total = r->launches;
   info->default_direct_delay = r->default_direct_delay;
   info->default_static_delay = r->default_static_delay;

@@ -69,7 +69,7 @@ class Info(C.Structure):
         ("num_partitions", C.c_uint32), ("object_splits", C.c_uint32), ("cmac_splits", C.c_uint32),
         ("history_samples", C.c_uint32), ("kernels_per_call", C.c_uint32), ("device_bytes", C.c_uint64),
         ("launches_total", C.c_uint64), ("default_direct_delay", C.c_double),
-        ("default_static_delay", C.c_double),
+        ("default_static_delay", C.c_double), ("shared_bytes", C.c_uint64),
     ]
 
 
@@ -91,6 +91,7 @@ EXPORTS = (
     "bear_cuda_host_alloc", "bear_cuda_host_free", "bear_cuda_read_data_file_info",
     "bear_cuda_tenf_read_f32", "bear_cuda_set_profiling", "bear_cuda_get_profile",
     "bear_cuda_process_device_static_scratch", "bear_cuda_control_tables", "bear_cuda_reset",
+    "bear_cuda_create_shared",
 )
 STATIC_SCRATCH_BYTES = 4 << 20
 NUM_KERNELS = 8
@@ -120,6 +121,7 @@ def lib():
         vp, u32, sz = C.c_void_p, C.c_uint32, C.c_size_t
         l.bear_cuda_create.argtypes = [C.POINTER(Config), C.POINTER(Data), C.POINTER(vp)]
         l.bear_cuda_create_from_file.argtypes = [C.POINTER(Config), C.c_char_p, C.POINTER(vp)]
+        l.bear_cuda_create_shared.argtypes = [C.POINTER(Config), vp, C.POINTER(vp)]
         l.bear_cuda_destroy.argtypes = [vp]
         l.bear_cuda_destroy.restype = None
         l.bear_cuda_last_error.argtypes = [vp]
@@ -208,7 +210,8 @@ class Renderer:
     def __init__(self, data, num_objects=0, num_direct_speakers=0, num_hoa=0, period=0, max_batch_blocks=1,
                  device=0, max_delay_samples=0, object_splits=0, cmac_splits=0, ramp_offsets=(1, 1, 1),
                  sample_rate=48000, chunk_blocks=0):
-        """`data`: path to a BEAR data file, or a bear_b200.data_file.DataFile."""
+        """`data`: path to a BEAR data file, a bear_b200.data_file.DataFile, or another Renderer whose
+        filter spectra and tables are to be shared (bear_cuda_create_shared)."""
         self._l = lib()
         self._h = C.c_void_p()
         cfg = Config()
@@ -217,7 +220,9 @@ class Renderer:
         cfg.max_batch_blocks, cfg.device, cfg.max_delay_samples = max_batch_blocks, device, max_delay_samples
         cfg.object_splits, cfg.cmac_splits, cfg.chunk_blocks = object_splits, cmac_splits, chunk_blocks
         cfg.gain_ramp_offset, cfg.delay_ramp_offset, cfg.xfade_ramp_offset = ramp_offsets
-        if isinstance(data, (str, os.PathLike)):
+        if isinstance(data, Renderer):   # share the filter spectra / data-file tables of an existing renderer
+            rc = self._l.bear_cuda_create_shared(C.byref(cfg), data._h, C.byref(self._h))
+        elif isinstance(data, (str, os.PathLike)):
             rc = self._l.bear_cuda_create_from_file(C.byref(cfg), str(data).encode(), C.byref(self._h))
         else:
             keep = [_as_f32(data.brirs), _as_f32(data.delays), _as_f32(data.decorrelation_filters),

@@ -98,6 +98,14 @@ int bear_cuda_create(const bear_cuda_config *config, const bear_cuda_data *data,
  * (tensorfile.cpp:187-215).  On failure *out is NULL and bear_cuda_last_error(NULL) has the text. */
 int bear_cuda_create_from_file(const bear_cuda_config *config, const char *data_path, bear_cuda_renderer **out);
 
+/* A further renderer that shares the filter spectra and data-file tables of `share_with` (same
+ * device, same period size; channel counts, batch size etc. are free).  The tables are reference
+ * counted and live until the last renderer using them is destroyed.  Construction is then a few
+ * allocations instead of the transform of all V*2L BRIRs -- what DynamicRenderer's background thread
+ * exists to hide in the reference (constructor_thread.cpp) -- and N instances for a batch of files
+ * hold one copy of the 212 MB table. */
+int bear_cuda_create_shared(const bear_cuda_config *config, const bear_cuda_renderer *share_with, bear_cuda_renderer **out);
+
 void bear_cuda_destroy(bear_cuda_renderer *r);
 
 /* Put the renderer back into the state of a freshly constructed one (all histories, the frequency-
@@ -203,9 +211,10 @@ typedef struct bear_cuda_info {
   uint32_t object_splits, cmac_splits;
   uint32_t history_samples;
   uint32_t kernels_per_call;    /* kernel launches one process call issues */
-  uint64_t device_bytes;        /* device memory held by this renderer */
+  uint64_t device_bytes;        /* device memory owned by this renderer (state, staging) */
   uint64_t launches_total;      /* kernels launched since creation */
   double default_direct_delay, default_static_delay; /* seconds, panner.cpp:172-186 */
+  uint64_t shared_bytes;        /* device memory of the (possibly shared) filter spectra and tables */
 } bear_cuda_info;
 
 int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);

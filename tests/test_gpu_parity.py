@@ -183,6 +183,29 @@ def test_reset_makes_one_instance_render_a_batch_of_files(oracle, small_data):
         np.testing.assert_array_equal(got[f], fresh)
 
 
+def test_shared_filter_bank(oracle, small_data):
+    """bear_cuda_create_shared: renderers with different channel counts share one set of spectra; each
+    matches the oracle, and the tables outlive the renderer that built them."""
+    from bear_b200.renderer import Renderer
+    B, T = 256, 6
+    ctl = control.HostControl(small_data)
+    first = Renderer(small_data, 1, 0, 0, B, max_batch_blocks=T)
+    kw, N, M, H = case_tables(ctl, "all_views", T, np.random.default_rng(3))
+    second = Renderer(first, N, M, H, B, max_batch_blocks=T)
+    third = Renderer(second, 0, 3, 0, B, max_batch_blocks=1)
+    assert first.info.shared_bytes == second.info.shared_bytes == third.info.shared_bytes > 0
+    with pytest.raises(ValueError, match="period size differs"):
+        Renderer(first, 1, 0, 0, 2 * B)
+    first.close()                                  # the bank lives on in the other two
+    tb = ctl.tables(T, **kw)
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((N, 0), (M, 100), (H, 200)))
+    check(second.render(obj, ds, hoa, tb), ref_render(oracle, small_data, N, M, H, B, tb, obj, ds, hoa), "second")
+    tb3 = ctl.tables(T, ds_speakers=[2, 5, -1])
+    out3 = np.concatenate([third.process(None, ds[:, k * B:(k + 1) * B], None, tb3.block(k)) for k in range(T)], axis=1)
+    check(out3, ref_render(oracle, small_data, 0, 3, 0, B, tb3, None, ds, None), "third")
+    second.close(); third.close()
+
+
 def test_argument_errors(small_data):
     from bear_b200.renderer import Renderer
     B = 256
