@@ -183,6 +183,39 @@ def test_reset_makes_one_instance_render_a_batch_of_files(oracle, small_data):
         np.testing.assert_array_equal(got[f], fresh)
 
 
+def _odd_data(L, A, brir_length, num_views=5):
+    """data file with fewer loudspeakers / a lower-order HOA decoder than default.tf"""
+    tree = data_file.synthetic_tree(seed=7, num_views=num_views, brir_length=brir_length)
+    tree["brirs"] = tree["brirs"][:, :L]
+    tree["delays"] = tree["delays"][:, :L]
+    tree["decorrelation_filters"] = tree["decorrelation_filters"][:L]
+    tree["layout"] = dict(tree["layout"], channels=tree["layout"]["channels"][:L])
+    tree["hoa"] = dict(tree["hoa"], irs=tree["hoa"]["irs"][:A])
+    return data_file.from_tree(tree)
+
+
+@pytest.mark.parametrize("L,A,brir_length,B,N,M,H", [
+    (10, 4, 100, 128, 3, 2, 4),      # single partition, first-order decoder, 10 loudspeakers
+    (7, 9, 1500, 1024, 33, 1, 9),    # odd loudspeaker count (gain rows not a multiple of 4), P = 2
+    (24, 16, 2976, 4096, 2, 0, 1),   # largest period, P = 1
+    (3, 1, 700, 256, 1, 5, 1),       # tiny layout, order-0 decoder
+])
+def test_unusual_shapes(oracle, L, A, brir_length, B, N, M, H):
+    data = _odd_data(L, A, brir_length)
+    ctl = control.HostControl(data)
+    T = max(4, 2048 // B)
+    rng = np.random.default_rng(L * 100 + A)
+    ds_spk = [int(rng.integers(-1, L)) for _ in range(M)]
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, N)), obj_diffuse=rng.uniform(0, 1, size=N),
+                    obj_gain=1.0 / np.sqrt(max(N, 1)), ds_speakers=ds_spk, hoa_gains=0.3 * rng.standard_normal((A, H)), H=H,
+                    yaw_deg=72.0 * np.arange(T))
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((N, 0), (M, 100), (H, 200)))
+    ref = ref_render(oracle, data, N, M, H, B, tb, obj, ds, hoa)
+    assert np.abs(ref).max() > 0.02
+    for mode in ("batch", "stream"):
+        check(gpu_render(data, N, M, H, B, tb, obj, ds, hoa, mode), ref, "L=%d A=%d B=%d %s" % (L, A, B, mode))
+
+
 def test_shared_filter_bank(oracle, small_data):
     """bear_cuda_create_shared: renderers with different channel counts share one set of spectra; each
     matches the oracle, and the tables outlive the renderer that built them."""
