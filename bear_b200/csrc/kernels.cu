@@ -328,39 +328,52 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
     asm volatile("cp.async.wait_group 0;");
     __syncthreads();
     const float dmax = (float)(p.hist - 4);
-    for (int ii = 0; ii < cnt; ii++) {
-      const float *xr = xt + ii * XW + p.hist + tid;
-      const unsigned md = smask[ii][0], mq = smask[ii][1];
-      if ((md | mq) == 0u) continue;   // silent channel in this period
-      const float4 *g0v = reinterpret_cast<const float4 *>(sg[ii]);
-      const float4 *dgv = g0v + kMaxSpeakers / 4;
-      const float4 *q0v = g0v + 2 * kMaxSpeakers / 4;
-      const float4 *dqv = g0v + 3 * kMaxSpeakers / 4;
-      if (md) {
-        const float xl = delayed_read(xr, fminf(ramped_delay(sd[ii][0], sd[ii][1], rd), dmax));
-        const float xR = delayed_read(xr, fminf(ramped_delay(sd[ii][2], sd[ii][3], rd), dmax));
+    // Channels are taken two at a time: both channels' fractional-delay gathers (two independent
+    // dependency chains per ear) are issued before either channel's accumulation, which gives the
+    // scheduler work to overlap at the low occupancy the 72 accumulators allow.
+    for (int ii = 0; ii < cnt; ii += 2) {
+      float xl2[2], xR2[2], x02[2];
 #pragma unroll
-        for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
-          if (md & (1u << l4)) {
-            const float4 g0 = g0v[l4], dg = dgv[l4];
-            float g;
-            g = fmaf(rg, dg.x, g0.x); accL[4 * l4 + 0] = fmaf(g, xl, accL[4 * l4 + 0]); accR[4 * l4 + 0] = fmaf(g, xR, accR[4 * l4 + 0]);
-            g = fmaf(rg, dg.y, g0.y); accL[4 * l4 + 1] = fmaf(g, xl, accL[4 * l4 + 1]); accR[4 * l4 + 1] = fmaf(g, xR, accR[4 * l4 + 1]);
-            g = fmaf(rg, dg.z, g0.z); accL[4 * l4 + 2] = fmaf(g, xl, accL[4 * l4 + 2]); accR[4 * l4 + 2] = fmaf(g, xR, accR[4 * l4 + 2]);
-            g = fmaf(rg, dg.w, g0.w); accL[4 * l4 + 3] = fmaf(g, xl, accL[4 * l4 + 3]); accR[4 * l4 + 3] = fmaf(g, xR, accR[4 * l4 + 3]);
+      for (int u = 0; u < 2; u++) {
+        const int j = min(ii + u, cnt - 1);
+        const float *xr = xt + j * XW + p.hist + tid;
+        xl2[u] = delayed_read(xr, fminf(ramped_delay(sd[j][0], sd[j][1], rd), dmax));
+        xR2[u] = delayed_read(xr, fminf(ramped_delay(sd[j][2], sd[j][3], rd), dmax));
+        x02[u] = xr[0];
+      }
+#pragma unroll
+      for (int u = 0; u < 2; u++) {
+        const int j = ii + u;
+        if (j >= cnt) break;
+        const unsigned md = smask[j][0], mq = smask[j][1];
+        const float4 *g0v = reinterpret_cast<const float4 *>(sg[j]);
+        const float4 *dgv = g0v + kMaxSpeakers / 4;
+        const float4 *q0v = g0v + 2 * kMaxSpeakers / 4;
+        const float4 *dqv = g0v + 3 * kMaxSpeakers / 4;
+        const float xl = xl2[u], xR = xR2[u], x0 = x02[u];
+        if (md) {
+#pragma unroll
+          for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
+            if (md & (1u << l4)) {
+              const float4 g0 = g0v[l4], dg = dgv[l4];
+              float g;
+              g = fmaf(rg, dg.x, g0.x); accL[4 * l4 + 0] = fmaf(g, xl, accL[4 * l4 + 0]); accR[4 * l4 + 0] = fmaf(g, xR, accR[4 * l4 + 0]);
+              g = fmaf(rg, dg.y, g0.y); accL[4 * l4 + 1] = fmaf(g, xl, accL[4 * l4 + 1]); accR[4 * l4 + 1] = fmaf(g, xR, accR[4 * l4 + 1]);
+              g = fmaf(rg, dg.z, g0.z); accL[4 * l4 + 2] = fmaf(g, xl, accL[4 * l4 + 2]); accR[4 * l4 + 2] = fmaf(g, xR, accR[4 * l4 + 2]);
+              g = fmaf(rg, dg.w, g0.w); accL[4 * l4 + 3] = fmaf(g, xl, accL[4 * l4 + 3]); accR[4 * l4 + 3] = fmaf(g, xR, accR[4 * l4 + 3]);
+            }
           }
         }
-      }
-      if (mq) {
-        const float x0 = xr[0];
+        if (mq) {
 #pragma unroll
-        for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
-          if (mq & (1u << l4)) {
-            const float4 q0 = q0v[l4], dq = dqv[l4];
-            accQ[4 * l4 + 0] = fmaf(fmaf(rg, dq.x, q0.x), x0, accQ[4 * l4 + 0]);
-            accQ[4 * l4 + 1] = fmaf(fmaf(rg, dq.y, q0.y), x0, accQ[4 * l4 + 1]);
-            accQ[4 * l4 + 2] = fmaf(fmaf(rg, dq.z, q0.z), x0, accQ[4 * l4 + 2]);
-            accQ[4 * l4 + 3] = fmaf(fmaf(rg, dq.w, q0.w), x0, accQ[4 * l4 + 3]);
+          for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
+            if (mq & (1u << l4)) {
+              const float4 q0 = q0v[l4], dq = dqv[l4];
+              accQ[4 * l4 + 0] = fmaf(fmaf(rg, dq.x, q0.x), x0, accQ[4 * l4 + 0]);
+              accQ[4 * l4 + 1] = fmaf(fmaf(rg, dq.y, q0.y), x0, accQ[4 * l4 + 1]);
+              accQ[4 * l4 + 2] = fmaf(fmaf(rg, dq.z, q0.z), x0, accQ[4 * l4 + 2]);
+              accQ[4 * l4 + 3] = fmaf(fmaf(rg, dq.w, q0.w), x0, accQ[4 * l4 + 3]);
+            }
           }
         }
       }
@@ -485,7 +498,7 @@ void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
 // fractional-delay gathers read are first staged in shared memory with 16-byte cp.async copies.
 // grid: T * (L + ceil(A/2)) (unit fastest); block: 2 * B/8.
 // ----------------------------------------------------------------------------------------------
-__global__ void bus_fdl_kernel(Layout p, int T, int nunits)
+__global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
 {
   extern __shared__ __align__(16) float2 sm[];
   const int M = p.B;
@@ -496,6 +509,7 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits)
   float2 *a = sm + (size_t)g * 2 * FB, *b = a + FB;
   const int RW = p.hist + 2 * M;                                     // staged row: history + window
   float *rows = reinterpret_cast<float *>(sm + 4 * FB);              // [2][RW]
+  float *cwin = rows + 2 * RW;                                       // [2][2M] direct-bus windows (S == 1)
   const float invB = 1.0f / (float)p.B;
   const int L2 = 2 * p.L;
   const bool bus = unit < p.L;
@@ -515,8 +529,19 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits)
       asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
     }
     asm volatile("cp.async.commit_group;");
-    asm volatile("cp.async.wait_group 0;");
   }
+  const bool cstaged = bus && stage_direct;
+  if (cstaged) {   // both ears' direct-bus windows [block k-1 | block k]
+    const int vec = (2 * M) >> 2;
+    for (int idx = threadIdx.x; idx < 2 * vec; idx += blockDim.x) {
+      const int r = idx / vec, v = idx - r * vec;
+      const float *src = p.cdir + (size_t)(2 * unit + r) * p.cs + (size_t)k * p.B + 4 * v;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(cwin + r * 2 * M + 4 * v);
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
+    }
+    asm volatile("cp.async.commit_group;");
+  }
+  asm volatile("cp.async.wait_group 0;");
   __syncthreads();
 
   if (active) {
@@ -529,11 +554,16 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits)
         const float t1 = p.d_stat[(size_t)(k + h + 1) * L2 + ch] * p.fs;
         d0[h] = t0; dd[h] = t1 - t0;
       }
+      const float2 *cw = reinterpret_cast<const float2 *>(cwin + g * 2 * M);
       for (int n = tid; n < M; n += nthr) {
         float2 v = make_float2(0.f, 0.f);
-        for (int s = 0; s < p.S; s++) {
-          const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
-          v.x += c.x; v.y += c.y;
+        if (cstaged) {
+          v = cw[n];
+        } else {
+          for (int s = 0; s < p.S; s++) {
+            const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
+            v.x += c.x; v.y += c.y;
+          }
         }
         if (dif) {
           const int t = 2 * n;            // window sample, both of the pair lie in the same block
@@ -566,16 +596,25 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits)
   }
 }
 
-static size_t bus_fdl_smem_bytes(int B, int hist)
+// shared memory of bus_fdl_kernel; the direct-bus windows are staged only when there is a single
+// partial (S == 1) and everything still fits (it does up to B = 2048)
+static bool bus_fdl_stage_direct(int B, int hist, int S)
 {
-  return (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float);
+  const size_t base = (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float);
+  return S == 1 && base + (size_t)2 * 2 * B * sizeof(float) <= 200 * 1024;
+}
+static size_t bus_fdl_smem_bytes(int B, int hist, int S)
+{
+  return (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float) +
+         (bus_fdl_stage_direct(B, hist, S) ? (size_t)2 * 2 * B * sizeof(float) : 0);
 }
 
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
 {
   int threads = 2 * (p.B / 8 < 32 ? 32 : p.B / 8);
   int nunits = p.L + (p.H > 0 ? (p.A + 1) / 2 : 0);
-  bus_fdl_kernel<<<T * nunits, threads, bus_fdl_smem_bytes(p.B, p.hist), st>>>(p, T, nunits);
+  bus_fdl_kernel<<<T * nunits, threads, bus_fdl_smem_bytes(p.B, p.hist, p.S), st>>>(p, T, nunits,
+                                                                                    bus_fdl_stage_direct(p.B, p.hist, p.S) ? 1 : 0);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -927,7 +966,7 @@ cudaError_t configure_mix(int hist, int B)
   cudaError_t e = cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
   if (e != cudaSuccess) return e;
   return cudaFuncSetAttribute(bus_fdl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)bus_fdl_smem_bytes(B, hist));
+                              (int)bus_fdl_smem_bytes(B, hist, 1));
 }
 
 cudaError_t configure_kernels(int B)

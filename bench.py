@@ -307,6 +307,35 @@ def run_ours(args, rank, world, local_rank):
                 rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
             stream_ms = (time.perf_counter() - t0) / 200 * 1e3
 
+    # ---- the "1000 objects in real time" target: 1024 moving objects, period 256 (BASELINE configs[3]
+    # shape on ONE GPU), 2 s of audio per launch, device-resident, same timing method ----
+    many = None
+    if rank == 0 and world == 1 and args.workload == "cfg2_ht":
+        from bear_b200 import control as _control
+        B4, T4 = 256, 376
+        N4, _, _, tb4 = _control.scenario(ctl, "cfg4_ht", T4, B4, seed=77)
+        audio4 = _control.synth_audio(N4, T4 * B4, seed_base=500000, scale=0.02)
+        with Renderer(data, N4, 0, 0, B4, max_batch_blocks=T4, device=local_rank) as r4:
+            io4 = device_io.DeviceBuffers(r4, device_index=local_rank)
+            io4.load_audio(audio4)
+            io4.load_tables(tb4)
+            r4.synchronize()
+            for _ in range(5):
+                r4.process_device(T4)
+            r4.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(io4.stream)
+            for _ in range(10):
+                r4.process_device(T4)
+            e1.record(io4.stream)
+            e1.synchronize()
+            ms4 = e0.elapsed_time(e1) / 10
+        rtf4 = (T4 * B4 / FS) / (ms4 * 1e-3)
+        many = {"objects": N4, "period": B4, "periods_per_launch": T4, "ms_per_launch": ms4, "rtf": rtf4,
+                "object_channels_x_rtf": N4 * rtf4,
+                "note": "1024 moving objects with per-period metadata and a view change every period on one GPU"}
+        del audio4, tb4
+
     # ---- control tail on the device (delays + gain normalisation + split), kernel time only ----
     control_ms = None
     if rank == 0:
@@ -381,6 +410,7 @@ def run_ours(args, rank, world, local_rank):
                     "api": "bear_cuda_process_batch (pinned host buffers)" if world == 1 else
                            "bear_cuda_process_batch (pinned host buffers) -> NCCL all-reduce of the partial mixes -> pinned host"},
             "gpu_launches": int(launches),
+            "many_objects": many,
             "control_tail": control_ms,
             "stream": {"ms_per_period_call": stream_ms, "period_ms": 1e3 * B / FS,
                        "note": "bear_cuda_process, one period per call incl. host<->device copies and sync (real-time use)"},
