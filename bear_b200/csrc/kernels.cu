@@ -801,6 +801,31 @@ __global__ void __launch_bounds__(256) carry_kernel(CarryPlan plan)
   }
 }
 
+// ----------------------------------------------------------------------------------------------
+// unpack_kernel: the single-period host path uploads audio and tables as ONE packed buffer; this
+// scatters the audio rows into the staging rows and copies each table into its "current period"
+// slot (or repeats the previous period's values for ports that did not change).
+// grid: 32; block 256.
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) unpack_kernel(Layout p, UnpackPlan plan)
+{
+  const int stride = gridDim.x * blockDim.x, g = blockIdx.x * blockDim.x + threadIdx.x;
+  const int na = plan.rows * p.B;
+  for (int i = g; i < na; i += stride) {
+    const int row = i / p.B, col = i - row * p.B;
+    p.xin[(size_t)row * p.xs + p.hist + col] = plan.audio[i];
+  }
+  for (int it = 0; it < plan.n; it++) {
+    const UnpackItem u = plan.item[it];
+    for (int i = g; i < u.count; i += stride) u.dst[i] = u.src[i];
+  }
+}
+
+void launch_unpack(const Layout &p, const UnpackPlan &plan, cudaStream_t st)
+{
+  unpack_kernel<<<32, 256, 0, st>>>(p, plan);
+}
+
 void launch_carry(const CarryPlan &plan, cudaStream_t st)
 {
   carry_kernel<<<plan.row_start[plan.n], 256, 0, st>>>(plan);

@@ -86,6 +86,12 @@ void launch_bus_fdl(const Layout &p, int T, cudaStream_t st);
 void launch_cmac(const Layout &p, int T, cudaStream_t st);
 void launch_ifft_out(const Layout &p, int T, cudaStream_t st);
 void launch_carry(const CarryPlan &plan, cudaStream_t st);
+
+// single-period host path: one packed upload (audio + tables), scattered on the device
+struct UnpackItem { const float *src; float *dst; int count; };
+constexpr int kMaxUnpack = 10;
+struct UnpackPlan { UnpackItem item[kMaxUnpack]; int n; const float *audio; int rows; };
+void launch_unpack(const Layout &p, const UnpackPlan &plan, cudaStream_t st);
 void launch_control(const Layout &p, int T, cudaStream_t st);
 cudaError_t configure_kernels(int B);
 cudaError_t configure_mix(int hist, int B);

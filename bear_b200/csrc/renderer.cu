@@ -97,8 +97,9 @@ struct bear_cuda_renderer {
 
   // staging (device) for the T blocks of the current call: slot 1 of each table
   float *audio_out = nullptr;
-  // pinned host staging for the single-block API
-  float *h_in = nullptr, *h_out = nullptr;
+  // pinned host staging for the single-block API: one packed buffer [audio | tables] and its
+  // device mirror, so that a period costs one upload
+  float *h_in = nullptr, *h_out = nullptr, *d_pack = nullptr;
   size_t h_in_floats = 0;
 
   template <class T>
@@ -362,8 +363,10 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   if (k.default_direct_delay * k.fs + 4 > p.hist) throw Unsupported{"default delay exceeds max_delay_samples"};
   set_initial_state(r.get());
 
-  r->h_in_floats = (size_t)std::max(1, p.N + p.M + p.H) * p.B;
+  r->h_in_floats = (size_t)std::max(1, p.N + p.M + p.H) * p.B + (size_t)2 * p.L * p.N + 2 * p.N + (size_t)p.L * p.M +
+                   2 * p.M + 2 * p.L + (size_t)p.A * p.H + 8;
   CK(cudaMallocHost(&r->h_in, r->h_in_floats * sizeof(float)));
+  r->d_pack = r->dalloc<float>(r->h_in_floats);
   CK(cudaMallocHost(&r->h_out, 2 * (size_t)p.B * sizeof(float)));
   CK(cudaStreamSynchronize(r->stream));
 
@@ -745,10 +748,42 @@ int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
     gather(objects_input, p.N, "objects");
     gather(direct_speakers_input, p.M, "direct_speakers");
     gather(hoa_input, p.H, "hoa");
-    if (row)
-      CK(cudaMemcpy2DAsync(p.xin + p.hist, p.xs * sizeof(float), r->h_in, B * sizeof(float), B * sizeof(float), row,
-                           cudaMemcpyHostToDevice, r->stream));
-    upload_tables(r, 1, tables, true, r->stream);
+    // tables: packed behind the audio; a port that did not change repeats the previous period's slot
+    UnpackPlan plan{};
+    plan.audio = r->d_pack;
+    plan.rows = row;
+    size_t off = (size_t)row * B;
+    auto item = [&](const float *host, float *dev, size_t per_block, size_t slot, const char *name) {
+      if (per_block == 0) return;
+      float *dst = dev + slot * per_block;
+      UnpackItem u{dst - per_block, dst, (int)per_block};      // default: unchanged
+      if (host) {
+        std::memcpy(r->h_in + off, host, per_block * sizeof(float));
+        u.src = r->d_pack + off;
+        off += per_block;
+      }
+      (void)name;
+      plan.item[plan.n++] = u;
+    };
+    if (tables) {
+      item(tables->direct_gains, p.g_dir, (size_t)p.L * p.N, 1, "direct_gains");
+      item(tables->diffuse_gains, p.g_dif, (size_t)p.L * p.N, 1, "diffuse_gains");
+      item(tables->direct_delays, p.d_dir, (size_t)2 * p.N, 1, "direct_delays");
+      item(tables->direct_speakers_gains, p.g_ds, (size_t)p.L * p.M, 1, "direct_speakers_gains");
+      item(tables->direct_speakers_delays, p.d_ds, (size_t)2 * p.M, 1, "direct_speakers_delays");
+      item(tables->static_delays, p.d_stat, (size_t)2 * p.L, 2, nullptr);
+      item(tables->hoa_gains, p.g_hoa, (size_t)p.A * p.H, 1, nullptr);
+      const bool have_view = tables->brir_index && tables->brir_index[0] >= 0;
+      if (have_view && tables->brir_index[0] >= p.V) throw InvalidArgument{"brir_index out of range"};
+      item(have_view ? reinterpret_cast<const float *>(tables->brir_index) : nullptr, reinterpret_cast<float *>(p.view), 1, 1,
+           nullptr);
+    } else {
+      if (!r->tables_on_device) throw InvalidArgument{"tables must not be NULL (no bear_cuda_control_tables call pending)"};
+      r->tables_on_device = false;
+    }
+    if (off) CK(cudaMemcpyAsync(r->d_pack, r->h_in, off * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+    launch_unpack(p, plan, r->stream);
+    r->launches++;
     run_pipeline(r, 1);
     CK(cudaMemcpy2DAsync(r->h_out, B * sizeof(float), p.out, p.os * sizeof(float), B * sizeof(float), 2,
                          cudaMemcpyDeviceToHost, r->stream));

@@ -295,6 +295,7 @@ def run_ours(args, rank, world, local_rank):
 
     # ---- real-time use: one period per call through bear_cuda_process (host pointers), wall clock ----
     stream_ms = None
+    stream_kernels = None
     if rank == 0:
         with Renderer(data, N, 0, 0, B, max_batch_blocks=1, device=local_rank) as rs:
             blk = [tb.block(k) for k in range(8)]
@@ -306,6 +307,10 @@ def run_ours(args, rank, world, local_rank):
             for k in range(200):
                 rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
             stream_ms = (time.perf_counter() - t0) / 200 * 1e3
+            rs.set_profiling(True)
+            for k in range(50):
+                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
+            stream_kernels = {kk: v[0] / max(v[1], 1) for kk, v in rs.get_profile().items() if v[1]}
 
     # ---- the "1000 objects in real time" target: 1024 moving objects, period 256 (BASELINE configs[3]
     # shape on ONE GPU), 2 s of audio per launch, device-resident, same timing method ----
@@ -413,6 +418,7 @@ def run_ours(args, rank, world, local_rank):
             "many_objects": many,
             "control_tail": control_ms,
             "stream": {"ms_per_period_call": stream_ms, "period_ms": 1e3 * B / FS,
+                       "kernel_ms_per_period": stream_kernels if rank == 0 else None,
                        "note": "bear_cuda_process, one period per call incl. host<->device copies and sync (real-time use)"},
             "clocks": clk,
         }
