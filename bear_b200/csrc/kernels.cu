@@ -243,10 +243,31 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 // registers; the gains of kMixChunk channels are staged in shared memory with their per-block
 // deltas so the inner loop is one FMA for the ramped gain + one FMA per ear.
 // ----------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
+// Two FP32 lanes in one 64-bit register: fma.rn.f32x2 (SASS FFMA2) does two IEEE fused multiply-adds
+// per issued instruction -- bit-identical to two fmaf() -- which halves the issue slots of the
+// accumulation (a scalar second operand is broadcast by the hardware).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
 {
-  // row = one channel: [g0 | dg | q0 | dq] x 24 speakers, padded by 4 floats so that the staging
-  // stores (consecutive channels, same speaker) spread over 8 banks instead of 1
+  f32x2 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
+{
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+
+__global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
+{
+  // row = one channel: [g0 | dg | q0 | dq] x 24 speakers, padded by 4 floats so that accesses to
+  // consecutive channels at the same speaker spread over 8 banks instead of 1
   __shared__ __align__(16) float sg[kMixChunk][4 * kMaxSpeakers + 4];
   __shared__ float sd[kMixChunk][4];
   // bit g of smask[ii][0/1]: some direct / diffuse gain of speakers 4g..4g+3 is non-zero in this
@@ -270,47 +291,57 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
   const float rg = (float)(n + p.goff) * invB;
   const float rd = (float)(n + p.doff) * invB;
   const int L = p.L;
+  const f32x2 rg2 = pack2(rg, rg);
 
-  float accL[kMaxSpeakers], accR[kMaxSpeakers], accQ[kMaxSpeakers];
+  f32x2 accL[kMaxSpeakers / 2], accR[kMaxSpeakers / 2], accQ[kMaxSpeakers / 2];
 #pragma unroll
-  for (int l = 0; l < kMaxSpeakers; l++) accL[l] = accR[l] = accQ[l] = 0.0f;
+  for (int l = 0; l < kMaxSpeakers / 2; l++) accL[l] = accR[l] = accQ[l] = 0ull;
 
   for (int cb = c0; cb < c1; cb += kMixChunk) {
     const int cnt = min(kMixChunk, c1 - cb);
     __syncthreads();
     if (tid < 2 * kMixChunk) smask[tid >> 1][tid & 1] = 0u;
     {
+      // warp w copies rows w, w+4, ...: 16-byte pieces, consecutive lanes consecutive pieces
       const int vec_per_row = XW >> 2;
       const float *src0 = p.xin + (size_t)cb * p.xs + (t - tid);   // column (hist + t0) - hist
-      for (int idx = tid; idx < cnt * vec_per_row; idx += kMixTile) {
-        const int row = idx / vec_per_row, v = idx - row * vec_per_row;
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(xt + row * XW + 4 * v);
-        const float *src = src0 + (size_t)row * p.xs + 4 * v;
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
+      for (int row = tid >> 5; row < cnt; row += kMixTile / 32) {
+        const float *src = src0 + (size_t)row * p.xs;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(xt + row * XW);
+        for (int v = tid & 31; v < vec_per_row; v += 32)
+          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
       }
-      asm volatile("cp.async.commit_group;");
     }
-    __syncthreads();
-    for (int idx = tid; idx < cnt * kMaxSpeakers; idx += kMixTile) {
-      const int l = idx / cnt, ii = idx - l * cnt, c = cb + ii;
-      float g0 = 0.f, g1 = 0.f, q0 = 0.f, q1 = 0.f;
-      if (l < L) {
-        if (c < p.N) {
-          g0 = p.g_dir[((size_t)k * L + l) * p.N + c];
-          g1 = p.g_dir[((size_t)(k + 1) * L + l) * p.N + c];
-          q0 = p.g_dif[((size_t)k * L + l) * p.N + c];
-          q1 = p.g_dif[((size_t)(k + 1) * L + l) * p.N + c];
+    // gain tables of periods k-1 (slot k) and k (slot k+1) straight into the rows of sg with 4-byte
+    // cp.async (consecutive threads consecutive channels: coalesced reads); deltas are formed below
+#pragma unroll
+    for (int it = 0; it < kMixChunk * kMaxSpeakers / kMixTile; it++) {
+      const int idx = it * kMixTile + tid;
+      const int l = idx / kMixChunk, ii = idx % kMixChunk, c = cb + ii;
+      if (ii < cnt) {
+        float *row = sg[ii];
+        if (l < L) {
+          const float *a0, *a1;
+          if (c < p.N) {
+            a0 = p.g_dir + ((size_t)k * L + l) * p.N + c;
+            a1 = a0 + (size_t)L * p.N;
+            const float *b0 = p.g_dif + ((size_t)k * L + l) * p.N + c;
+            const float *b1 = b0 + (size_t)L * p.N;
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + 2 * kMaxSpeakers + l)), "l"(b0));
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + 3 * kMaxSpeakers + l)), "l"(b1));
+          } else {
+            a0 = p.g_ds + ((size_t)k * L + l) * p.M + (c - p.N);
+            a1 = a0 + (size_t)L * p.M;
+            row[2 * kMaxSpeakers + l] = 0.f; row[3 * kMaxSpeakers + l] = 0.f;
+          }
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + l)), "l"(a0));
+          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + kMaxSpeakers + l)), "l"(a1));
         } else {
-          const int j = c - p.N;
-          g0 = p.g_ds[((size_t)k * L + l) * p.M + j];
-          g1 = p.g_ds[((size_t)(k + 1) * L + l) * p.M + j];
+          row[l] = 0.f; row[kMaxSpeakers + l] = 0.f; row[2 * kMaxSpeakers + l] = 0.f; row[3 * kMaxSpeakers + l] = 0.f;
         }
       }
-      sg[ii][l] = g0; sg[ii][kMaxSpeakers + l] = g1 - g0;
-      sg[ii][2 * kMaxSpeakers + l] = q0; sg[ii][3 * kMaxSpeakers + l] = q1 - q0;
-      if (g0 != 0.f || g1 != 0.f) atomicOr(&smask[ii][0], 1u << (l >> 2));
-      if (q0 != 0.f || q1 != 0.f) atomicOr(&smask[ii][1], 1u << (l >> 2));
     }
+    asm volatile("cp.async.commit_group;");
     for (int idx = tid; idx < cnt * 2; idx += kMixTile) {
       const int ii = idx >> 1, e = idx & 1, c = cb + ii;
       float d0, d1;
@@ -326,6 +357,17 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
       sd[ii][2 * e] = d0; sd[ii][2 * e + 1] = d1 - d0;
     }
     asm volatile("cp.async.wait_group 0;");
+    __syncthreads();
+    // deltas and sparsity masks; consecutive threads consecutive speakers of one channel (conflict-free)
+    for (int idx = tid; idx < cnt * kMaxSpeakers; idx += kMixTile) {
+      const int ii = idx / kMaxSpeakers, l = idx - ii * kMaxSpeakers;
+      float *row = sg[ii];
+      const float g0 = row[l], g1 = row[kMaxSpeakers + l], q0 = row[2 * kMaxSpeakers + l], q1 = row[3 * kMaxSpeakers + l];
+      row[kMaxSpeakers + l] = g1 - g0;
+      row[3 * kMaxSpeakers + l] = q1 - q0;
+      if (g0 != 0.f || g1 != 0.f) atomicOr(&smask[ii][0], 1u << (l >> 2));
+      if (q0 != 0.f || q1 != 0.f) atomicOr(&smask[ii][1], 1u << (l >> 2));
+    }
     __syncthreads();
     const float dmax = (float)(p.hist - 4);
     // Channels are taken two at a time: both channels' fractional-delay gathers (two independent
@@ -346,21 +388,19 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
         const int j = ii + u;
         if (j >= cnt) break;
         const unsigned md = smask[j][0], mq = smask[j][1];
-        const float4 *g0v = reinterpret_cast<const float4 *>(sg[j]);
-        const float4 *dgv = g0v + kMaxSpeakers / 4;
-        const float4 *q0v = g0v + 2 * kMaxSpeakers / 4;
-        const float4 *dqv = g0v + 3 * kMaxSpeakers / 4;
-        const float xl = xl2[u], xR = xR2[u], x0 = x02[u];
+        const ulonglong2 *g0v = reinterpret_cast<const ulonglong2 *>(sg[j]);
+        const ulonglong2 *dgv = g0v + kMaxSpeakers / 4;
+        const ulonglong2 *q0v = g0v + 2 * kMaxSpeakers / 4;
+        const ulonglong2 *dqv = g0v + 3 * kMaxSpeakers / 4;
+        const f32x2 xl = pack2(xl2[u], xl2[u]), xR = pack2(xR2[u], xR2[u]), x0 = pack2(x02[u], x02[u]);
         if (md) {
 #pragma unroll
           for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
             if (md & (1u << l4)) {
-              const float4 g0 = g0v[l4], dg = dgv[l4];
-              float g;
-              g = fmaf(rg, dg.x, g0.x); accL[4 * l4 + 0] = fmaf(g, xl, accL[4 * l4 + 0]); accR[4 * l4 + 0] = fmaf(g, xR, accR[4 * l4 + 0]);
-              g = fmaf(rg, dg.y, g0.y); accL[4 * l4 + 1] = fmaf(g, xl, accL[4 * l4 + 1]); accR[4 * l4 + 1] = fmaf(g, xR, accR[4 * l4 + 1]);
-              g = fmaf(rg, dg.z, g0.z); accL[4 * l4 + 2] = fmaf(g, xl, accL[4 * l4 + 2]); accR[4 * l4 + 2] = fmaf(g, xR, accR[4 * l4 + 2]);
-              g = fmaf(rg, dg.w, g0.w); accL[4 * l4 + 3] = fmaf(g, xl, accL[4 * l4 + 3]); accR[4 * l4 + 3] = fmaf(g, xR, accR[4 * l4 + 3]);
+              const ulonglong2 g0 = g0v[l4], dg = dgv[l4];
+              const f32x2 ga = fma2(rg2, dg.x, g0.x), gb = fma2(rg2, dg.y, g0.y);
+              accL[2 * l4] = fma2(ga, xl, accL[2 * l4]);         accR[2 * l4] = fma2(ga, xR, accR[2 * l4]);
+              accL[2 * l4 + 1] = fma2(gb, xl, accL[2 * l4 + 1]); accR[2 * l4 + 1] = fma2(gb, xR, accR[2 * l4 + 1]);
             }
           }
         }
@@ -368,11 +408,9 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
 #pragma unroll
           for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
             if (mq & (1u << l4)) {
-              const float4 q0 = q0v[l4], dq = dqv[l4];
-              accQ[4 * l4 + 0] = fmaf(fmaf(rg, dq.x, q0.x), x0, accQ[4 * l4 + 0]);
-              accQ[4 * l4 + 1] = fmaf(fmaf(rg, dq.y, q0.y), x0, accQ[4 * l4 + 1]);
-              accQ[4 * l4 + 2] = fmaf(fmaf(rg, dq.z, q0.z), x0, accQ[4 * l4 + 2]);
-              accQ[4 * l4 + 3] = fmaf(fmaf(rg, dq.w, q0.w), x0, accQ[4 * l4 + 3]);
+              const ulonglong2 q0 = q0v[l4], dq = dqv[l4];
+              accQ[2 * l4] = fma2(fma2(rg2, dq.x, q0.x), x0, accQ[2 * l4]);
+              accQ[2 * l4 + 1] = fma2(fma2(rg2, dq.y, q0.y), x0, accQ[2 * l4 + 1]);
             }
           }
         }
@@ -381,11 +419,17 @@ __global__ void __launch_bounds__(kMixTile) mix_kernel(Layout p, int T)
   }
   const size_t col = (size_t)p.B + t;
 #pragma unroll
-  for (int l = 0; l < kMaxSpeakers; l++) {
-    if (l < L) {
-      p.cdir[((size_t)s * 2 * L + 2 * l) * p.cs + col] = accL[l];
-      p.cdir[((size_t)s * 2 * L + 2 * l + 1) * p.cs + col] = accR[l];
-      p.qdif[((size_t)s * L + l) * p.cs + col] = accQ[l];
+  for (int l2 = 0; l2 < kMaxSpeakers / 2; l2++) {
+    float vL[2], vR[2], vQ[2];
+    unpack2(accL[l2], vL[0], vL[1]); unpack2(accR[l2], vR[0], vR[1]); unpack2(accQ[l2], vQ[0], vQ[1]);
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      const int l = 2 * l2 + h;
+      if (l < L) {
+        p.cdir[((size_t)s * 2 * L + 2 * l) * p.cs + col] = vL[h];
+        p.cdir[((size_t)s * 2 * L + 2 * l + 1) * p.cs + col] = vR[h];
+        p.qdif[((size_t)s * L + l) * p.cs + col] = vQ[h];
+      }
     }
   }
 }
@@ -548,12 +592,11 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
     if (bus) {
       const float *wrow = rows + p.hist;    // window sample 0
       const bool dif = p.N > 0;
-      float d0[2], dd[2];
-      for (int h = 0; h < 2; h++) {  // h = 0: block k-1, h = 1: block k
-        const float t0 = p.d_stat[(size_t)(k + h) * L2 + ch] * p.fs;
-        const float t1 = p.d_stat[(size_t)(k + h + 1) * L2 + ch] * p.fs;
-        d0[h] = t0; dd[h] = t1 - t0;
-      }
+      // static delays at the ends of blocks k-2, k-1, k (table slot = block + 2)
+      const float ta = p.d_stat[(size_t)k * L2 + ch] * p.fs;
+      const float tb = p.d_stat[(size_t)(k + 1) * L2 + ch] * p.fs;
+      const float tc = p.d_stat[(size_t)(k + 2) * L2 + ch] * p.fs;
+      const float dda = tb - ta, ddb = tc - tb;
       const float2 *cw = reinterpret_cast<const float2 *>(cwin + g * 2 * M);
       for (int n = tid; n < M; n += nthr) {
         float2 v = make_float2(0.f, 0.f);
@@ -567,10 +610,11 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
         }
         if (dif) {
           const int t = 2 * n;            // window sample, both of the pair lie in the same block
-          const int h = t >= p.B;
-          const int nn = t - h * p.B;
-          v.x += delayed_read(wrow + t, ramped_delay(d0[h], dd[h], (float)(nn + p.doff) * invB));
-          v.y += delayed_read(wrow + t + 1, ramped_delay(d0[h], dd[h], (float)(nn + 1 + p.doff) * invB));
+          const bool h = t >= p.B;        // false: block k-1, true: block k
+          const int nn = h ? t - p.B : t;
+          const float d0 = h ? tb : ta, dd = h ? ddb : dda;
+          v.x += delayed_read(wrow + t, ramped_delay(d0, dd, (float)(nn + p.doff) * invB));
+          v.y += delayed_read(wrow + t + 1, ramped_delay(d0, dd, (float)(nn + 1 + p.doff) * invB));
         }
         a[padi(n)] = v;
       }
