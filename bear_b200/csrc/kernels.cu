@@ -31,7 +31,8 @@ __device__ __forceinline__ float2 cmul_conj(float2 a, float2 w)  // a * conj(w)
 {
   return make_float2(fmaf(a.x, w.x, a.y * w.y), fmaf(a.y, w.x, -a.x * w.y));
 }
-// table of exp(-i pi q / M), q in [0, M); q in [M, 2M) by symmetry
+// table of exp(-i pi q / M), q in [0, M); q in [M, 2M) by symmetry.  (The table itself has 2M
+// entries: [M, 2M) holds the per-pass twiddles of the radix-8 passes, see fft_shared.)
 __device__ __forceinline__ float2 ldtw(const float2 *__restrict__ tw, int q, int M)
 {
   if (q < M) return __ldg(tw + q);
@@ -97,12 +98,11 @@ __device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int l
 #pragma unroll
       for (int r = 0; r < 8; r++) v[r] = a[padi(j + r * Q)];
       if (ls > 0) {
-        const int q = k << (logM - 2 - ls);   // exp(-2 pi i k / (8 Ns)) = tw[k M / (4 Ns)]
-        const float2 w1 = __ldg(tw + q), w2 = __ldg(tw + 2 * q), w4 = __ldg(tw + 4 * q);
-        const float2 w3 = cmul(w1, w2), w5 = cmul(w1, w4), w6 = cmul(w2, w4), w7 = cmul(w3, w4);
-        v[1] = twid<INV>(v[1], w1); v[2] = twid<INV>(v[2], w2); v[3] = twid<INV>(v[3], w3);
-        v[4] = twid<INV>(v[4], w4); v[5] = twid<INV>(v[5], w5); v[6] = twid<INV>(v[6], w6);
-        v[7] = twid<INV>(v[7], w7);
+        // exp(-2 pi i r k / (8 Ns)), r = 1..7, from the per-pass table behind the first M entries:
+        // consecutive threads read consecutive entries (k is the low bits of j)
+        const float2 *w = tw + M + (Ns - 8) + k;
+#pragma unroll
+        for (int r = 1; r < 8; r++) v[r] = twid<INV>(v[r], __ldg(w + (r - 1) * Ns));
       }
       dft8<INV>(v);
       const int j0 = ((j - k) << 3) + k;
@@ -560,31 +560,39 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
   const int ch = bus ? 2 * unit + g : L2 + 2 * (unit - p.L) + g;
   const bool active = bus || ch < L2 + p.A;                          // odd A: last group idles
 
-  // stage the source rows: columns [k*B, k*B + hist + 2B) of the (B + hist)-prefixed row
+  // static delays at the ends of blocks k-2, k-1, k (table slot = block + 2); loaded before the
+  // copies below so that their latency overlaps
+  float ta = 0.f, tb = 0.f, tc = 0.f;
+  if (bus) {
+    ta = p.d_stat[(size_t)k * L2 + ch] * p.fs;
+    tb = p.d_stat[(size_t)(k + 1) * L2 + ch] * p.fs;
+    tc = p.d_stat[(size_t)(k + 2) * L2 + ch] * p.fs;
+  }
+  // stage the source rows: columns [k*B, k*B + hist + 2B) of the (B + hist)-prefixed row; group g
+  // copies row g (bus units have one row: both groups share the copy of row 0)
   if (!bus || p.N > 0) {
-    const int nrows = bus ? 1 : 2;
     const int vec = RW >> 2;
-    for (int idx = threadIdx.x; idx < nrows * vec; idx += blockDim.x) {
-      const int r = idx / vec, v = idx - r * vec;
-      const int am = 2 * (unit - p.L) + r;
-      if (!bus && am >= p.A) continue;
-      const float *src = (bus ? p.w + (size_t)unit * p.ws : p.amb + (size_t)am * p.ws) + (size_t)k * p.B + 4 * v;
-      const unsigned dst = (unsigned)__cvta_generic_to_shared(rows + r * RW + 4 * v);
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
+    if (bus) {
+      const float *src = p.w + (size_t)unit * p.ws + (size_t)k * p.B;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(rows);
+      for (int v = threadIdx.x; v < vec; v += blockDim.x)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
+    } else if (active) {
+      const float *src = p.amb + (size_t)(ch - L2) * p.ws + (size_t)k * p.B;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(rows + g * RW);
+      for (int v = tid; v < vec; v += nthr)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
     }
-    asm volatile("cp.async.commit_group;");
   }
   const bool cstaged = bus && stage_direct;
-  if (cstaged) {   // both ears' direct-bus windows [block k-1 | block k]
+  if (cstaged) {   // this group's direct-bus window [block k-1 | block k]
     const int vec = (2 * M) >> 2;
-    for (int idx = threadIdx.x; idx < 2 * vec; idx += blockDim.x) {
-      const int r = idx / vec, v = idx - r * vec;
-      const float *src = p.cdir + (size_t)(2 * unit + r) * p.cs + (size_t)k * p.B + 4 * v;
-      const unsigned dst = (unsigned)__cvta_generic_to_shared(cwin + r * 2 * M + 4 * v);
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src));
-    }
-    asm volatile("cp.async.commit_group;");
+    const float *src = p.cdir + (size_t)ch * p.cs + (size_t)k * p.B;
+    const unsigned dst = (unsigned)__cvta_generic_to_shared(cwin + g * 2 * M);
+    for (int v = tid; v < vec; v += nthr)
+      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
   }
+  asm volatile("cp.async.commit_group;");
   asm volatile("cp.async.wait_group 0;");
   __syncthreads();
 
@@ -592,10 +600,6 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
     if (bus) {
       const float *wrow = rows + p.hist;    // window sample 0
       const bool dif = p.N > 0;
-      // static delays at the ends of blocks k-2, k-1, k (table slot = block + 2)
-      const float ta = p.d_stat[(size_t)k * L2 + ch] * p.fs;
-      const float tb = p.d_stat[(size_t)(k + 1) * L2 + ch] * p.fs;
-      const float tc = p.d_stat[(size_t)(k + 2) * L2 + ch] * p.fs;
       const float dda = tb - ta, ddb = tc - tb;
       const float2 *cw = reinterpret_cast<const float2 *>(cwin + g * 2 * M);
       for (int n = tid; n < M; n += nthr) {

@@ -48,7 +48,7 @@ struct Layout {
   const float2 *h_dec;       // [L][B]
   const float2 *h_hoa;       // [A][2][B]
   float2 *ypart;             // [Tmax][2][2][KS][B]
-  const float2 *tw;          // [B] exp(-i pi q / B)
+  const float2 *tw;          // [2B]: [0,B) exp(-i pi q / B); [B,2B) per-pass radix-8 twiddles
   // out
   float *out;  size_t os;    // [2][os]
   // control tail (optional): data-file delay table, gain-normalisation factors, raw gains of this call

@@ -208,11 +208,18 @@ std::shared_ptr<FilterBank> build_bank(const bear_cuda_config &cfg, const bear_c
   cudaStream_t st = nullptr;
   CK(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
   struct StreamGuard { cudaStream_t s; ~StreamGuard() { cudaStreamDestroy(s); } } guard{st};
-  {  // twiddles exp(-i pi q / B), computed in double
-    std::vector<float2> tw(B);
+  {  // twiddles, computed in double: [0, B) exp(-i pi q / B); [B, 2B) the per-pass tables of the
+     // radix-8 FFT passes, exp(-2 pi i r j / (8 Ns)) at B + (Ns - 8) + (r - 1) Ns + j  (kernels.cu fft_shared)
+    std::vector<float2> tw(2 * (size_t)B, make_float2(0.f, 0.f));
     const double pi = 3.14159265358979323846264338327950288;
     for (uint32_t q = 0; q < B; q++) tw[q] = make_float2((float)std::cos(pi * q / B), (float)-std::sin(pi * q / B));
-    float2 *dtw = k.alloc<float2>(B);
+    for (uint32_t Ns = 8; Ns * 8 <= B; Ns *= 8)
+      for (uint32_t r = 1; r < 8; r++)
+        for (uint32_t j = 0; j < Ns; j++) {
+          const double a = 2.0 * pi * (double)r * (double)j / (8.0 * Ns);
+          tw[B + (Ns - 8) + (r - 1) * Ns + j] = make_float2((float)std::cos(a), (float)-std::sin(a));
+        }
+    float2 *dtw = k.alloc<float2>(2 * (size_t)B);
     CK(cudaMemcpyAsync(dtw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice, st));
     CK(cudaStreamSynchronize(st));
     k.tw = dtw;
