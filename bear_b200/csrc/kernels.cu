@@ -172,6 +172,46 @@ __device__ __forceinline__ void irfft_pre(float2 xk, float2 xm, float2 w, float2
   zm = make_float2(ev.x + od.y, od.x - ev.y);
 }
 
+// Two FP32 lanes in one 64-bit register: fma.rn.f32x2 (SASS FFMA2) does two IEEE fused multiply-adds
+// per issued instruction -- bit-identical to two fmaf() -- which halves the issue slots of the
+// accumulation (a scalar second operand is broadcast by the hardware).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float lo, float hi)
+{
+  f32x2 r;
+  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
+{
+  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
+{
+  f32x2 d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
+{
+  f32x2 d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b)
+{
+  f32x2 d;
+  asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b)
+{
+  f32x2 d;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ f32x2 splat2(float v) { return pack2(v, v); }
+
 // Lagrange order-3 coefficients for position s in [1,2) relative to the first of the nodes 0..3
 __device__ __forceinline__ void lagrange3(float s, float c[4])
 {
@@ -196,6 +236,29 @@ __device__ __forceinline__ float delayed_read(const float *__restrict__ x, float
   acc = fmaf(c[1], q[-1], acc);
   acc = fmaf(c[2], q[-2], acc);
   acc = fmaf(c[3], q[-3], acc);
+  return acc;
+}
+// Two delayed reads at once, (delayed_read(xa, da), delayed_read(xb, db)), with the coefficient
+// arithmetic in packed form: the same IEEE operations in the same order as the scalar version, two
+// lanes per instruction.  (ptxas contracts a packed multiply feeding a packed add into FFMA2 even
+// for mul.rn/add.rn, so there is deliberately no such pair here; ramped_delay stays scalar.)
+__device__ __forceinline__ f32x2 delayed_read2(const float *__restrict__ xa, float da, const float *__restrict__ xb, float db)
+{
+  const f32x2 d = pack2(da, db);
+  float ha, hb;
+  unpack2(add2(d, splat2(0.5f)), ha, hb);
+  const float fa = floorf(ha), fb = floorf(hb);
+  const f32x2 s = add2(splat2(1.5f), sub2(d, pack2(fa, fb)));
+  const f32x2 s1 = add2(s, splat2(-1.0f)), s2 = add2(s, splat2(-2.0f)), s3 = add2(s, splat2(-3.0f));
+  const f32x2 c0 = mul2(mul2(mul2(s1, s2), s3), splat2(-1.0f / 6.0f));
+  const f32x2 c1 = mul2(mul2(mul2(s, s2), s3), splat2(0.5f));
+  const f32x2 c2 = mul2(mul2(mul2(s, s1), s3), splat2(-0.5f));
+  const f32x2 c3 = mul2(mul2(mul2(s, s1), s2), splat2(1.0f / 6.0f));
+  const float *qa = xa - (int)fa, *qb = xb - (int)fb;
+  f32x2 acc = mul2(c0, pack2(qa[0], qb[0]));
+  acc = fma2(c1, pack2(qa[-1], qb[-1]), acc);
+  acc = fma2(c2, pack2(qa[-2], qb[-2]), acc);
+  acc = fma2(c3, pack2(qa[-3], qb[-3]), acc);
   return acc;
 }
 
@@ -243,27 +306,6 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 // registers; the gains of kMixChunk channels are staged in shared memory with their per-block
 // deltas so the inner loop is one FMA for the ramped gain + one FMA per ear.
 // ----------------------------------------------------------------------------------------------
-// Two FP32 lanes in one 64-bit register: fma.rn.f32x2 (SASS FFMA2) does two IEEE fused multiply-adds
-// per issued instruction -- bit-identical to two fmaf() -- which halves the issue slots of the
-// accumulation (a scalar second operand is broadcast by the hardware).
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pack2(float lo, float hi)
-{
-  f32x2 r;
-  asm("mov.b64 %0, {%1,%2};" : "=l"(r) : "f"(lo), "f"(hi));
-  return r;
-}
-__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi)
-{
-  asm("mov.b64 {%0,%1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
-}
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
-{
-  f32x2 d;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
-  return d;
-}
-
 __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
 {
   // row = one channel: [g0 | dg | q0 | dq] x 24 speakers, padded by 4 floats so that accesses to
@@ -379,8 +421,8 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
       for (int u = 0; u < 2; u++) {
         const int j = min(ii + u, cnt - 1);
         const float *xr = xt + j * XW + p.hist + tid;
-        xl2[u] = delayed_read(xr, fminf(ramped_delay(sd[j][0], sd[j][1], rd), dmax));
-        xR2[u] = delayed_read(xr, fminf(ramped_delay(sd[j][2], sd[j][3], rd), dmax));
+        unpack2(delayed_read2(xr, fminf(ramped_delay(sd[j][0], sd[j][1], rd), dmax),
+                              xr, fminf(ramped_delay(sd[j][2], sd[j][3], rd), dmax)), xl2[u], xR2[u]);
         x02[u] = xr[0];
       }
 #pragma unroll
@@ -617,8 +659,10 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
           const bool h = t >= p.B;        // false: block k-1, true: block k
           const int nn = h ? t - p.B : t;
           const float d0 = h ? tb : ta, dd = h ? ddb : dda;
-          v.x += delayed_read(wrow + t, ramped_delay(d0, dd, (float)(nn + p.doff) * invB));
-          v.y += delayed_read(wrow + t + 1, ramped_delay(d0, dd, (float)(nn + 1 + p.doff) * invB));
+          float ra, rb;
+          unpack2(delayed_read2(wrow + t, ramped_delay(d0, dd, (float)(nn + p.doff) * invB),
+                                wrow + t + 1, ramped_delay(d0, dd, (float)(nn + 1 + p.doff) * invB)), ra, rb);
+          v.x += ra; v.y += rb;
         }
         a[padi(n)] = v;
       }
@@ -756,8 +800,10 @@ __global__ void __launch_bounds__(128) cmac_kernel(Layout p, int T)
   else cmac_body<false, true>(p, j, e, ks, pair, v, accA, accB);
   const size_t hB = p.B >> 1;
   float4 *y = reinterpret_cast<float4 *>(p.ypart) + pair;
-  if (doA) y[((((size_t)j * 2 + e) * 2 + 0) * p.KS + ks) * hB] = accA;
-  if (doB) y[((((size_t)(j + 1) * 2 + e) * 2 + 1) * p.KS + ks) * hB] = accB;
+  // partial spectra are scratch of this launch: indexed by the period within the launch
+  const int jl = j - p.k0;
+  if (doA) y[((((size_t)jl * 2 + e) * 2 + 0) * p.KS + ks) * hB] = accA;
+  if (doB) y[((((size_t)(jl + 1) * 2 + e) * 2 + 1) * p.KS + ks) * hB] = accB;
 }
 
 void launch_cmac(const Layout &p, int T, cudaStream_t st)
@@ -773,28 +819,38 @@ void launch_cmac(const Layout &p, int T, cudaStream_t st)
 // (rcl::InterpolatingFirFilterMatrix with transitionSamples = period, dsp.cpp:73-87).
 // grid: 2T; block: B/4.
 // ----------------------------------------------------------------------------------------------
-__global__ void ifft_out_kernel(Layout p, int T)
+__global__ void __launch_bounds__(512) ifft_out_kernel(Layout p, int T)
 {
   extern __shared__ float2 sm[];
   const int M = p.B;
-  float2 *a = sm, *b = sm + M + (M >> 3);
+  const int FB = M + (M >> 3);
   const int k = p.k0 + (blockIdx.x >> 1), e = blockIdx.x & 1;
-  const int tid = threadIdx.x, nthr = blockDim.x;
+  // two thread groups in lockstep: group 0 transforms the new-view spectrum, group 1 the old-view
+  // one of a view-change period (idle otherwise, it only keeps the barriers company)
+  const int nthr = blockDim.x >> 1;
+  const int g = threadIdx.x >= nthr, tid = threadIdx.x - g * nthr;
+  float2 *a = sm + (size_t)g * 2 * FB, *b = a + FB;
   const bool xf = p.view[k + 1] != p.view[k];
+  const bool work = g == 0 || xf;
   const float invB = 1.0f / (float)p.B;
   float2 *dst = reinterpret_cast<float2 *>(p.out + (size_t)e * p.os + (size_t)k * p.B);
-  for (int pass = xf ? 1 : 0; pass >= 0; pass--) {   // pass 1 = old view, pass 0 = new view
-    const float2 *y = p.ypart + ((((size_t)k * 2 + e) * 2 + pass) * p.KS) * M;
-    __syncthreads();
+  if (work) {
+    const float2 *y = p.ypart + ((((size_t)(k - p.k0) * 2 + e) * 2 + g) * p.KS) * M;   // g = 1: old view
     for (int kk = tid; kk <= M / 2; kk += nthr) {
+      // partial spectra summed in order; the loads of four partials are issued together
       float2 xk = make_float2(0.f, 0.f), xm = xk;
-      for (int s = 0; s < p.KS; s++) {
-        const float2 u = y[(size_t)s * M + kk];
-        xk.x += u.x; xk.y += u.y;
-        if (kk) {
-          const float2 v = y[(size_t)s * M + M - kk];
-          xm.x += v.x; xm.y += v.y;
-        }
+      const int km = kk ? M - kk : 0;
+      int s = 0;
+      for (; s + 4 <= p.KS; s += 4) {
+        float2 u[4], v[4];
+#pragma unroll
+        for (int i = 0; i < 4; i++) { u[i] = y[(size_t)(s + i) * M + kk]; v[i] = y[(size_t)(s + i) * M + km]; }
+#pragma unroll
+        for (int i = 0; i < 4; i++) { xk.x += u[i].x; xk.y += u[i].y; xm.x += v[i].x; xm.y += v[i].y; }
+      }
+      for (; s < p.KS; s++) {
+        const float2 u = y[(size_t)s * M + kk], v = y[(size_t)s * M + km];
+        xk.x += u.x; xk.y += u.y; xm.x += v.x; xm.y += v.y;
       }
       if (kk == 0) {
         a[0] = make_float2(xk.x + xk.y, xk.x - xk.y);
@@ -805,17 +861,27 @@ __global__ void ifft_out_kernel(Layout p, int T)
         a[padi(M - kk)] = zm;
       }
     }
-    float2 *z = fft_shared<true>(a, b, M, p.logB, p.tw);
+  }
+  float2 *z = fft_shared<true>(a, b, M, p.logB, p.tw, tid, nthr);
+  // old view faded out (in place), then the new view faded in on top of it
+  if (g == 1 && xf) {
+    for (int n = tid; n < M / 2; n += nthr) {
+      float2 v = z[padi(M / 2 + n)];
+      const float r0 = (float)(2 * n + p.xoff) * invB, r1 = (float)(2 * n + 1 + p.xoff) * invB;
+      v.x *= (1.0f - r0); v.y *= (1.0f - r1);
+      z[padi(M / 2 + n)] = v;
+    }
+  }
+  __syncthreads();
+  if (g == 0) {
+    // group 1's result sits in the same one of its two buffers as ours (same pass count)
+    const float2 *zo = z + 2 * FB;
     for (int n = tid; n < M / 2; n += nthr) {
       float2 v = z[padi(M / 2 + n)];
       if (xf) {
         const float r0 = (float)(2 * n + p.xoff) * invB, r1 = (float)(2 * n + 1 + p.xoff) * invB;
-        if (pass == 1) {
-          v.x *= (1.0f - r0); v.y *= (1.0f - r1);
-        } else {
-          const float2 o = dst[n];
-          v.x = fmaf(r0, v.x, o.x); v.y = fmaf(r1, v.y, o.y);
-        }
+        const float2 o = zo[padi(M / 2 + n)];
+        v.x = fmaf(r0, v.x, o.x); v.y = fmaf(r1, v.y, o.y);
       }
       dst[n] = v;
     }
@@ -824,8 +890,10 @@ __global__ void ifft_out_kernel(Layout p, int T)
 
 void launch_ifft_out(const Layout &p, int T, cudaStream_t st)
 {
-  int threads = p.B / 8 < 32 ? 32 : p.B / 8;
-  ifft_out_kernel<<<2 * T, threads, fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T);
+  // B/4 threads per group (the FFT passes use the first B/8 of them, the partial-sum and output
+  // loops all): a single period is two CTAs, so the sum over the partial spectra is spread wide
+  int threads = 2 * (p.B / 4 < 32 ? 32 : (p.B / 4 > 256 ? 256 : p.B / 4));
+  ifft_out_kernel<<<2 * T, threads, 2 * fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -1049,8 +1117,9 @@ cudaError_t configure_kernels(int B)
     cudaError_t e;
     if ((e = cudaFuncSetAttribute(filter_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
     if ((e = cudaFuncSetAttribute(decorrelate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
-    if ((e = cudaFuncSetAttribute(ifft_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
   }
+  if (2 * smem > 48 * 1024)   // two transforms per CTA
+    return cudaFuncSetAttribute(ifft_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * smem);
   return cudaSuccess;
 }
 

@@ -47,7 +47,7 @@ struct Layout {
   const float2 *h_brir;      // [V][2L][P][B], pre-scaled by 1/(2B)
   const float2 *h_dec;       // [L][B]
   const float2 *h_hoa;       // [A][2][B]
-  float2 *ypart;             // [Tmax][2][2][KS][B]
+  float2 *ypart;             // [periods of one launch][2][2][KS][B], KS chosen per launch
   const float2 *tw;          // [2B]: [0,B) exp(-i pi q / B); [B,2B) per-pass radix-8 twiddles
   // out
   float *out;  size_t os;    // [2][os]

@@ -75,7 +75,12 @@ struct bear_cuda_renderer {
   int device = 0;
   cudaStream_t stream = nullptr;
   cudaStream_t copy_stream = nullptr;      // host->device uploads of the host-buffer path
+  cudaStream_t d2h_stream = nullptr;       // device->host reads of finished chunks (host-buffer path)
+  int ks_cfg = 1;                          // configured cMAC splits (the minimum; short launches use more)
+  int ks_units = 1;                        // cMAC work units (loudspeakers + HOA decode)
+  bool ks_dynamic = true;                  // false while the caller provides the partial-spectrum scratch
   std::vector<cudaEvent_t> h2d_events;     // one per upload chunk
+  std::vector<cudaEvent_t> done_events;    // one per rendered chunk
   bool tables_on_device = false;           // bear_cuda_control_tables filled the staging tables
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
@@ -128,7 +133,9 @@ struct bear_cuda_renderer {
     if (h_in) cudaFreeHost(h_in);
     if (h_out) cudaFreeHost(h_out);
     for (cudaEvent_t e : h2d_events) cudaEventDestroy(e);
+    for (cudaEvent_t e : done_events) cudaEventDestroy(e);
     if (copy_stream) cudaStreamDestroy(copy_stream);
+    if (d2h_stream) cudaStreamDestroy(d2h_stream);
     if (stream) cudaStreamDestroy(stream);
   }
 };
@@ -267,6 +274,8 @@ std::shared_ptr<FilterBank> build_bank(const bear_cuda_config &cfg, const bear_c
   return bank;
 }
 
+int cmac_splits_for(const bear_cuda_renderer *r, int n);
+
 bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_ptr<FilterBank> bank)
 {
   const FilterBank &k = *bank;
@@ -283,6 +292,7 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   CK(cudaSetDevice(r->device));
   CK(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&r->d2h_stream, cudaStreamNonBlocking));
 
   Layout &p = r->lay;
   p.N = cfg.num_objects_channels; p.M = cfg.num_direct_speakers_channels; p.H = cfg.num_hoa_channels;
@@ -318,13 +328,17 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
     int KS = cfg.cmac_splits;
     if (KS == 0) KS = (4 * 148 + base - 1) / base;
     p.KS = std::max(1, std::min(KS, nunits));
+    r->ks_cfg = p.KS;
+    r->ks_units = nunits;
   }
   p.R = p.Tmax + p.P - 1;
   r->chunk = (int)cfg.chunk_blocks;
   // host-buffer path: upload in ~12 chunks (at least 16 periods each) so copies overlap the kernels
   r->h2d_chunk = cfg.chunk_blocks ? (int)cfg.chunk_blocks : std::max(16, (p.Tmax + 11) / 12);
   r->h2d_events.resize((p.Tmax + r->h2d_chunk - 1) / r->h2d_chunk);
+  r->done_events.resize(r->h2d_events.size());
   for (cudaEvent_t &e : r->h2d_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+  for (cudaEvent_t &e : r->done_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 
   // ---- allocations -----------------------------------------------------------------------
   const size_t TB = (size_t)p.Tmax * p.B;
@@ -346,7 +360,11 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   p.w = r->dalloc<float>((size_t)p.L * p.ws);
   p.amb = r->dalloc<float>((size_t)std::max(1, p.A) * p.ws);
   p.fdl = r->dalloc<float2>((size_t)p.CH * p.R * p.B);
-  p.ypart = r->dalloc<float2>((size_t)p.Tmax * 2 * 2 * p.KS * p.B);
+  {  // partial spectra of one launch, [periods of the launch][2][2][splits][B]; sized for the worst launch
+    size_t cap = 0;
+    for (int n = 1; n <= p.Tmax; n++) cap = std::max(cap, (size_t)n * cmac_splits_for(r.get(), n));
+    p.ypart = r->dalloc<float2>(cap * 2 * 2 * p.B);
+  }
   p.os = round_up(TB, 4);
   p.out = r->dalloc<float>(2 * p.os);
   r->audio_out = p.out;
@@ -386,13 +404,34 @@ bear_cuda_renderer *create_impl(const bear_cuda_config &cfg, const bear_cuda_dat
   return create_with_bank(cfg, build_bank(cfg, d));
 }
 
+// cMAC splits of a launch of n periods: the configured number, or as many as it takes to put about
+// four CTAs on every SM when the launch is short (a single period is otherwise 4 CTAs that walk all
+// 24 loudspeakers x P partitions one after the other).
+int cmac_splits_for(const bear_cuda_renderer *r, int n)
+{
+  const Layout &p = r->lay;
+  if (!r->ks_dynamic) return r->ks_cfg;
+  const int threads = std::min(p.B / 2, 128);
+  const int base = (p.B / 2 / threads) * 2 * (n + 1);
+  return std::max(r->ks_cfg, std::min((4 * 148 + base - 1) / base, r->ks_units));
+}
+
+// Chunk sizes of a call of T periods issued `chunk` periods at a time (chunk <= 0: all at once).
+static std::vector<int> uniform_chunks(int T, int chunk)
+{
+  std::vector<int> v;
+  if (chunk <= 0 || chunk > T) chunk = T;
+  for (int k0 = 0; k0 < T; k0 += chunk) v.push_back(std::min(chunk, T - k0));
+  return v;
+}
 // Queue the kernels for T blocks whose audio and tables are already in the staging areas.
-// A call may be issued in chunks of `chunk` periods (all kernels of chunk c, then chunk c+1, ...):
-// every intermediate buffer is indexed by the period number within the call, so later chunks just
-// read earlier columns.  `before_chunk(c, k0, n)` runs on the host before chunk c is queued (the
-// host-buffer path uses it to make the stream wait for that chunk's upload).
-template <class Hook>
-void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Hook &&before_chunk)
+// A call may be issued in chunks (all kernels of chunk c, then chunk c+1, ...): every intermediate
+// buffer is indexed by the period number within the call, so later chunks just read earlier
+// columns.  `before_chunk(c, k0, n)` runs on the host before chunk c is queued (the host-buffer path
+// uses it to make the stream wait for that chunk's upload), `after_chunk(c, k0, n)` after it.
+template <class Before, class After>
+void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, Before &&before_chunk,
+                  After &&after_chunk)
 {
   Layout &p = r->lay;
   cudaStream_t st = r->stream;
@@ -407,18 +446,21 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Hook &&before_chunk)
     chain.push_back(e);
     if (kernel_id >= 0) ids.push_back(kernel_id);
   };
-  if (chunk <= 0 || chunk > T) chunk = T;
   int nchunks = 0;
-  for (int k0 = 0; k0 < T; k0 += chunk, nchunks++) {
-    const int n = std::min(chunk, T - k0);
+  for (int k0 = 0; k0 < T; nchunks++) {
+    const int n = chunks[nchunks];
     before_chunk(nchunks, k0, n);
     p.k0 = k0;
     if (p.N + p.M > 0) { mark(BEAR_CUDA_KERNEL_MIX); launch_mix(p, n, st); }
     if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, n, st); }
     if (p.N > 0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, st); }
     mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, st);
+    p.KS = cmac_splits_for(r, n);
     mark(BEAR_CUDA_KERNEL_CMAC); launch_cmac(p, n, st);
     mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, st);
+    p.KS = r->ks_cfg;
+    after_chunk(nchunks, k0, n);
+    k0 += n;
   }
   p.k0 = 0;
   mark(BEAR_CUDA_KERNEL_CARRY);
@@ -469,7 +511,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Hook &&before_chunk)
 
 void run_pipeline(bear_cuda_renderer *r, int T)
 {
-  run_pipeline(r, T, r->chunk, [](int, int, int) {});
+  run_pipeline(r, T, uniform_chunks(T, r->chunk), [](int, int, int) {}, [](int, int, int) {});
 }
 
 template <class F>
@@ -707,7 +749,6 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
     Layout &p = r->lay;
     if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
     if (!output) throw InvalidArgument{"output must not be NULL"};
-    const size_t TB = (size_t)T * p.B;
     if (p.N && !objects) throw InvalidArgument{"objects input must not be NULL"};
     if (p.M && !direct_speakers) throw InvalidArgument{"direct_speakers input must not be NULL"};
     if (p.H && !hoa) throw InvalidArgument{"hoa input must not be NULL"};
@@ -715,9 +756,11 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
     // chunk c before it queues the kernels of chunk c: copies of later chunks overlap the kernels.
     cudaStream_t cs = r->copy_stream;
     upload_tables(r, (int)T, tables, false, cs);
-    const int hc = r->h2d_chunk;
-    for (int k0 = 0, c = 0; k0 < (int)T; k0 += hc, c++) {
-      const size_t col = (size_t)k0 * p.B, width = (size_t)std::min(hc, (int)T - k0) * p.B * sizeof(float);
+    // (Shorter chunks towards the end do not pay: a chunk of a few periods still takes ~0.1 ms to
+    // go through the six kernels, longer than its upload.)
+    const std::vector<int> chunks = uniform_chunks((int)T, r->h2d_chunk);
+    for (int k0 = 0, c = 0; k0 < (int)T; k0 += chunks[c], c++) {
+      const size_t col = (size_t)k0 * p.B, width = (size_t)chunks[c] * p.B * sizeof(float);
       auto up_audio = [&](int row0, int rows, const float *host, size_t stride) {
         if (rows)
           CK(cudaMemcpy2DAsync(p.xin + (size_t)row0 * p.xs + p.hist + col, p.xs * sizeof(float), host + col,
@@ -728,9 +771,17 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
       up_audio(p.N + p.M, p.H, hoa, hoa_stride);
       CK(cudaEventRecord(r->h2d_events[c], cs));
     }
-    run_pipeline(r, (int)T, hc, [&](int c, int, int) { CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0)); });
-    CK(cudaMemcpy2DAsync(output, out_stride * sizeof(float), p.out, p.os * sizeof(float), TB * sizeof(float), 2,
-                         cudaMemcpyDeviceToHost, r->stream));
+    // finished chunks are read back on a third stream while later chunks still upload and render
+    run_pipeline(
+        r, (int)T, chunks, [&](int c, int, int) { CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0)); },
+        [&](int c, int k0, int n) {
+          CK(cudaEventRecord(r->done_events[c], r->stream));
+          CK(cudaStreamWaitEvent(r->d2h_stream, r->done_events[c], 0));
+          CK(cudaMemcpy2DAsync(output + (size_t)k0 * p.B, out_stride * sizeof(float), p.out + (size_t)k0 * p.B,
+                               p.os * sizeof(float), (size_t)n * p.B * sizeof(float), 2, cudaMemcpyDeviceToHost,
+                               r->d2h_stream));
+        });
+    CK(cudaStreamSynchronize(r->d2h_stream));
     CK(cudaStreamSynchronize(r->stream));
   });
 }
@@ -889,15 +940,18 @@ int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T)
     const bool prof = r->profiling;
     p.ypart = scratch;
     r->profiling = false;  // the event pool may grow; this entry point must not create anything
+    r->ks_dynamic = false; // the size check above is for the configured number of splits
     try {
       run_pipeline(r, (int)T);
     } catch (...) {
       p.ypart = own;
       r->profiling = prof;
+      r->ks_dynamic = true;
       throw;
     }
     p.ypart = own;
     r->profiling = prof;
+    r->ks_dynamic = true;
   });
 }
 

@@ -292,6 +292,24 @@ def run_ours(args, rank, world, local_rank):
         step_e2e()
     ms_e2e = timed(step_e2e, e2e_steps)
     clk = clocks.stop() if rank == 0 else None
+    # per-launch kernel times at the chunk size of the host-buffer path (untimed extra call)
+    r.set_profiling(True)
+    r.get_profile(reset=True)
+    step_e2e()
+    e2e_prof = {k: v[0] / max(v[1], 1) for k, v in r.get_profile(reset=True).items() if v[1]}
+    r.set_profiling(False)
+
+    # the PCIe floor of that call: the same bytes copied host->device from pinned memory, nothing else
+    h_flat = torch.from_numpy(h_audio.reshape(-1))
+    d_flat = torch.empty(h2d // 4, dtype=torch.float32, device="cuda")
+
+    def step_copy():
+        with torch.cuda.stream(stream):
+            d_flat[:h_flat.numel()].copy_(h_flat, non_blocking=True)
+            d_flat[h_flat.numel():].copy_(h_flat[:d_flat.numel() - h_flat.numel()], non_blocking=True)
+
+    step_copy()
+    ms_copy = timed(step_copy, e2e_steps) / e2e_steps
 
     # ---- real-time use: one period per call through bear_cuda_process (host pointers), wall clock ----
     stream_ms = None
@@ -412,6 +430,8 @@ def run_ours(args, rank, world, local_rank):
             "kernel_ms_per_step": {k: v[0] / max(args.steps, 1) for k, v in prof.items() if v[1]},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / e2e_steps, "steps": e2e_steps,
+                    "kernel_ms_per_chunk_launch": e2e_prof,
+                    "h2d_copy_only_ms": ms_copy, "h2d_copy_only_gbs": h2d / ms_copy * 1e-6,
                     "api": "bear_cuda_process_batch (pinned host buffers)" if world == 1 else
                            "bear_cuda_process_batch (pinned host buffers) -> NCCL all-reduce of the partial mixes -> pinned host"},
             "gpu_launches": int(launches),
