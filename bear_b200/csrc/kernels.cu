@@ -91,6 +91,15 @@ __device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int l
   int ls = 0;
   for (; ls + 3 <= logM; ls += 3) {
     const int Ns = 1 << ls, Q = M >> 3;
+    // exp(-2 pi i r k / (8 Ns)), r = 1..7, from the per-pass table behind the first M entries:
+    // consecutive threads read consecutive entries (k is the low bits of j).  The twiddles of the
+    // thread's first butterfly are fetched ahead of the barrier, they do not depend on the data.
+    float2 w0[7];
+    if (ls > 0 && tid < Q) {
+      const float2 *w = tw + M + (Ns - 8) + (tid & (Ns - 1));
+#pragma unroll
+      for (int r = 1; r < 8; r++) w0[r - 1] = __ldg(w + (r - 1) * Ns);
+    }
     __syncthreads();
     for (int j = tid; j < Q; j += nthr) {
       const int k = j & (Ns - 1);
@@ -98,11 +107,14 @@ __device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int l
 #pragma unroll
       for (int r = 0; r < 8; r++) v[r] = a[padi(j + r * Q)];
       if (ls > 0) {
-        // exp(-2 pi i r k / (8 Ns)), r = 1..7, from the per-pass table behind the first M entries:
-        // consecutive threads read consecutive entries (k is the low bits of j)
-        const float2 *w = tw + M + (Ns - 8) + k;
+        if (j == tid) {
 #pragma unroll
-        for (int r = 1; r < 8; r++) v[r] = twid<INV>(v[r], __ldg(w + (r - 1) * Ns));
+          for (int r = 1; r < 8; r++) v[r] = twid<INV>(v[r], w0[r - 1]);
+        } else {
+          const float2 *w = tw + M + (Ns - 8) + k;
+#pragma unroll
+          for (int r = 1; r < 8; r++) v[r] = twid<INV>(v[r], __ldg(w + (r - 1) * Ns));
+        }
       }
       dft8<INV>(v);
       const int j0 = ((j - k) << 3) + k;
@@ -532,13 +544,23 @@ __global__ void decorrelate_kernel(Layout p, int T)
   float2 *a = sm, *b = sm + M + (M >> 3);
   const int l = blockIdx.x % p.L, k = p.k0 + blockIdx.x / p.L;
   const int tid = threadIdx.x, nthr = blockDim.x;
-  for (int n = tid; n < M; n += nthr) {
-    float2 z = make_float2(0.f, 0.f);
+  // window [block k-1 | block k] of the diffuse bus (sum of the partials), eight loads in flight per
+  // thread before the first one is used
+  for (int n0 = tid; n0 < M; n0 += 8 * nthr) {
+    float2 z[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) z[i] = make_float2(0.f, 0.f);
     for (int s = 0; s < p.S; s++) {
-      const float2 v = reinterpret_cast<const float2 *>(p.qdif + ((size_t)s * p.L + l) * p.cs + (size_t)k * p.B)[n];
-      z.x += v.x; z.y += v.y;
+      const float2 *src = reinterpret_cast<const float2 *>(p.qdif + ((size_t)s * p.L + l) * p.cs + (size_t)k * p.B);
+      float2 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) v[i] = n0 + i * nthr < M ? src[n0 + i * nthr] : make_float2(0.f, 0.f);
+#pragma unroll
+      for (int i = 0; i < 8; i++) { z[i].x += v[i].x; z[i].y += v[i].y; }
     }
-    a[padi(n)] = z;
+#pragma unroll
+    for (int i = 0; i < 8; i++)
+      if (n0 + i * nthr < M) a[padi(n0 + i * nthr)] = z[i];
   }
   float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw);
   float2 *o = (z == a) ? b : a;
