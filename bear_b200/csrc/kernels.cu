@@ -16,6 +16,8 @@
 //   carry_kernel      moves histories / table state to the front for the next call
 #include "kernels.cuh"
 
+#include <type_traits>
+
 namespace bearcuda {
 
 // ----------------------------------------------------------------------------------------------
@@ -160,6 +162,95 @@ template <bool INV>
 __device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int logM, const float2 *__restrict__ tw)
 {
   return fft_shared<INV>(a, b, M, logM, tw, threadIdx.x, blockDim.x);
+}
+
+// The same transform with length and group size known at compile time (the per-period kernels are
+// instantiated per period size): the passes unroll, and because M/8 and Ns >= 8 are multiples of 8
+// the padded index of element j + r*stride is padi(j) + r*(stride + stride/8), a constant offset
+// from one base address per butterfly instead of eight index computations.
+template <bool INV, int LOGM, int NTHR>
+__device__ __forceinline__ float2 *fft_shared_c(float2 *a, float2 *b, const float2 *__restrict__ tw, int tid)
+{
+  constexpr int M = 1 << LOGM, Q = M >> 3, QP = Q + (Q >> 3);
+  constexpr int NP = LOGM / 3, REM = LOGM % 3;
+  static_assert(LOGM >= 6, "constant-offset addressing needs M/8 to be a multiple of 8");
+#pragma unroll
+  for (int pass = 0; pass < NP; pass++) {
+    const int Ns = 1 << (3 * pass), NsP = Ns + (Ns >> 3);
+    float2 w0[7];
+    if (pass > 0 && tid < Q) {
+      const float2 *w = tw + M + (Ns - 8) + (tid & (Ns - 1));
+#pragma unroll
+      for (int r = 1; r < 8; r++) w0[r - 1] = __ldg(w + (r - 1) * Ns);
+    }
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < (Q + NTHR - 1) / NTHR; it++) {
+      const int j = tid + it * NTHR;
+      if (Q % NTHR == 0 || j < Q) {
+        const int k = j & (Ns - 1);
+        float2 v[8];
+        const float2 *ap = a + padi(j);
+#pragma unroll
+        for (int r = 0; r < 8; r++) v[r] = ap[r * QP];
+        if (pass > 0) {
+          if (it == 0) {
+#pragma unroll
+            for (int r = 1; r < 8; r++) v[r] = twid<INV>(v[r], w0[r - 1]);
+          } else {
+            const float2 *w = tw + M + (Ns - 8) + k;
+#pragma unroll
+            for (int r = 1; r < 8; r++) v[r] = twid<INV>(v[r], __ldg(w + (r - 1) * Ns));
+          }
+        }
+        dft8<INV>(v);
+        float2 *bp = b + padi(((j - k) << 3) + k);
+#pragma unroll
+        for (int r = 0; r < 8; r++) bp[pass == 0 ? r : r * NsP] = v[r];   // pass 0: padi(8j + r) = 9j + r
+      }
+    }
+    float2 *t = a; a = b; b = t;
+  }
+  constexpr int ls = 3 * NP, Ns = 1 << ls;
+  if constexpr (REM == 2) {
+    constexpr int Q4 = M >> 2, Q4P = Q4 + (Q4 >> 3), NsP = Ns + (Ns >> 3);
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < (Q4 + NTHR - 1) / NTHR; it++) {
+      const int j = tid + it * NTHR;
+      if (Q4 % NTHR == 0 || j < Q4) {
+        const int k = j & (Ns - 1);
+        const float2 *ap = a + padi(j);
+        float2 v0 = ap[0], v1 = ap[Q4P], v2 = ap[2 * Q4P], v3 = ap[3 * Q4P];
+        const int q = k << (LOGM - 1 - ls);
+        v1 = twid<INV>(v1, ldtw(tw, q, M)); v2 = twid<INV>(v2, ldtw(tw, 2 * q, M)); v3 = twid<INV>(v3, ldtw(tw, 3 * q, M));
+        float2 x0, x1, x2, x3;
+        dft4<INV>(v0, v1, v2, v3, x0, x1, x2, x3);
+        float2 *bp = b + padi(((j - k) << 2) + k);
+        bp[0] = x0; bp[NsP] = x1; bp[2 * NsP] = x2; bp[3 * NsP] = x3;
+      }
+    }
+    float2 *t = a; a = b; b = t;
+  } else if constexpr (REM == 1) {
+    constexpr int Hh = M >> 1, HhP = Hh + (Hh >> 3), NsP = Ns + (Ns >> 3);
+    __syncthreads();
+#pragma unroll
+    for (int it = 0; it < (Hh + NTHR - 1) / NTHR; it++) {
+      const int j = tid + it * NTHR;
+      if (Hh % NTHR == 0 || j < Hh) {
+        const int k = j & (Ns - 1);
+        const float2 *ap = a + padi(j);
+        const float2 v0 = ap[0];
+        const float2 v1 = twid<INV>(ap[HhP], ldtw(tw, k << (LOGM - ls), M));
+        float2 *bp = b + padi(((j - k) << 1) + k);
+        bp[0] = cadd(v0, v1);
+        bp[NsP] = csub(v0, v1);
+      }
+    }
+    float2 *t = a; a = b; b = t;
+  }
+  __syncthreads();
+  return a;
 }
 
 // real-FFT split: Z = FFT_M(x[2n] + i x[2n+1]);  X[k], X[M-k] of the length-2M real transform
@@ -533,17 +624,34 @@ void launch_hoa_mix(const Layout &p, int T, cudaStream_t st)
   hoa_mix_kernel<<<T * p.B / kMixTile, kMixTile, 0, st>>>(p, T);
 }
 
+// The per-period FFT kernels are compiled once per supported period size (128 .. 4096).
+template <class F>
+static void dispatch_logb(int logB, F &&f)
+{
+  switch (logB) {
+    case 7: f(std::integral_constant<int, 7>{}); break;
+    case 8: f(std::integral_constant<int, 8>{}); break;
+    case 9: f(std::integral_constant<int, 9>{}); break;
+    case 10: f(std::integral_constant<int, 10>{}); break;
+    case 11: f(std::integral_constant<int, 11>{}); break;
+    case 12: f(std::integral_constant<int, 12>{}); break;
+    default: break;   // bear_cuda_create rejects other period sizes
+  }
+}
+
 // ----------------------------------------------------------------------------------------------
 // decorrelate_kernel: w[l] = dec[l] (*) q[l], one partition overlap-save (dsp.cpp:61-72,132-135).
 // grid: T*L (l fastest); block: B/4; smem 2*B float2.
 // ----------------------------------------------------------------------------------------------
+template <int LOGB>
 __global__ void decorrelate_kernel(Layout p, int T)
 {
   extern __shared__ float2 sm[];
-  const int M = p.B;
+  constexpr int M = 1 << LOGB, NTHR = (M >> 3) < 32 ? 32 : (M >> 3);
   float2 *a = sm, *b = sm + M + (M >> 3);
   const int l = blockIdx.x % p.L, k = p.k0 + blockIdx.x / p.L;
-  const int tid = threadIdx.x, nthr = blockDim.x;
+  const int tid = threadIdx.x;
+  constexpr int nthr = NTHR;
   // window [block k-1 | block k] of the diffuse bus (sum of the partials), eight loads in flight per
   // thread before the first one is used
   for (int n0 = tid; n0 < M; n0 += 8 * nthr) {
@@ -562,7 +670,7 @@ __global__ void decorrelate_kernel(Layout p, int T)
     for (int i = 0; i < 8; i++)
       if (n0 + i * nthr < M) a[padi(n0 + i * nthr)] = z[i];
   }
-  float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw);
+  float2 *z = fft_shared_c<false, LOGB, NTHR>(a, b, p.tw, tid);
   float2 *o = (z == a) ? b : a;
   const float2 *h = p.h_dec + (size_t)l * M;
   for (int kk = tid; kk <= M / 2; kk += nthr) {
@@ -581,15 +689,16 @@ __global__ void decorrelate_kernel(Layout p, int T)
       o[padi(M - kk)] = zm;
     }
   }
-  float2 *y = fft_shared<true>(o, z, M, p.logB, p.tw);
+  float2 *y = fft_shared_c<true, LOGB, NTHR>(o, z, p.tw, tid);
   float2 *dst = reinterpret_cast<float2 *>(p.w + (size_t)l * p.ws + p.B + p.hist + (size_t)k * p.B);
   for (int n = tid; n < M / 2; n += nthr) dst[n] = y[padi(M / 2 + n)];
 }
 
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
 {
-  int threads = p.B / 8 < 32 ? 32 : p.B / 8;
-  decorrelate_kernel<<<T * p.L, threads, fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T);
+  const int threads = p.B / 8 < 32 ? 32 : p.B / 8;
+  const size_t smem = fft_smem_floats2(p.B) * sizeof(float2);
+  dispatch_logb(p.logB, [&](auto lb) { decorrelate_kernel<decltype(lb)::value><<<T * p.L, threads, smem, st>>>(p, T); });
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -606,12 +715,13 @@ void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
 // fractional-delay gathers read are first staged in shared memory with 16-byte cp.async copies.
 // grid: T * (L + ceil(A/2)) (unit fastest); block: 2 * B/8.
 // ----------------------------------------------------------------------------------------------
+template <int LOGB>
 __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
 {
   extern __shared__ __align__(16) float2 sm[];
-  const int M = p.B;
+  constexpr int M = 1 << LOGB, NTHR = (M >> 3) < 32 ? 32 : (M >> 3);
   const int unit = blockIdx.x % nunits, k = p.k0 + blockIdx.x / nunits;
-  const int nthr = blockDim.x >> 1;
+  constexpr int nthr = NTHR;                                          // threads per group (blockDim.x / 2)
   const int g = threadIdx.x >= nthr, tid = threadIdx.x - g * nthr;   // group 0 / 1
   const int FB = M + (M >> 3);                                       // padded FFT buffer, float2
   float2 *a = sm + (size_t)g * 2 * FB, *b = a + FB;
@@ -694,7 +804,7 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
         a[padi(n)] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
     }
   }
-  float2 *z = fft_shared<false>(a, b, M, p.logB, p.tw, tid, nthr);
+  float2 *z = fft_shared_c<false, LOGB, NTHR>(a, b, p.tw, tid);
   if (!active) return;
   const int slot = (p.fdl_head + k) % p.R;
   float2 *dst = p.fdl + ((size_t)ch * p.R + slot) * M;
@@ -725,10 +835,13 @@ static size_t bus_fdl_smem_bytes(int B, int hist, int S)
 
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
 {
-  int threads = 2 * (p.B / 8 < 32 ? 32 : p.B / 8);
-  int nunits = p.L + (p.H > 0 ? (p.A + 1) / 2 : 0);
-  bus_fdl_kernel<<<T * nunits, threads, bus_fdl_smem_bytes(p.B, p.hist, p.S), st>>>(p, T, nunits,
-                                                                                    bus_fdl_stage_direct(p.B, p.hist, p.S) ? 1 : 0);
+  const int threads = 2 * (p.B / 8 < 32 ? 32 : p.B / 8);
+  const int nunits = p.L + (p.H > 0 ? (p.A + 1) / 2 : 0);
+  const size_t smem = bus_fdl_smem_bytes(p.B, p.hist, p.S);
+  const int stage = bus_fdl_stage_direct(p.B, p.hist, p.S) ? 1 : 0;
+  dispatch_logb(p.logB, [&](auto lb) {
+    bus_fdl_kernel<decltype(lb)::value><<<T * nunits, threads, smem, st>>>(p, T, nunits, stage);
+  });
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -841,15 +954,17 @@ void launch_cmac(const Layout &p, int T, cudaStream_t st)
 // (rcl::InterpolatingFirFilterMatrix with transitionSamples = period, dsp.cpp:73-87).
 // grid: 2T; block: B/4.
 // ----------------------------------------------------------------------------------------------
+template <int LOGB>
 __global__ void __launch_bounds__(512) ifft_out_kernel(Layout p, int T)
 {
   extern __shared__ float2 sm[];
-  const int M = p.B;
+  constexpr int M = 1 << LOGB;
+  constexpr int NTHR = (M >> 2) < 32 ? 32 : ((M >> 2) > 256 ? 256 : (M >> 2));   // threads per group
   const int FB = M + (M >> 3);
   const int k = p.k0 + (blockIdx.x >> 1), e = blockIdx.x & 1;
   // two thread groups in lockstep: group 0 transforms the new-view spectrum, group 1 the old-view
   // one of a view-change period (idle otherwise, it only keeps the barriers company)
-  const int nthr = blockDim.x >> 1;
+  constexpr int nthr = NTHR;
   const int g = threadIdx.x >= nthr, tid = threadIdx.x - g * nthr;
   float2 *a = sm + (size_t)g * 2 * FB, *b = a + FB;
   const bool xf = p.view[k + 1] != p.view[k];
@@ -884,7 +999,7 @@ __global__ void __launch_bounds__(512) ifft_out_kernel(Layout p, int T)
       }
     }
   }
-  float2 *z = fft_shared<true>(a, b, M, p.logB, p.tw, tid, nthr);
+  float2 *z = fft_shared_c<true, LOGB, NTHR>(a, b, p.tw, tid);
   // old view faded out (in place), then the new view faded in on top of it
   if (g == 1 && xf) {
     for (int n = tid; n < M / 2; n += nthr) {
@@ -914,8 +1029,9 @@ void launch_ifft_out(const Layout &p, int T, cudaStream_t st)
 {
   // B/4 threads per group (the FFT passes use the first B/8 of them, the partial-sum and output
   // loops all): a single period is two CTAs, so the sum over the partial spectra is spread wide
-  int threads = 2 * (p.B / 4 < 32 ? 32 : (p.B / 4 > 256 ? 256 : p.B / 4));
-  ifft_out_kernel<<<2 * T, threads, 2 * fft_smem_floats2(p.B) * sizeof(float2), st>>>(p, T);
+  const int threads = 2 * (p.B / 4 < 32 ? 32 : (p.B / 4 > 256 ? 256 : p.B / 4));
+  const size_t smem = 2 * fft_smem_floats2(p.B) * sizeof(float2);
+  dispatch_logb(p.logB, [&](auto lb) { ifft_out_kernel<decltype(lb)::value><<<2 * T, threads, smem, st>>>(p, T); });
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -1124,25 +1240,40 @@ cudaError_t static_scratch_pointer(float2 **out)
 
 size_t mix_smem_bytes(int hist) { return (size_t)kMixChunk * (hist + kMixTile) * sizeof(float); }
 
+static int ilog2(int v)
+{
+  int l = 0;
+  while ((1 << l) < v) l++;
+  return l;
+}
+
 cudaError_t configure_mix(int hist, int B)
 {
   cudaError_t e = cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
   if (e != cudaSuccess) return e;
-  return cudaFuncSetAttribute(bus_fdl_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                              (int)bus_fdl_smem_bytes(B, hist, 1));
+  dispatch_logb(ilog2(B), [&](auto lb) {
+    e = cudaFuncSetAttribute(bus_fdl_kernel<decltype(lb)::value>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)bus_fdl_smem_bytes(B, hist, 1));
+  });
+  return e;
 }
 
 cudaError_t configure_kernels(int B)
 {
   const int smem = fft_smem_floats2(B) * (int)sizeof(float2);
+  cudaError_t e = cudaSuccess;
   if (smem > 48 * 1024) {
-    cudaError_t e;
     if ((e = cudaFuncSetAttribute(filter_fft_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
-    if ((e = cudaFuncSetAttribute(decorrelate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem))) return e;
+    dispatch_logb(ilog2(B), [&](auto lb) {
+      e = cudaFuncSetAttribute(decorrelate_kernel<decltype(lb)::value>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    });
+    if (e) return e;
   }
   if (2 * smem > 48 * 1024)   // two transforms per CTA
-    return cudaFuncSetAttribute(ifft_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * smem);
-  return cudaSuccess;
+    dispatch_logb(ilog2(B), [&](auto lb) {
+      e = cudaFuncSetAttribute(ifft_out_kernel<decltype(lb)::value>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * smem);
+    });
+  return e;
 }
 
 }  // namespace bearcuda

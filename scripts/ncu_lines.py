@@ -50,13 +50,13 @@ def line_table(kernel_re):
             last, i = mangled[j:j + n], j + n
         return last
     names = [k for k in table if re.fullmatch(kernel_re, base(k))]
-    if len(names) != 1:
-        raise SystemExit(f"kernel regex matches {names}")
-    return table[names[0]]
+    if not names:
+        raise SystemExit(f"kernel regex matches nothing in {sorted(table)}")
+    return [table[n] for n in names]   # one per template instantiation
 
 
 def sass_page(report, kernel_re):
-    out = subprocess.run(["ncu", "-i", report, "--page", "source", "--csv", "--kernel-name", f"regex:^{kernel_re}$"],
+    out = subprocess.run(["ncu", "-i", report, "--page", "source", "--csv", "--kernel-name", f"regex:^{kernel_re}(<.*>)?$"],
                          check=True, capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
     heads = [i for i, r in enumerate(rows) if r and r[0] == "Address"]
@@ -71,10 +71,11 @@ def sass_page(report, kernel_re):
 def main():
     report, kre = sys.argv[1], sys.argv[2]
     top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-    table = line_table(kre)
     body, ie, smp, stall_cols = sass_page(report, kre)
-    if len(table) != len(body):
-        raise SystemExit(f"library has {len(table)} instructions, report {len(body)}: not the same build")
+    tables = [t for t in line_table(kre) if len(t) == len(body)]
+    if not tables:
+        raise SystemExit(f"no instantiation in the library has the report's {len(body)} instructions: not the same build")
+    table = tables[0]
     samples, insts, stalls = collections.Counter(), collections.Counter(), collections.defaultdict(collections.Counter)
     for (line, _), r in zip(table, body):
         samples[line] += int(r[smp])
