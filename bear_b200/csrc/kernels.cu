@@ -861,11 +861,14 @@ void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
 __device__ __forceinline__ void cmac2(float4 &acc, const float4 x, const float4 h, const bool packed0)
 {
   // bin 0 of the packed spectrum holds (DC, Nyquist), both real: two real products instead of a complex one
+  // order of the two products of each component as in cmac2_packed: x.re * h first, then x.im * (i h)
   acc.x = fmaf(x.x, h.x, acc.x);
-  acc.y = fmaf(x.y, packed0 ? h.y : h.x, acc.y);
-  if (!packed0) {
-    acc.x = fmaf(-x.y, h.y, acc.x);
+  if (packed0) {
+    acc.y = fmaf(x.y, h.y, acc.y);
+  } else {
     acc.y = fmaf(x.x, h.y, acc.y);
+    acc.x = fmaf(-x.y, h.y, acc.x);
+    acc.y = fmaf(x.y, h.x, acc.y);
   }
   acc.z = fmaf(x.z, h.z, acc.z); acc.z = fmaf(-x.w, h.w, acc.z);
   acc.w = fmaf(x.z, h.w, acc.w); acc.w = fmaf(x.w, h.z, acc.w);
@@ -878,9 +881,13 @@ __device__ __forceinline__ float4 ldg_stream(const float4 *p)
   return v;
 }
 
-template <bool DO_A, bool DO_B>
-__device__ __forceinline__ void cmac_body(const Layout &p, int j, int e, int ks, int pair, int v, float4 &accA,
-                                          float4 &accB)
+// Partial spectra of up to CNT periods that use the same view: the new-view spectrum of each period
+// and (HAS_B) the old-view spectrum of the period after it.  One filter load serves all of them.
+// Flags are per CTA, not per period: a period of the item that does not need one of its two spectra
+// still accumulates it (its result is not stored), so the inner loop has no branches.
+template <int CNT, bool HAS_B>
+__device__ __forceinline__ void cmac_item(const Layout &p, const int (&j)[kCmacGroup], int e, int ks, int pair, int v,
+                                          int T, unsigned maskA, unsigned maskB)
 {
   const int B = p.B, P = p.P, L = p.L, R = p.R;
   const int nunits = L + (p.H > 0 ? 1 : 0);
@@ -888,64 +895,350 @@ __device__ __forceinline__ void cmac_body(const Layout &p, int j, int e, int ks,
   const int u0 = ks * per, u1 = min(nunits, u0 + per);
   const bool packed0 = pair == 0;
   const int hB = B >> 1;                                   // float4 per spectrum
-  int slotA = p.fdl_head + j;                              // ring slot of period j (j >= -1)
-  slotA = slotA < 0 ? slotA + R : (slotA >= R ? slotA - R : slotA);
-  const int slotB = slotA + 1 == R ? 0 : slotA + 1;        // period j+1
+  float4 accA[CNT], accB[HAS_B ? CNT : 1];
+  int slotA[CNT];
+#pragma unroll
+  for (int g = 0; g < CNT; g++) {
+    accA[g] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (HAS_B) accB[g] = accA[g];
+    int sl = p.fdl_head + j[g];                            // ring slot of period j (j >= -1)
+    slotA[g] = sl < 0 ? sl + R : (sl >= R ? sl - R : sl);
+  }
   const float4 *fdl4 = reinterpret_cast<const float4 *>(p.fdl) + pair;
   for (int u = u0; u < u1; u++) {
     if (u < L) {
       const int ch = 2 * u + e;
       const float4 *x = fdl4 + (size_t)ch * R * hB;
       const float4 *h = reinterpret_cast<const float4 *>(p.h_brir) + ((size_t)(v * 2 * L + ch) * P) * hB + pair;
-      float4 xb = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (DO_B) xb = __ldg(x + (size_t)slotB * hB);
-      int slot = slotA;
-#pragma unroll 6
+      float4 xb[HAS_B ? CNT : 1];
+      int slot[CNT];
+#pragma unroll
+      for (int g = 0; g < CNT; g++) {
+        slot[g] = slotA[g];
+        if (HAS_B) xb[g] = __ldg(x + (size_t)(slotA[g] + 1 == R ? 0 : slotA[g] + 1) * hB);   // period j+1
+      }
+#pragma unroll(CNT == 1 ? 6 : (CNT <= 3 ? 3 : 2))
       for (int part = 0; part < P; part++) {
-        const float4 xa = __ldg(x + (size_t)slot * hB);
         const float4 hv = ldg_stream(h + (size_t)part * hB);
-        if (DO_A) cmac2(accA, xa, hv, packed0);
-        if (DO_B) cmac2(accB, xb, hv, packed0);
-        xb = xa;
-        slot = slot == 0 ? R - 1 : slot - 1;
+#pragma unroll
+        for (int g = 0; g < CNT; g++) {
+          const float4 xa = __ldg(x + (size_t)slot[g] * hB);
+          cmac2(accA[g], xa, hv, packed0);
+          if (HAS_B) { cmac2(accB[g], xb[g], hv, packed0); xb[g] = xa; }
+          slot[g] = slot[g] == 0 ? R - 1 : slot[g] - 1;
+        }
       }
     } else {
       for (int am = 0; am < p.A; am++) {
         const float4 *x = fdl4 + (size_t)(2 * L + am) * R * hB;
         const float4 hv = __ldg(reinterpret_cast<const float4 *>(p.h_hoa) + ((size_t)am * 2 + e) * hB + pair);
-        if (DO_A) cmac2(accA, __ldg(x + (size_t)slotA * hB), hv, packed0);
-        if (DO_B) cmac2(accB, __ldg(x + (size_t)slotB * hB), hv, packed0);
+#pragma unroll
+        for (int g = 0; g < CNT; g++) {
+          cmac2(accA[g], __ldg(x + (size_t)slotA[g] * hB), hv, packed0);
+          if (HAS_B) cmac2(accB[g], __ldg(x + (size_t)(slotA[g] + 1 == R ? 0 : slotA[g] + 1) * hB), hv, packed0);
+        }
       }
+    }
+  }
+  // partial spectra are scratch of this launch: indexed by the period within the launch
+  float4 *y = reinterpret_cast<float4 *>(p.ypart) + pair;
+#pragma unroll
+  for (int g = 0; g < CNT; g++) {
+    const int jl = j[g] - p.k0;
+    if (maskA >> g & 1) y[((((size_t)jl * 2 + e) * 2 + 0) * p.KS + ks) * hB] = accA[g];
+    if (HAS_B && (maskB >> g & 1)) y[((((size_t)(jl + 1) * 2 + e) * 2 + 1) * p.KS + ks) * hB] = accB[g];
+  }
+}
+
+// The same for the grouped kernel, with the operands prefetched through shared memory: every thread
+// copies its own 16-byte pieces (one filter piece + CNT delay-line pieces per term) with cp.async
+// into a private ring of kCmacSlots pieces and reads them back itself, so no barrier is needed and
+// loads in flight cost no registers.  Terms of one loudspeaker: part = -1 (delay-line slot of period
+// j+1, the first operand of the old-view accumulation) then part = 0 .. P-1.
+// The accumulation uses packed FMAs: acc(re,im) += x.re * (h.re,h.im) + x.im * (-h.im,h.re), two
+// FFMA2 per bin.  Only the warp that owns packed bin 0 (DC, Nyquist) takes the scalar path.
+constexpr int kCmacSlots = 21;     // float4 pieces per thread
+constexpr int kCmacRingStride = 128;   // float4 between the pieces of one thread (= max threads per CTA)
+struct CmacAcc { f32x2 lo, hi; };  // bins 2*pair and 2*pair+1
+
+__device__ __forceinline__ void cmac2_packed(CmacAcc &acc, const float4 x, const f32x2 h01, const f32x2 r01,
+                                             const f32x2 h23, const f32x2 r23)
+{
+  acc.lo = fma2(splat2(x.x), h01, acc.lo); acc.lo = fma2(splat2(x.y), r01, acc.lo);
+  acc.hi = fma2(splat2(x.z), h23, acc.hi); acc.hi = fma2(splat2(x.w), r23, acc.hi);
+}
+__device__ __forceinline__ void cmac2_scalar(CmacAcc &acc, const float4 x, const float4 h, const bool packed0)
+{
+  float4 a;
+  unpack2(acc.lo, a.x, a.y); unpack2(acc.hi, a.z, a.w);
+  cmac2(a, x, h, packed0);
+  acc.lo = pack2(a.x, a.y); acc.hi = pack2(a.z, a.w);
+}
+
+// delay-line pieces g = G .. CNT-1 of one term (the shared-memory offset is an immediate)
+template <int G, int CNT>
+__device__ __forceinline__ void cmac_request_fdl(unsigned pdst, const float4 *px, int (&poff)[CNT], int hB, int ringlen)
+{
+  if constexpr (G < CNT) {
+    asm volatile("cp.async.cg.shared.global [%0+%2], [%1], 16;" ::"r"(pdst), "l"(px + poff[G]),
+                 "n"((1 + G) * kCmacRingStride * (int)sizeof(float4)) : "memory");
+    poff[G] -= hB;
+    if (poff[G] < 0) poff[G] += ringlen;
+    cmac_request_fdl<G + 1, CNT>(pdst, px, poff, hB, ringlen);
+  }
+}
+
+template <int CNT, bool HAS_B>
+__device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[kCmacGroup], int e, int ks, int KS,
+                                               int pair, int v, unsigned maskA, unsigned maskB, float4 *ring)
+{
+  constexpr int W = 1 + CNT;                 // pieces per term
+  constexpr int S = kCmacSlots / W;          // stages
+  constexpr int RS = kCmacRingStride;
+  constexpr unsigned kStageBytes = W * RS * sizeof(float4);
+  const int B = p.B, P = p.P, L = p.L, R = p.R;
+  const int nunits = L + (p.H > 0 ? 1 : 0);
+  const int per = (nunits + KS - 1) / KS;
+  const int u0 = ks * per, u1 = min(nunits, u0 + per), ub = min(u1, L);   // [u0, ub): BRIR units
+  const bool packed0 = pair == 0;
+  const bool scalar_warp = blockIdx.x == 0 && threadIdx.x < 32;           // the warp with packed bin 0
+  const int hB = B >> 1;
+  CmacAcc accA[CNT], accB[HAS_B ? CNT : 1];
+  float4 xb[HAS_B ? CNT : 1];
+  int slotA[CNT];
+#pragma unroll
+  for (int g = 0; g < CNT; g++) {
+    accA[g].lo = accA[g].hi = 0ull;
+    if (HAS_B) { accB[g] = accA[g]; xb[g] = make_float4(0.f, 0.f, 0.f, 0.f); }
+    int sl = p.fdl_head + j[g];
+    slotA[g] = sl < 0 ? sl + R : (sl >= R ? sl - R : sl);
+  }
+  const float4 *fdl4 = reinterpret_cast<const float4 *>(p.fdl) + pair;
+  constexpr int first_part = HAS_B ? -1 : 0;
+  const int tpu = P - first_part;                              // terms per unit
+  const int nterms = (ub - u0) * tpu;
+  // ---- producer: walks (unit, part) one term ahead of the consumer by S-1 stages
+  const int ringlen = R * hB;                                  // float4 per delay-line channel
+  int poff[CNT];                                               // float4 offset of the next delay-line piece
+#pragma unroll
+  for (int g = 0; g < CNT; g++) {
+    const int sl = HAS_B ? (slotA[g] + 1 == R ? 0 : slotA[g] + 1) : slotA[g];
+    poff[g] = sl * hB;
+  }
+  const float4 *px = fdl4 + (size_t)(2 * u0 + e) * ringlen;
+  const float4 *ph = reinterpret_cast<const float4 *>(p.h_brir) + ((size_t)(v * 2 * L + 2 * u0 + e) * P) * hB + pair;
+  const unsigned ring0 = (unsigned)__cvta_generic_to_shared(ring + threadIdx.x);
+  unsigned pdst = ring0;
+  int pstage = 0, ppart = first_part, pt = 0;
+  auto request = [&]() {
+    if (pt < nterms) {
+      if (ppart >= 0) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pdst), "l"(ph) : "memory");
+        ph += hB;
+      }
+      cmac_request_fdl<0, CNT>(pdst, px, poff, hB, ringlen);
+      pt++;
+      pdst += kStageBytes;
+      if (++pstage == S) { pstage = 0; pdst = ring0; }
+      if (++ppart == P) {                                      // next loudspeaker, same ear
+        ppart = first_part;
+        px += 2 * (size_t)ringlen;
+        ph += (size_t)P * hB;
+#pragma unroll
+        for (int g = 0; g < CNT; g++) {
+          poff[g] += tpu * hB;
+          if (poff[g] >= ringlen) poff[g] -= ringlen;
+        }
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");
+  };
+#pragma unroll 1
+  for (int i = 0; i < S - 1; i++) request();
+  // ---- consumer
+  const float4 *csrc = ring + threadIdx.x;
+  int cstage = 0, part = first_part;
+#pragma unroll 1
+  for (int t = 0; t < nterms; t++) {
+    request();
+    // "memory": the reads below must not be moved above the wait (there is no barrier to stop them)
+    asm volatile("cp.async.wait_group %0;" ::"n"(S - 1) : "memory");
+    if (HAS_B && part < 0) {
+#pragma unroll
+      for (int g = 0; g < CNT; g++) xb[g] = csrc[(1 + g) * RS];
+    } else {
+      const float4 hv = csrc[0];
+      if (scalar_warp) {
+#pragma unroll
+        for (int g = 0; g < CNT; g++) {
+          const float4 xa = csrc[(1 + g) * RS];
+          cmac2_scalar(accA[g], xa, hv, packed0);
+          if (HAS_B) { cmac2_scalar(accB[g], xb[g], hv, packed0); xb[g] = xa; }
+        }
+      } else {
+        const f32x2 h01 = pack2(hv.x, hv.y), r01 = pack2(-hv.y, hv.x), h23 = pack2(hv.z, hv.w), r23 = pack2(-hv.w, hv.z);
+#pragma unroll
+        for (int g = 0; g < CNT; g++) {
+          const float4 xa = csrc[(1 + g) * RS];
+          cmac2_packed(accA[g], xa, h01, r01, h23, r23);
+          if (HAS_B) { cmac2_packed(accB[g], xb[g], h01, r01, h23, r23); xb[g] = xa; }
+        }
+      }
+    }
+    if (++part == P) part = first_part;
+    csrc += W * RS;
+    if (++cstage == S) { cstage = 0; csrc = ring + threadIdx.x; }
+  }
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+  if (u0 <= L && L < u1) {   // the HOA decode unit (index L) is in this split
+    for (int am = 0; am < p.A; am++) {
+      const float4 *x = fdl4 + (size_t)(2 * L + am) * ringlen;
+      const float4 hv = __ldg(reinterpret_cast<const float4 *>(p.h_hoa) + ((size_t)am * 2 + e) * hB + pair);
+#pragma unroll
+      for (int g = 0; g < CNT; g++) {
+        cmac2_scalar(accA[g], __ldg(x + (size_t)slotA[g] * hB), hv, packed0);
+        if (HAS_B) cmac2_scalar(accB[g], __ldg(x + (size_t)(slotA[g] + 1 == R ? 0 : slotA[g] + 1) * hB), hv, packed0);
+      }
+    }
+  }
+  float4 *y = reinterpret_cast<float4 *>(p.ypart) + pair;
+#pragma unroll
+  for (int g = 0; g < CNT; g++) {
+    const int jl = j[g] - p.k0;
+    float4 a;
+    if (maskA >> g & 1) {
+      unpack2(accA[g].lo, a.x, a.y); unpack2(accA[g].hi, a.z, a.w);
+      y[((((size_t)jl * 2 + e) * 2 + 0) * KS + ks) * hB] = a;
+    }
+    if (HAS_B && (maskB >> g & 1)) {
+      unpack2(accB[g].lo, a.x, a.y); unpack2(accB[g].hi, a.z, a.w);
+      y[((((size_t)(jl + 1) * 2 + e) * 2 + 1) * KS + ks) * hB] = a;
     }
   }
 }
 
-__global__ void __launch_bounds__(128) cmac_kernel(Layout p, int T)
+template <int CNT>
+__device__ __forceinline__ void cmac_item_pipe_flags(const Layout &p, const int (&j)[kCmacGroup], int e, int ks, int KS,
+                                                     int pair, int v, unsigned maskA, unsigned maskB, float4 *ring)
+{
+  if (maskB) cmac_item_pipe<CNT, true>(p, j, e, ks, KS, pair, v, maskA, maskB, ring);
+  else cmac_item_pipe<CNT, false>(p, j, e, ks, KS, pair, v, maskA, maskB, ring);
+}
+
+template <int CNT>
+__device__ __forceinline__ void cmac_item_flags(const Layout &p, const int (&j)[kCmacGroup], int e, int ks, int pair,
+                                                int v, int T, unsigned maskA, unsigned maskB)
+{
+  if (maskB) cmac_item<CNT, true>(p, j, e, ks, pair, v, T, maskA, maskB);
+  else cmac_item<CNT, false>(p, j, e, ks, pair, v, T, maskA, maskB);
+}
+
+// GROUPED = false: item z is period k0 - 1 + z.  GROUPED = true: item z is entry z of the table
+// view_group_kernel made for this launch (up to kCmacGroup periods of one view).
+template <bool GROUPED>
+__global__ void __launch_bounds__(128, 4) cmac_kernel(Layout p, int T)
 {
   const int pair = blockIdx.x * blockDim.x + threadIdx.x;  // bins 2*pair, 2*pair+1
   const int ks = blockIdx.y;
-  const int j = p.k0 + (int)(blockIdx.z >> 1) - 1, e = blockIdx.z & 1;
-  const int v = p.view[j + 1];                              // view of period j (slot 0: previous call)
-  const bool doA = j >= p.k0;                               // earlier chunks already did their periods
-  const bool doB = j + 1 < p.k0 + T && p.view[j + 2] != v;   // period j+1 must be in this launch
-  if (!doA && !doB) return;
-  float4 accA = make_float4(0.f, 0.f, 0.f, 0.f), accB = accA;
-  if (doA && doB) cmac_body<true, true>(p, j, e, ks, pair, v, accA, accB);
-  else if (doA) cmac_body<true, false>(p, j, e, ks, pair, v, accA, accB);
-  else cmac_body<false, true>(p, j, e, ks, pair, v, accA, accB);
-  const size_t hB = p.B >> 1;
-  float4 *y = reinterpret_cast<float4 *>(p.ypart) + pair;
-  // partial spectra are scratch of this launch: indexed by the period within the launch
-  const int jl = j - p.k0;
-  if (doA) y[((((size_t)jl * 2 + e) * 2 + 0) * p.KS + ks) * hB] = accA;
-  if (doB) y[((((size_t)(jl + 1) * 2 + e) * 2 + 1) * p.KS + ks) * hB] = accB;
+  const int item = blockIdx.z >> 1, e = blockIdx.z & 1;
+  int j[kCmacGroup];
+  int cnt = 1;
+  int KS = p.KS;
+  if (GROUPED) {
+    // the builder decided how many of the launch's p.KS splits to use once it knew the item count
+    KS = p.grp_count[1];
+    if (item >= p.grp_count[0] || ks >= KS) return;
+    const int2 it = p.grp_items[item];
+    cnt = it.y;
+#pragma unroll
+    for (int g = 0; g < kCmacGroup; g++) j[g] = p.k0 - 1 + p.grp_sorted[it.x + min(g, cnt - 1)];
+  } else {
+#pragma unroll
+    for (int g = 0; g < kCmacGroup; g++) j[g] = p.k0 - 1 + item;
+  }
+  const int v = p.view[j[0] + 1];                           // view of period j (slot 0: previous call)
+  unsigned maskA = 0, maskB = 0;
+#pragma unroll
+  for (int g = 0; g < kCmacGroup; g++) {
+    if (g < cnt) {
+      if (j[g] >= p.k0) maskA |= 1u << g;                   // earlier launches already did their periods
+      if (j[g] + 1 < p.k0 + T && p.view[j[g] + 2] != v) maskB |= 1u << g;   // period j+1 must be in this launch
+    }
+  }
+  if (!maskA && !maskB) return;
+  if (!GROUPED) { cmac_item_flags<1>(p, j, e, ks, pair, v, T, maskA, maskB); return; }
+  extern __shared__ __align__(16) float4 cmac_ring[];
+  switch (cnt) {
+    case 1: cmac_item_pipe_flags<1>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+    case 2: cmac_item_pipe_flags<2>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+    case 3: cmac_item_pipe_flags<3>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+    case 4: cmac_item_pipe_flags<4>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+    case 5: cmac_item_pipe_flags<5>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+    default: cmac_item_pipe_flags<6>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+  }
+}
+static_assert(kCmacGroup == 6, "cmac_kernel dispatches on the item size");
+
+// view_group_kernel: the periods k0-1 .. k0+n-1 of a launch sorted by view and cut into items of up
+// to kCmacGroup periods (counting sort in one CTA).  grp_sorted holds period indices relative to
+// k0-1, grp_items (first, count) pairs into it, grp_count the number of items.
+// grid: 1; block: 1024; dynamic shared memory: 3*V + 2048 ints.
+__global__ void __launch_bounds__(1024) view_group_kernel(Layout p, int n)
+{
+  extern __shared__ int gsh[];
+  const int V = p.V, tid = threadIdx.x;
+  int *cnt = gsh, *off = gsh + V, *ioff = gsh + 2 * V, *scanA = gsh + 3 * V, *scanB = scanA + 1024;
+  const int32_t *view = p.view + p.k0;                       // view[i] = view of period k0 - 1 + i
+  for (int v = tid; v < V; v += 1024) cnt[v] = 0;
+  __syncthreads();
+  for (int i = tid; i <= n; i += 1024) atomicAdd(&cnt[view[i]], 1);
+  __syncthreads();
+  // exclusive scans over the views of the counts and of the items per view
+  const int cpt = (V + 1023) / 1024, v0 = tid * cpt, v1 = min(V, v0 + cpt);
+  int sumc = 0, sumi = 0;
+  for (int v = v0; v < v1; v++) { sumc += cnt[v]; sumi += (cnt[v] + kCmacGroup - 1) / kCmacGroup; }
+  scanA[tid] = sumc; scanB[tid] = sumi;
+  __syncthreads();
+  for (int d = 1; d < 1024; d <<= 1) {
+    const int a = tid >= d ? scanA[tid - d] : 0, b = tid >= d ? scanB[tid - d] : 0;
+    __syncthreads();
+    scanA[tid] += a; scanB[tid] += b;
+    __syncthreads();
+  }
+  int oc = scanA[tid] - sumc, oi = scanB[tid] - sumi;
+  for (int v = v0; v < v1; v++) {
+    off[v] = oc; ioff[v] = oi;
+    const int c = cnt[v], ni = (c + kCmacGroup - 1) / kCmacGroup;
+    for (int s = 0; s < ni; s++) p.grp_items[oi + s] = make_int2(oc + s * kCmacGroup, min(kCmacGroup, c - s * kCmacGroup));
+    oc += c; oi += ni;
+  }
+  if (tid == 1023) {
+    // splits: about 12 CTAs per SM over the items there turned out to be (at most the launch's p.KS)
+    const int nitems = scanB[1023];
+    const int threads = p.B / 2 < 128 ? p.B / 2 : 128;
+    const int base = (p.B / 2 / threads) * 2 * max(nitems, 1);
+    const int nunits = p.L + (p.H > 0 ? 1 : 0);
+    p.grp_count[0] = nitems;
+    p.grp_count[1] = max(1, min(min((12 * 148 + base - 1) / base, nunits), p.KS));
+  }
+  __syncthreads();
+  for (int i = tid; i <= n; i += 1024) p.grp_sorted[atomicAdd(&off[view[i]], 1)] = i;
 }
 
-void launch_cmac(const Layout &p, int T, cudaStream_t st)
+// Grouping pays when views repeat within the launch; it needs the view histogram in shared memory.
+bool cmac_groups_by_view(const Layout &p, int T) { return T >= 8 && p.V <= 2560 && p.grp_items != nullptr; }
+
+int launch_cmac(const Layout &p, int T, cudaStream_t st)
 {
   int threads = p.B / 2 < 128 ? p.B / 2 : 128;
   dim3 grid(p.B / 2 / threads, p.KS, 2 * (T + 1));
-  cmac_kernel<<<grid, threads, 0, st>>>(p, T);
+  if (cmac_groups_by_view(p, T)) {
+    view_group_kernel<<<1, 1024, (3 * p.V + 2048) * sizeof(int), st>>>(p, T);
+    cmac_kernel<true><<<grid, threads, (size_t)kCmacSlots * kCmacRingStride * sizeof(float4), st>>>(p, T);
+    return 2;
+  }
+  cmac_kernel<false><<<grid, threads, 0, st>>>(p, T);
+  return 1;
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -971,21 +1264,22 @@ __global__ void __launch_bounds__(512) ifft_out_kernel(Layout p, int T)
   const bool work = g == 0 || xf;
   const float invB = 1.0f / (float)p.B;
   float2 *dst = reinterpret_cast<float2 *>(p.out + (size_t)e * p.os + (size_t)k * p.B);
+  const int KS = p.ks_dev ? p.grp_count[1] : p.KS;
   if (work) {
-    const float2 *y = p.ypart + ((((size_t)(k - p.k0) * 2 + e) * 2 + g) * p.KS) * M;   // g = 1: old view
+    const float2 *y = p.ypart + ((((size_t)(k - p.k0) * 2 + e) * 2 + g) * KS) * M;   // g = 1: old view
     for (int kk = tid; kk <= M / 2; kk += nthr) {
       // partial spectra summed in order; the loads of four partials are issued together
       float2 xk = make_float2(0.f, 0.f), xm = xk;
       const int km = kk ? M - kk : 0;
       int s = 0;
-      for (; s + 4 <= p.KS; s += 4) {
+      for (; s + 4 <= KS; s += 4) {
         float2 u[4], v[4];
 #pragma unroll
         for (int i = 0; i < 4; i++) { u[i] = y[(size_t)(s + i) * M + kk]; v[i] = y[(size_t)(s + i) * M + km]; }
 #pragma unroll
         for (int i = 0; i < 4; i++) { xk.x += u[i].x; xk.y += u[i].y; xm.x += v[i].x; xm.y += v[i].y; }
       }
-      for (; s < p.KS; s++) {
+      for (; s < KS; s++) {
         const float2 u = y[(size_t)s * M + kk], v = y[(size_t)s * M + km];
         xk.x += u.x; xk.y += u.y; xm.x += v.x; xm.y += v.y;
       }

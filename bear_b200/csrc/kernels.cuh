@@ -8,6 +8,7 @@ namespace bearcuda {
 constexpr int kMaxSpeakers = 24;  // accumulator tile of the mix kernel (L <= 24)
 constexpr int kMixTile = 128;     // samples per CTA in the mix kernels
 constexpr int kMixChunk = 32;     // channels staged in shared memory per pass
+constexpr int kCmacGroup = 6;     // periods of one view that share a filter load in the cMAC kernel
 
 // Everything a kernel needs to find its data.  Passed by value (fits the 4 KB param space).
 struct Layout {
@@ -60,6 +61,11 @@ struct Layout {
   double fs_d, dec_delay_d;
   int front;
   int fdl_head;              // ring slot of block 0 of this call
+  // periods of a launch grouped by view (scratch of view_group_kernel / cmac_kernel)
+  int *grp_sorted;           // [Tmax + 1] period indices relative to k0 - 1, sorted by view
+  int2 *grp_items;           // [Tmax + 1] (first, count) into grp_sorted
+  int *grp_count;            // [2] number of items, cMAC splits in use (<= KS)
+  int ks_dev;                // this launch's number of splits is grp_count[1] (grouped launch), not KS
   int k0;                    // first period of this launch (a call may be issued in chunks)
 };
 
@@ -83,7 +89,8 @@ void launch_mix(const Layout &p, int T, cudaStream_t st);
 void launch_hoa_mix(const Layout &p, int T, cudaStream_t st);
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st);
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st);
-void launch_cmac(const Layout &p, int T, cudaStream_t st);
+int launch_cmac(const Layout &p, int T, cudaStream_t st);   // returns the number of kernels launched
+bool cmac_groups_by_view(const Layout &p, int T);            // whether a launch of T periods is grouped by view
 void launch_ifft_out(const Layout &p, int T, cudaStream_t st);
 void launch_carry(const CarryPlan &plan, cudaStream_t st);
 

@@ -360,6 +360,9 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   p.w = r->dalloc<float>((size_t)p.L * p.ws);
   p.amb = r->dalloc<float>((size_t)std::max(1, p.A) * p.ws);
   p.fdl = r->dalloc<float2>((size_t)p.CH * p.R * p.B);
+  p.grp_sorted = r->dalloc<int>((size_t)p.Tmax + 1);
+  p.grp_items = r->dalloc<int2>((size_t)p.Tmax + 1);
+  p.grp_count = r->dalloc<int>(2);
   {  // partial spectra of one launch, [periods of the launch][2][2][splits][B]; sized for the worst launch
     size_t cap = 0;
     for (int n = 1; n <= p.Tmax; n++) cap = std::max(cap, (size_t)n * cmac_splits_for(r.get(), n));
@@ -412,6 +415,13 @@ int cmac_splits_for(const bear_cuda_renderer *r, int n)
   const Layout &p = r->lay;
   if (!r->ks_dynamic) return r->ks_cfg;
   const int threads = std::min(p.B / 2, 128);
+  if (cmac_groups_by_view(p, n)) {
+    // grouped launch: an item is up to kCmacGroup periods of one view.  How many items there are
+    // depends on the views (device data): this is the upper bound (fewest possible items, ~12 CTAs
+    // per SM) that sizes the grid and the scratch; view_group_kernel picks the number actually used
+    const int base = (p.B / 2 / threads) * 2 * ((n + kCmacGroup) / kCmacGroup);
+    return std::max(r->ks_cfg, std::min((12 * 148 + base - 1) / base, r->ks_units));
+  }
   const int base = (p.B / 2 / threads) * 2 * (n + 1);
   return std::max(r->ks_cfg, std::min((4 * 148 + base - 1) / base, r->ks_units));
 }
@@ -446,7 +456,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
     chain.push_back(e);
     if (kernel_id >= 0) ids.push_back(kernel_id);
   };
-  int nchunks = 0;
+  int nchunks = 0, extra_launches = 0;
   for (int k0 = 0; k0 < T; nchunks++) {
     const int n = chunks[nchunks];
     before_chunk(nchunks, k0, n);
@@ -456,9 +466,11 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
     if (p.N > 0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, st); }
     mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, st);
     p.KS = cmac_splits_for(r, n);
-    mark(BEAR_CUDA_KERNEL_CMAC); launch_cmac(p, n, st);
+    p.ks_dev = cmac_groups_by_view(p, n);
+    mark(BEAR_CUDA_KERNEL_CMAC); extra_launches += launch_cmac(p, n, st) - 1;
     mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, st);
     p.KS = r->ks_cfg;
+    p.ks_dev = 0;
     after_chunk(nchunks, k0, n);
     k0 += n;
   }
@@ -505,7 +517,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
     r->ev_kernel.push_back(std::move(ids));
   }
   CK(cudaGetLastError());
-  r->launches += (uint64_t)(r->kernels_per_call - 1) * nchunks + 1;
+  r->launches += (uint64_t)(r->kernels_per_call - 1) * nchunks + 1 + extra_launches;
   p.fdl_head = (p.fdl_head + T) % p.R;
 }
 

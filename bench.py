@@ -52,6 +52,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-blocks", type=int, default=0, help="blocks of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk-blocks", type=int, default=0, help="periods per launch group (0 = library default)")
+    ap.add_argument("--cmac-splits", type=int, default=0, help="partial spectra per period (0 = library default)")
     return ap.parse_args()
 
 
@@ -216,7 +217,8 @@ def run_ours(args, rank, world, local_rank):
     scen, B, N = WORKLOADS[args.workload]
     T = max(8, int(args.seconds * FS / B) // 8 * 8)
     data, ctl, N, B, tb, audio = make_workload(args.workload, T, group=rank)
-    r = Renderer(data, N, 0, 0, B, max_batch_blocks=T, device=local_rank, chunk_blocks=args.chunk_blocks)
+    r = Renderer(data, N, 0, 0, B, max_batch_blocks=T, device=local_rank, chunk_blocks=args.chunk_blocks,
+                 cmac_splits=args.cmac_splits)
     io = device_io.DeviceBuffers(r, device_index=local_rank)
     io.load_audio(audio)
     io.load_tables(tb)
