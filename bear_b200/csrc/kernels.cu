@@ -164,18 +164,33 @@ __device__ __forceinline__ float2 *fft_shared(float2 *a, float2 *b, int M, int l
   return fft_shared<INV>(a, b, M, logM, tw, threadIdx.x, blockDim.x);
 }
 
+// First radix-8 pass of fft_shared_c with the input in registers: thread tid < M/8 holds
+// v[r] = x[tid + r * M/8].  The butterfly has no twiddles (Ns = 1); its output goes to `out` in the
+// layout the second pass reads, so the input never makes a round trip through shared memory.
+template <bool INV, int LOGM>
+__device__ __forceinline__ void fft_first_pass_reg(float2 (&v)[8], float2 *out, int tid)
+{
+  if (tid < (1 << LOGM) / 8) {
+    dft8<INV>(v);
+    float2 *bp = out + 9 * tid;   // padi(8 tid + r) = 9 tid + r
+#pragma unroll
+    for (int r = 0; r < 8; r++) bp[r] = v[r];
+  }
+}
+
 // The same transform with length and group size known at compile time (the per-period kernels are
 // instantiated per period size): the passes unroll, and because M/8 and Ns >= 8 are multiples of 8
 // the padded index of element j + r*stride is padi(j) + r*(stride + stride/8), a constant offset
 // from one base address per butterfly instead of eight index computations.
-template <bool INV, int LOGM, int NTHR>
+// FIRST = 1: the first radix-8 pass has been done by fft_first_pass_reg (its output is in `a`).
+template <bool INV, int LOGM, int NTHR, int FIRST = 0>
 __device__ __forceinline__ float2 *fft_shared_c(float2 *a, float2 *b, const float2 *__restrict__ tw, int tid)
 {
   constexpr int M = 1 << LOGM, Q = M >> 3, QP = Q + (Q >> 3);
   constexpr int NP = LOGM / 3, REM = LOGM % 3;
   static_assert(LOGM >= 6, "constant-offset addressing needs M/8 to be a multiple of 8");
 #pragma unroll
-  for (int pass = 0; pass < NP; pass++) {
+  for (int pass = FIRST; pass < NP; pass++) {
     const int Ns = 1 << (3 * pass), NsP = Ns + (Ns >> 3);
     float2 w0[7];
     if (pass > 0 && tid < Q) {
@@ -652,25 +667,24 @@ __global__ void decorrelate_kernel(Layout p, int T)
   const int l = blockIdx.x % p.L, k = p.k0 + blockIdx.x / p.L;
   const int tid = threadIdx.x;
   constexpr int nthr = NTHR;
-  // window [block k-1 | block k] of the diffuse bus (sum of the partials), eight loads in flight per
-  // thread before the first one is used
-  for (int n0 = tid; n0 < M; n0 += 8 * nthr) {
-    float2 z[8];
+  // window [block k-1 | block k] of the diffuse bus (sum of the partials) straight into the registers
+  // of the first FFT pass: thread tid takes samples tid + r M/8, eight loads in flight
+  constexpr int Q = M >> 3;
+  float2 v0[8];
 #pragma unroll
-    for (int i = 0; i < 8; i++) z[i] = make_float2(0.f, 0.f);
+  for (int r = 0; r < 8; r++) v0[r] = make_float2(0.f, 0.f);
+  if (tid < Q) {
     for (int s = 0; s < p.S; s++) {
-      const float2 *src = reinterpret_cast<const float2 *>(p.qdif + ((size_t)s * p.L + l) * p.cs + (size_t)k * p.B);
+      const float2 *src = reinterpret_cast<const float2 *>(p.qdif + ((size_t)s * p.L + l) * p.cs + (size_t)k * p.B) + tid;
       float2 v[8];
 #pragma unroll
-      for (int i = 0; i < 8; i++) v[i] = n0 + i * nthr < M ? src[n0 + i * nthr] : make_float2(0.f, 0.f);
+      for (int r = 0; r < 8; r++) v[r] = src[r * Q];
 #pragma unroll
-      for (int i = 0; i < 8; i++) { z[i].x += v[i].x; z[i].y += v[i].y; }
+      for (int r = 0; r < 8; r++) { v0[r].x += v[r].x; v0[r].y += v[r].y; }
     }
-#pragma unroll
-    for (int i = 0; i < 8; i++)
-      if (n0 + i * nthr < M) a[padi(n0 + i * nthr)] = z[i];
   }
-  float2 *z = fft_shared_c<false, LOGB, NTHR>(a, b, p.tw, tid);
+  fft_first_pass_reg<false, LOGB>(v0, b, tid);
+  float2 *z = fft_shared_c<false, LOGB, NTHR, 1>(b, a, p.tw, tid);
   float2 *o = (z == a) ? b : a;
   const float2 *h = p.h_dec + (size_t)l * M;
   for (int kk = tid; kk <= M / 2; kk += nthr) {
@@ -770,41 +784,56 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
   asm volatile("cp.async.wait_group 0;");
   __syncthreads();
 
+  constexpr int Q = M >> 3;
+  float2 v0[8];
+#pragma unroll
+  for (int r = 0; r < 8; r++) v0[r] = make_float2(0.f, 0.f);
   if (active) {
     if (bus) {
       const float *wrow = rows + p.hist;    // window sample 0
       const bool dif = p.N > 0;
       const float dda = tb - ta, ddb = tc - tb;
       const float2 *cw = reinterpret_cast<const float2 *>(cwin + g * 2 * M);
-      for (int n = tid; n < M; n += nthr) {
-        float2 v = make_float2(0.f, 0.f);
-        if (cstaged) {
-          v = cw[n];
-        } else {
-          for (int s = 0; s < p.S; s++) {
-            const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
-            v.x += c.x; v.y += c.y;
+      if (tid < Q) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+          const int n = tid + r * Q;
+          float2 v = make_float2(0.f, 0.f);
+          if (cstaged) {
+            v = cw[n];
+          } else {
+            for (int s = 0; s < p.S; s++) {
+              const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
+              v.x += c.x; v.y += c.y;
+            }
           }
+          if (dif) {
+            const int t = 2 * n;            // window sample, both of the pair lie in the same block
+            const bool h = t >= p.B;        // false: block k-1, true: block k
+            const int nn = h ? t - p.B : t;
+            const float d0 = h ? tb : ta, dd = h ? ddb : dda;
+            float ra, rb;
+            unpack2(delayed_read2(wrow + t, ramped_delay(d0, dd, (float)(nn + p.doff) * invB),
+                                  wrow + t + 1, ramped_delay(d0, dd, (float)(nn + 1 + p.doff) * invB)), ra, rb);
+            v.x += ra; v.y += rb;
+          }
+          v0[r] = v;
         }
-        if (dif) {
-          const int t = 2 * n;            // window sample, both of the pair lie in the same block
-          const bool h = t >= p.B;        // false: block k-1, true: block k
-          const int nn = h ? t - p.B : t;
-          const float d0 = h ? tb : ta, dd = h ? ddb : dda;
-          float ra, rb;
-          unpack2(delayed_read2(wrow + t, ramped_delay(d0, dd, (float)(nn + p.doff) * invB),
-                                wrow + t + 1, ramped_delay(d0, dd, (float)(nn + 1 + p.doff) * invB)), ra, rb);
-          v.x += ra; v.y += rb;
-        }
-        a[padi(n)] = v;
       }
     } else {
       const float *arow = rows + g * RW + p.hist;
-      for (int n = tid; n < M; n += nthr)
-        a[padi(n)] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
+      if (tid < Q) {
+#pragma unroll
+        for (int r = 0; r < 8; r++) {
+          const int n = tid + r * Q;
+          v0[r] = make_float2(delayed_read(arow + 2 * n, p.hoa_delay), delayed_read(arow + 2 * n + 1, p.hoa_delay));
+        }
+      }
     }
   }
-  float2 *z = fft_shared_c<false, LOGB, NTHR>(a, b, p.tw, tid);
+  // the assembled window goes into the first FFT pass from registers (thread tid holds samples tid + r M/8)
+  fft_first_pass_reg<false, LOGB>(v0, b, tid);
+  float2 *z = fft_shared_c<false, LOGB, NTHR, 1>(b, a, p.tw, tid);
   if (!active) return;
   const int slot = (p.fdl_head + k) % p.R;
   float2 *dst = p.fdl + ((size_t)ch * p.R + slot) * M;

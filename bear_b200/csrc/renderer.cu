@@ -995,6 +995,11 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info)
   info->kernels_per_call = r->kernels_per_call;
   info->device_bytes = r->device_bytes;
   info->shared_bytes = r->bank ? r->bank->bytes : 0;
+  int grp[2] = {0, 0};
+  if (r->lay.grp_count && cudaMemcpyAsync(grp, r->lay.grp_count, sizeof grp, cudaMemcpyDeviceToHost, r->stream) == cudaSuccess)
+    cudaStreamSynchronize(r->stream);
+  info->cmac_items_last = (uint32_t)grp[0];
+  info->cmac_splits_last = (uint32_t)grp[1];
   info->launches_total = r->launches;
   info->default_direct_delay = r->default_direct_delay;
   info->default_static_delay = r->default_static_delay;

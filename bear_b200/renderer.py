@@ -70,6 +70,7 @@ class Info(C.Structure):
         ("history_samples", C.c_uint32), ("kernels_per_call", C.c_uint32), ("device_bytes", C.c_uint64),
         ("launches_total", C.c_uint64), ("default_direct_delay", C.c_double),
         ("default_static_delay", C.c_double), ("shared_bytes", C.c_uint64),
+        ("cmac_items_last", C.c_uint32), ("cmac_splits_last", C.c_uint32),
     ]
 
 

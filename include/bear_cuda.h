@@ -215,6 +215,9 @@ typedef struct bear_cuda_info {
   uint64_t launches_total;      /* kernels launched since creation */
   double default_direct_delay, default_static_delay; /* seconds, panner.cpp:172-186 */
   uint64_t shared_bytes;        /* device memory of the (possibly shared) filter spectra and tables */
+  /* the most recent launch whose periods were grouped by BRIR view (>= 8 periods): number of
+   * (view, <= 6 periods) work items and of partial spectra per period the device chose; 0 if none yet */
+  uint32_t cmac_items_last, cmac_splits_last;
 } bear_cuda_info;
 
 int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
