@@ -533,10 +533,11 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
     // Channels are taken two at a time: both channels' fractional-delay gathers (two independent
     // dependency chains per ear) are issued before either channel's accumulation, which gives the
     // scheduler work to overlap at the low occupancy the 72 accumulators allow.
-    for (int ii = 0; ii < cnt; ii += 2) {
-      float xl2[2], xR2[2], x02[2];
+    constexpr int UC = 4;   // channels whose delayed reads are issued together
+    for (int ii = 0; ii < cnt; ii += UC) {
+      float xl2[UC], xR2[UC], x02[UC];
 #pragma unroll
-      for (int u = 0; u < 2; u++) {
+      for (int u = 0; u < UC; u++) {
         const int j = min(ii + u, cnt - 1);
         const float *xr = xt + j * XW + p.hist + tid;
         unpack2(delayed_read2(xr, fminf(ramped_delay(sd[j][0], sd[j][1], rd), dmax),
@@ -544,7 +545,7 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
         x02[u] = xr[0];
       }
 #pragma unroll
-      for (int u = 0; u < 2; u++) {
+      for (int u = 0; u < UC; u++) {
         const int j = ii + u;
         if (j >= cnt) break;
         const unsigned md = smask[j][0], mq = smask[j][1];

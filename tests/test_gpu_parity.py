@@ -119,6 +119,50 @@ def test_chunked_launch_and_overlapped_upload(oracle, small_data, chunk):
     check(out2, ref, "chunk %d, two calls" % chunk)
 
 
+VIEW_PATTERNS = {
+    "constant": lambda T, rng: np.zeros(T),
+    "alternating": lambda T, rng: 30.0 * (np.arange(T) % 2),
+    "runs": lambda T, rng: 30.0 * (np.arange(T) // 7),                    # 7 periods per view: items of 6 + 1
+    "random4": lambda T, rng: 30.0 * rng.integers(0, 4, size=T),          # many repeats, items of every size
+    "cycle": lambda T, rng: 30.0 * (np.arange(T) % 12),                   # every view, 3-4 periods each
+}
+
+
+@pytest.mark.parametrize("mode,kw", [("batch", {}), ("batch17", {}), ("batch", {"chunk_blocks": 9}),
+                                     ("batch", {"cmac_splits": 5})])
+@pytest.mark.parametrize("pattern", sorted(VIEW_PATTERNS))
+def test_view_grouped_convolution(oracle, small_data, pattern, mode, kw):
+    """Launches of >= 8 periods group their periods by BRIR view in the cMAC kernel (one filter load
+    for up to 6 periods): view sequences with every item size, across calls and chunked launches."""
+    B, T = 256, 40
+    ctl = control.HostControl(small_data)
+    rng = np.random.default_rng(len(pattern))
+    yaw = VIEW_PATTERNS[pattern](T, rng)
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, 3)), obj_diffuse=[0, .5, 1], ds_speakers=[4],
+                    hoa_gains=np.eye(16, 4, dtype=np.float32), H=4, yaw_deg=yaw)
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((3, 0), (1, 100), (4, 200)))
+    ref = ref_render(oracle, small_data, 3, 1, 4, B, tb, obj, ds, hoa)
+    out = gpu_render(small_data, 3, 1, 4, B, tb, obj, ds, hoa, mode, **kw)
+    assert np.abs(ref).max() > 0.05
+    check(out, ref, "%s %s %s" % (pattern, mode, kw))
+
+
+def test_more_views_than_the_grouping_table_holds(oracle):
+    """A data file with more views than the grouping kernel's histogram (2560) renders through the
+    ungrouped kernel; an out-of-range brir_index is still refused."""
+    data = data_file.from_tree(data_file.synthetic_tree(seed=5, num_views=2600, brir_length=100))
+    B, T = 128, 12
+    ctl = control.HostControl(data)
+    rng = np.random.default_rng(11)
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, 2)), obj_diffuse=[0, .7], yaw_deg=rng.uniform(0, 360, size=T))
+    assert len(set(tb["brir_index"].tolist())) > 6 and tb["brir_index"].max() > 1000
+    obj = control.synth_audio(2, T * B, 0)
+    none = np.zeros((0, T * B), np.float32)
+    ref = ref_render(oracle, data, 2, 0, 0, B, tb, obj, none, none)
+    out = gpu_render(data, 2, 0, 0, B, tb, obj, none, none, "batch")
+    check(out, ref, "2600 views")
+
+
 def test_unity_fixture_path_delays_through_file_loader(oracle, unity_data):
     """visr_bear/test/test_delays.py:114-136 on the CUDA path, data file read by the C++ loader."""
     B, T = 512, 10
