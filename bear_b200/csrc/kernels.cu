@@ -836,8 +836,7 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
   fft_first_pass_reg<false, LOGB>(v0, b, tid);
   float2 *z = fft_shared_c<false, LOGB, NTHR, 1>(b, a, p.tw, tid);
   if (!active) return;
-  const int slot = (p.fdl_head + k) % p.R;
-  float2 *dst = p.fdl + ((size_t)ch * p.R + slot) * M;
+  float2 *dst = p.fdl + ((size_t)ch * p.R + p.P + k) * M;   // period k lives in slot P + k
   for (int kk = tid; kk <= M / 2; kk += nthr) {
     if (kk == 0) {
       dst[0] = make_float2(z[0].x + z[0].y, z[0].x - z[0].y);
@@ -931,8 +930,7 @@ __device__ __forceinline__ void cmac_item(const Layout &p, const int (&j)[kCmacG
   for (int g = 0; g < CNT; g++) {
     accA[g] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (HAS_B) accB[g] = accA[g];
-    int sl = p.fdl_head + j[g];                            // ring slot of period j (j >= -1)
-    slotA[g] = sl < 0 ? sl + R : (sl >= R ? sl - R : sl);
+    slotA[g] = P + j[g];                                   // slot of period j (j >= -1)
   }
   const float4 *fdl4 = reinterpret_cast<const float4 *>(p.fdl) + pair;
   for (int u = u0; u < u1; u++) {
@@ -945,7 +943,7 @@ __device__ __forceinline__ void cmac_item(const Layout &p, const int (&j)[kCmacG
 #pragma unroll
       for (int g = 0; g < CNT; g++) {
         slot[g] = slotA[g];
-        if (HAS_B) xb[g] = __ldg(x + (size_t)(slotA[g] + 1 == R ? 0 : slotA[g] + 1) * hB);   // period j+1
+        if (HAS_B) xb[g] = __ldg(x + (size_t)(slotA[g] + 1) * hB);   // period j+1
       }
 #pragma unroll(CNT == 1 ? 6 : (CNT <= 3 ? 3 : 2))
       for (int part = 0; part < P; part++) {
@@ -955,7 +953,7 @@ __device__ __forceinline__ void cmac_item(const Layout &p, const int (&j)[kCmacG
           const float4 xa = __ldg(x + (size_t)slot[g] * hB);
           cmac2(accA[g], xa, hv, packed0);
           if (HAS_B) { cmac2(accB[g], xb[g], hv, packed0); xb[g] = xa; }
-          slot[g] = slot[g] == 0 ? R - 1 : slot[g] - 1;
+          slot[g]--;
         }
       }
     } else {
@@ -965,7 +963,7 @@ __device__ __forceinline__ void cmac_item(const Layout &p, const int (&j)[kCmacG
 #pragma unroll
         for (int g = 0; g < CNT; g++) {
           cmac2(accA[g], __ldg(x + (size_t)slotA[g] * hB), hv, packed0);
-          if (HAS_B) cmac2(accB[g], __ldg(x + (size_t)(slotA[g] + 1 == R ? 0 : slotA[g] + 1) * hB), hv, packed0);
+          if (HAS_B) cmac2(accB[g], __ldg(x + (size_t)(slotA[g] + 1) * hB), hv, packed0);
         }
       }
     }
@@ -1007,14 +1005,13 @@ __device__ __forceinline__ void cmac2_scalar(CmacAcc &acc, const float4 x, const
 
 // delay-line pieces g = G .. CNT-1 of one term (the shared-memory offset is an immediate)
 template <int G, int CNT>
-__device__ __forceinline__ void cmac_request_fdl(unsigned pdst, const float4 *px, int (&poff)[CNT], int hB, int ringlen)
+__device__ __forceinline__ void cmac_request_fdl(unsigned pdst, const float4 *px, int (&poff)[CNT], int hB)
 {
   if constexpr (G < CNT) {
     asm volatile("cp.async.cg.shared.global [%0+%2], [%1], 16;" ::"r"(pdst), "l"(px + poff[G]),
                  "n"((1 + G) * kCmacRingStride * (int)sizeof(float4)) : "memory");
     poff[G] -= hB;
-    if (poff[G] < 0) poff[G] += ringlen;
-    cmac_request_fdl<G + 1, CNT>(pdst, px, poff, hB, ringlen);
+    cmac_request_fdl<G + 1, CNT>(pdst, px, poff, hB);
   }
 }
 
@@ -1040,8 +1037,7 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
   for (int g = 0; g < CNT; g++) {
     accA[g].lo = accA[g].hi = 0ull;
     if (HAS_B) { accB[g] = accA[g]; xb[g] = make_float4(0.f, 0.f, 0.f, 0.f); }
-    int sl = p.fdl_head + j[g];
-    slotA[g] = sl < 0 ? sl + R : (sl >= R ? sl - R : sl);
+    slotA[g] = P + j[g];
   }
   const float4 *fdl4 = reinterpret_cast<const float4 *>(p.fdl) + pair;
   constexpr int first_part = HAS_B ? -1 : 0;
@@ -1052,8 +1048,7 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
   int poff[CNT];                                               // float4 offset of the next delay-line piece
 #pragma unroll
   for (int g = 0; g < CNT; g++) {
-    const int sl = HAS_B ? (slotA[g] + 1 == R ? 0 : slotA[g] + 1) : slotA[g];
-    poff[g] = sl * hB;
+    poff[g] = (HAS_B ? slotA[g] + 1 : slotA[g]) * hB;
   }
   const float4 *px = fdl4 + (size_t)(2 * u0 + e) * ringlen;
   const float4 *ph = reinterpret_cast<const float4 *>(p.h_brir) + ((size_t)(v * 2 * L + 2 * u0 + e) * P) * hB + pair;
@@ -1066,7 +1061,7 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
         asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(pdst), "l"(ph) : "memory");
         ph += hB;
       }
-      cmac_request_fdl<0, CNT>(pdst, px, poff, hB, ringlen);
+      cmac_request_fdl<0, CNT>(pdst, px, poff, hB);
       pt++;
       pdst += kStageBytes;
       if (++pstage == S) { pstage = 0; pdst = ring0; }
@@ -1075,10 +1070,7 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
         px += 2 * (size_t)ringlen;
         ph += (size_t)P * hB;
 #pragma unroll
-        for (int g = 0; g < CNT; g++) {
-          poff[g] += tpu * hB;
-          if (poff[g] >= ringlen) poff[g] -= ringlen;
-        }
+        for (int g = 0; g < CNT; g++) poff[g] += tpu * hB;
       }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -1127,7 +1119,7 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
 #pragma unroll
       for (int g = 0; g < CNT; g++) {
         cmac2_scalar(accA[g], __ldg(x + (size_t)slotA[g] * hB), hv, packed0);
-        if (HAS_B) cmac2_scalar(accB[g], __ldg(x + (size_t)(slotA[g] + 1 == R ? 0 : slotA[g] + 1) * hB), hv, packed0);
+        if (HAS_B) cmac2_scalar(accB[g], __ldg(x + (size_t)(slotA[g] + 1) * hB), hv, packed0);
       }
     }
   }
@@ -1365,6 +1357,24 @@ void launch_ifft_out(const Layout &p, int T, cudaStream_t st)
 // ----------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) carry_kernel(CarryPlan plan)
 {
+  if ((int)blockIdx.x >= plan.row_start[plan.n]) {
+    // delay line: the last P spectra of every channel move to slots 0..P-1.  One thread per
+    // (channel, bin): it reads its own column of slots before it writes it, so source and destination
+    // may overlap (calls of fewer than P periods) and no barrier is needed.
+    const long long t = (long long)(blockIdx.x - plan.row_start[plan.n]) * blockDim.x + threadIdx.x;
+    if (t >= (long long)plan.fdl_channels * plan.fdl_B) return;
+    float2 *col = plan.fdl + (t / plan.fdl_B) * plan.fdl_stride + (t % plan.fdl_B);
+    for (int s0 = 0; s0 < plan.fdl_P; s0 += 8) {
+      float2 v[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+        if (s0 + i < plan.fdl_P) v[i] = col[(size_t)(s0 + i + plan.fdl_T) * plan.fdl_B];
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+        if (s0 + i < plan.fdl_P) col[(size_t)(s0 + i) * plan.fdl_B] = v[i];
+    }
+    return;
+  }
   int e = 0;
   while (e + 1 < plan.n && (int)blockIdx.x >= plan.row_start[e + 1]) e++;
   const CarryRow r = plan.e[e];
@@ -1406,7 +1416,8 @@ void launch_unpack(const Layout &p, const UnpackPlan &plan, cudaStream_t st)
 
 void launch_carry(const CarryPlan &plan, cudaStream_t st)
 {
-  carry_kernel<<<plan.row_start[plan.n], 256, 0, st>>>(plan);
+  const long long cols = (long long)plan.fdl_channels * plan.fdl_B;
+  carry_kernel<<<plan.row_start[plan.n] + (int)((cols + 255) / 256), 256, 0, st>>>(plan);
 }
 
 // ----------------------------------------------------------------------------------------------

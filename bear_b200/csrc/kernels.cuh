@@ -23,7 +23,7 @@ struct Layout {
   int hist;           // time-domain history (samples) kept in front of every delayed signal
   int S;              // object splits (partial bus buffers)
   int KS;             // cMAC splits (partial spectra)
-  int R;              // FDL ring slots
+  int R;              // FDL slots per channel (P + Tmax)
   int goff, doff, xoff;  // ramp offsets
   float fs;
   float hoa_delay;    // samples
@@ -44,7 +44,7 @@ struct Layout {
   float *w;     size_t ws;   // [L][ws]       prefix B+hist  (decorrelator outputs)
   float *amb;                // [A][ws]       prefix B+hist  (HOA decoder inputs)
   // spectra (packed: bin 0 = (DC, Nyquist), bins 1..B-1 complex)
-  float2 *fdl;               // [CH][R][B]
+  float2 *fdl;               // [CH][R][B], R = P + Tmax: slots 0..P-1 = the P periods before this call, slot P + k = period k
   const float2 *h_brir;      // [V][2L][P][B], pre-scaled by 1/(2B)
   const float2 *h_dec;       // [L][B]
   const float2 *h_hoa;       // [A][2][B]
@@ -60,7 +60,6 @@ struct Layout {
   float *raw_ds;             // [Tmax][L][M]
   double fs_d, dec_delay_d;
   int front;
-  int fdl_head;              // ring slot of block 0 of this call
   // periods of a launch grouped by view (scratch of view_group_kernel / cmac_kernel)
   int *grp_sorted;           // [Tmax + 1] period indices relative to k0 - 1, sorted by view
   int2 *grp_items;           // [Tmax + 1] (first, count) into grp_sorted
@@ -81,6 +80,10 @@ struct CarryPlan {
   CarryRow e[kMaxCarry];
   int row_start[kMaxCarry + 1];
   int n;
+  // frequency-domain delay line: slots [T, T+P) -> [0, P) of every channel
+  float2 *fdl;
+  long long fdl_stride;   // float2 per channel
+  int fdl_channels, fdl_B, fdl_P, fdl_T;
 };
 
 void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, int logB, int P, const float2 *tw,

@@ -165,7 +165,6 @@ void set_initial_state(bear_cuda_renderer *r)
   if (p.N) fill_device(r, p.d_dir, 2 * p.N, (float)r->default_direct_delay);
   if (p.M) fill_device(r, p.d_ds, 2 * p.M, (float)r->default_direct_delay);
   fill_device(r, p.d_stat, 2 * 2 * p.L, (float)r->default_static_delay);
-  p.fdl_head = 0;
   r->tables_on_device = false;
 }
 
@@ -331,7 +330,7 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
     r->ks_cfg = p.KS;
     r->ks_units = nunits;
   }
-  p.R = p.Tmax + p.P - 1;
+  p.R = p.Tmax + p.P;
   r->chunk = (int)cfg.chunk_blocks;
   // host-buffer path: upload in ~12 chunks (at least 16 periods each) so copies overlap the kernels
   r->h2d_chunk = cfg.chunk_blocks ? (int)cfg.chunk_blocks : std::max(16, (p.Tmax + 11) / 12);
@@ -510,6 +509,12 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
   add(reinterpret_cast<float *>(p.view), 1, 0, 1, T);
   plan.n = n;
   plan.row_start[n] = rows;
+  plan.fdl = p.fdl;
+  plan.fdl_stride = (long long)p.R * p.B;
+  plan.fdl_channels = p.CH;
+  plan.fdl_B = p.B;
+  plan.fdl_P = p.P;
+  plan.fdl_T = T;
   launch_carry(plan, st);
   mark(-1);
   if (r->profiling) {
@@ -518,7 +523,6 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
   }
   CK(cudaGetLastError());
   r->launches += (uint64_t)(r->kernels_per_call - 1) * nchunks + 1 + extra_launches;
-  p.fdl_head = (p.fdl_head + T) % p.R;
 }
 
 void run_pipeline(bear_cuda_renderer *r, int T)
