@@ -10,10 +10,14 @@
 //   bus_fdl_kernel    direct partials + static-delayed decorrelator outputs -> 48 ch bus -> rFFT(2B)
 //                     -> frequency-domain delay line; HOA bus (fixed delay commuted in front of
 //                     the decode filters) -> rFFT(2B) -> FDL                           [a6,a8,a12]
+//   view_group_kernel periods of the launch sorted by BRIR view -> work items of <= 6 periods
 //   cmac_kernel       Y[e] = sum_{l,p} FDL[2l+e][k-p] * H[view][2l+e][p] (+ HOA decode terms),
-//                     for the new view and, in a view-change block, the old one        [a9,a11]
+//                     for the new view and, in a view-change block, the old one; one filter load
+//                     serves all periods of a work item                               [a9,a11]
 //   ifft_out_kernel   sum partial spectra -> irFFT -> overlap-save discard -> view crossfade -> out [a9,a13]
-//   carry_kernel      moves histories / table state to the front for the next call
+//   carry_kernel      moves histories / table state / the last P delay-line spectra to the front
+//   unpack_kernel     single-period host call: scatters the packed upload (audio + tables)
+//   control_kernel    optional: the Control graph's table producers on the device      [a15]
 #include "kernels.cuh"
 
 #include <type_traits>

@@ -147,6 +147,29 @@ def test_view_grouped_convolution(oracle, small_data, pattern, mode, kw):
     check(out, ref, "%s %s %s" % (pattern, mode, kw))
 
 
+def test_calls_of_irregular_length(oracle, small_data):
+    """One renderer fed calls of 1, 2, 9, 3, 14, 1, 5, 8 ... periods: state carried between calls
+    (delay-line history of P = 6 periods, input/bus histories, previous tables) whatever the call sizes,
+    shorter and longer than the number of partitions, grouped and ungrouped launches."""
+    from bear_b200.renderer import Renderer
+    B, sizes = 128, [1, 2, 9, 3, 14, 1, 5, 8, 1, 1, 11]
+    T = sum(sizes)
+    ctl = control.HostControl(small_data)
+    rng = np.random.default_rng(21)
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, 4)), obj_diffuse=[0, .3, 1, .6], ds_speakers=[1, 7],
+                    hoa_gains=np.eye(16, 4, dtype=np.float32), H=4, yaw_deg=30.0 * rng.integers(0, 5, size=T))
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((4, 0), (2, 100), (4, 200)))
+    ref = ref_render(oracle, small_data, 4, 2, 4, B, tb, obj, ds, hoa)
+    out = np.empty((2, T * B), np.float32)
+    with Renderer(small_data, 4, 2, 4, B, max_batch_blocks=max(sizes)) as r:
+        k0 = 0
+        for n in sizes:
+            a, b = k0 * B, (k0 + n) * B
+            out[:, a:b] = r.process_batch(obj[:, a:b], ds[:, a:b], hoa[:, a:b], tb.slice(k0, k0 + n))
+            k0 += n
+    check(out, ref, "irregular calls")
+
+
 def test_more_views_than_the_grouping_table_holds(oracle):
     """A data file with more views than the grouping kernel's histogram (2560) renders through the
     ungrouped kernel; an out-of-range brir_index is still refused."""
