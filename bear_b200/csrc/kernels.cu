@@ -439,7 +439,7 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
   // groups are skipped with a CTA-uniform branch; skipped terms would have added exact zeros.
   __shared__ unsigned smask[kMixChunk][2];
   // input rows of the staged channels: [hist history samples | kMixTile samples of this tile],
-  // filled with 16-byte cp.async copies so that the per-ear fractional-delay reads are shared-memory
+  // filled by one bulk copy per row so that the per-ear fractional-delay reads are shared-memory
   // reads (the reads themselves are unaligned 4-tap gathers, which made the kernel wait on L2)
   extern __shared__ __align__(16) float xt[];
   const int XW = p.hist + kMixTile;
@@ -461,19 +461,27 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
 #pragma unroll
   for (int l = 0; l < kMaxSpeakers / 2; l++) accL[l] = accR[l] = accQ[l] = 0ull;
 
+  __shared__ __align__(8) unsigned long long xbar;   // completion of the bulk copies into xt
+  const unsigned xbar_addr = (unsigned)__cvta_generic_to_shared(&xbar);
+  unsigned xphase = 0;
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(xbar_addr) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
   for (int cb = c0; cb < c1; cb += kMixChunk) {
     const int cnt = min(kMixChunk, c1 - cb);
     __syncthreads();
     if (tid < 2 * kMixChunk) smask[tid >> 1][tid & 1] = 0u;
-    {
-      // warp w copies rows w, w+4, ...: 16-byte pieces, consecutive lanes consecutive pieces
-      const int vec_per_row = XW >> 2;
-      const float *src0 = p.xin + (size_t)cb * p.xs + (t - tid);   // column (hist + t0) - hist
-      for (int row = tid >> 5; row < cnt; row += kMixTile / 32) {
-        const float *src = src0 + (size_t)row * p.xs;
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(xt + row * XW);
-        for (int v = tid & 31; v < vec_per_row; v += 32)
-          asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
+    if (tid < 32) {
+      // one bulk copy (TMA, 1-D) per input row, issued by the lanes of warp 0; the rows land on xbar
+      if (tid == 0)
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(xbar_addr), "r"(cnt * XW * 4) : "memory");
+      __syncwarp();
+      if (tid < cnt) {
+        const float *src = p.xin + (size_t)(cb + tid) * p.xs + (t - tid);   // column (hist + t0) - hist
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(xt + tid * XW);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst), "l"(src), "r"(XW * 4), "r"(xbar_addr) : "memory");
       }
     }
     // gain tables of periods k-1 (slot k) and k (slot k+1) straight into the rows of sg with 4-byte
@@ -521,6 +529,14 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
       sd[ii][2 * e] = d0; sd[ii][2 * e + 1] = d1 - d0;
     }
     asm volatile("cp.async.wait_group 0;");
+    {  // wait for the input rows of this chunk (phase bit flips per use of the barrier)
+      unsigned done;
+      do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(done) : "r"(xbar_addr), "r"(xphase) : "memory");
+      } while (!done);
+      xphase ^= 1u;
+    }
     __syncthreads();
     // deltas and sparsity masks; consecutive threads consecutive speakers of one channel (conflict-free)
     for (int idx = tid; idx < cnt * kMaxSpeakers; idx += kMixTile) {
