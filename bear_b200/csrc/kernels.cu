@@ -777,33 +777,39 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
     tb = p.d_stat[(size_t)(k + 1) * L2 + ch] * p.fs;
     tc = p.d_stat[(size_t)(k + 2) * L2 + ch] * p.fs;
   }
-  // stage the source rows: columns [k*B, k*B + hist + 2B) of the (B + hist)-prefixed row; group g
-  // copies row g (bus units have one row: both groups share the copy of row 0)
-  if (!bus || p.N > 0) {
-    const int vec = RW >> 2;
-    if (bus) {
-      const float *src = p.w + (size_t)unit * p.ws + (size_t)k * p.B;
-      const unsigned dst = (unsigned)__cvta_generic_to_shared(rows);
-      for (int v = threadIdx.x; v < vec; v += blockDim.x)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
-    } else if (active) {
-      const float *src = p.amb + (size_t)(ch - L2) * p.ws + (size_t)k * p.B;
-      const unsigned dst = (unsigned)__cvta_generic_to_shared(rows + g * RW);
-      for (int v = tid; v < vec; v += nthr)
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
-    }
-  }
+  // stage the source rows -- columns [k*B, k*B + hist + 2B) of the (B + hist)-prefixed row -- and, for
+  // bus units, both ears' direct-bus windows [block k-1 | block k]: one bulk copy (TMA, 1-D) each,
+  // issued by thread 0, landing on one mbarrier that every thread then waits on
+  __shared__ __align__(8) unsigned long long sbar;
+  const unsigned sbar_addr = (unsigned)__cvta_generic_to_shared(&sbar);
   const bool cstaged = bus && stage_direct;
-  if (cstaged) {   // this group's direct-bus window [block k-1 | block k]
-    const int vec = (2 * M) >> 2;
-    const float *src = p.cdir + (size_t)ch * p.cs + (size_t)k * p.B;
-    const unsigned dst = (unsigned)__cvta_generic_to_shared(cwin + g * 2 * M);
-    for (int v = tid; v < vec; v += nthr)
-      asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * v), "l"(src + 4 * v));
+  if (threadIdx.x == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(sbar_addr) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    const unsigned row_bytes = (unsigned)RW * 4u, win_bytes = 2u * M * 4u;
+    const int nrows = bus ? (p.N > 0 ? 1 : 0) : min(2, p.A - 2 * (unit - p.L));
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                 ::"r"(sbar_addr), "r"(nrows * row_bytes + (cstaged ? 2u * win_bytes : 0u)) : "memory");
+    for (int r = 0; r < nrows; r++) {
+      const float *src = (bus ? p.w + (size_t)unit * p.ws : p.amb + (size_t)(2 * (unit - p.L) + r) * p.ws) + (size_t)k * p.B;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"((unsigned)__cvta_generic_to_shared(rows + r * RW)), "l"(src), "r"(row_bytes), "r"(sbar_addr) : "memory");
+    }
+    if (cstaged)
+      for (int r = 0; r < 2; r++) {
+        const float *src = p.cdir + (size_t)(2 * unit + r) * p.cs + (size_t)k * p.B;
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"((unsigned)__cvta_generic_to_shared(cwin + r * 2 * M)), "l"(src), "r"(win_bytes), "r"(sbar_addr) : "memory");
+      }
   }
-  asm volatile("cp.async.commit_group;");
-  asm volatile("cp.async.wait_group 0;");
-  __syncthreads();
+  __syncthreads();   // the barrier is initialised and armed before anyone polls it
+  {
+    unsigned done;
+    do {
+      asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\nselp.u32 %0, 1, 0, p;\n}"
+                   : "=r"(done) : "r"(sbar_addr) : "memory");
+    } while (!done);
+  }
 
   constexpr int Q = M >> 3;
   float2 v0[8];
