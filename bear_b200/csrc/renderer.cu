@@ -105,6 +105,18 @@ struct bear_cuda_renderer {
   // pinned host staging for the single-block API: one packed buffer [audio | tables] and its
   // device mirror, so that a period costs one upload
   float *h_in = nullptr, *h_out = nullptr, *d_pack = nullptr;
+  // single-period host path as one CUDA graph (upload, scatter, the kernels, read-back): every
+  // parameter of a one-period call is constant, only the contents of h_graph change.  h_graph holds
+  // the audio and ALL tables of the period at fixed offsets; a port passed as NULL keeps last period's
+  // values there, which is valid as long as the last call went through this path (shadow_valid).
+  float *h_graph = nullptr;
+  struct StreamSlot { size_t off, count; float *dev; size_t slot; };
+  std::vector<StreamSlot> stream_slots;    // direct gains, diffuse gains, ..., view (order of bear_cuda_process)
+  size_t stream_floats = 0;
+  bool shadow_valid = false, graph_ok = true;
+  cudaGraph_t graph = nullptr;
+  cudaGraphExec_t graph_exec = nullptr;
+  uint64_t graph_launch_count = 0;         // kernels in the graph
   size_t h_in_floats = 0;
 
   template <class T>
@@ -130,6 +142,9 @@ struct bear_cuda_renderer {
     for (auto &c : ev_pending)
       for (cudaEvent_t e : c) cudaEventDestroy(e);
     for (cudaEvent_t e : ev_free) cudaEventDestroy(e);
+    if (graph_exec) cudaGraphExecDestroy(graph_exec);
+    if (graph) cudaGraphDestroy(graph);
+    if (h_graph) cudaFreeHost(h_graph);
     if (h_in) cudaFreeHost(h_in);
     if (h_out) cudaFreeHost(h_out);
     for (cudaEvent_t e : h2d_events) cudaEventDestroy(e);
@@ -159,6 +174,22 @@ void fill_device(bear_cuda_renderer *r, float *dst, size_t count, float value)
 // Initial state of the DSP graph (dsp.cpp:24-29,41-46,137-144; panner.cpp:172-186): gains 0 (buffers are
 // zeroed), object / DirectSpeakers delays = default direct delay, static delays = default static delay,
 // view 0.
+// The tables of "the period before the first one" in the fixed-offset host buffer of the graph path.
+void init_stream_shadow(bear_cuda_renderer *r)
+{
+  if (!r->h_graph) return;
+  Layout &p = r->lay;
+  std::fill(r->h_graph, r->h_graph + r->stream_floats, 0.0f);
+  auto fill = [&](float *dev, float v) {
+    for (auto &sl : r->stream_slots)
+      if (sl.dev == dev) std::fill(r->h_graph + sl.off, r->h_graph + sl.off + sl.count, v);
+  };
+  fill(p.d_dir, (float)r->default_direct_delay);
+  fill(p.d_ds, (float)r->default_direct_delay);
+  fill(p.d_stat, (float)r->default_static_delay);
+  r->shadow_valid = true;   // view 0 = all-zero bits, gains 0
+}
+
 void set_initial_state(bear_cuda_renderer *r)
 {
   Layout &p = r->lay;
@@ -166,6 +197,7 @@ void set_initial_state(bear_cuda_renderer *r)
   if (p.M) fill_device(r, p.d_ds, 2 * p.M, (float)r->default_direct_delay);
   fill_device(r, p.d_stat, 2 * 2 * p.L, (float)r->default_static_delay);
   r->tables_on_device = false;
+  init_stream_shadow(r);
 }
 
 std::shared_ptr<FilterBank> build_bank(const bear_cuda_config &cfg, const bear_cuda_data &d)
@@ -395,6 +427,25 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   CK(cudaMallocHost(&r->h_in, r->h_in_floats * sizeof(float)));
   r->d_pack = r->dalloc<float>(r->h_in_floats);
   CK(cudaMallocHost(&r->h_out, 2 * (size_t)p.B * sizeof(float)));
+  {
+    size_t off = (size_t)(p.N + p.M + p.H) * p.B;
+    auto slot = [&](float *dev, size_t per_block, size_t sl) {
+      if (per_block == 0) return;
+      r->stream_slots.push_back({off, per_block, dev, sl});
+      off += per_block;
+    };
+    slot(p.g_dir, (size_t)p.L * p.N, 1);
+    slot(p.g_dif, (size_t)p.L * p.N, 1);
+    slot(p.d_dir, (size_t)2 * p.N, 1);
+    slot(p.g_ds, (size_t)p.L * p.M, 1);
+    slot(p.d_ds, (size_t)2 * p.M, 1);
+    slot(p.d_stat, (size_t)2 * p.L, 2);
+    slot(p.g_hoa, (size_t)p.A * p.H, 1);
+    slot(reinterpret_cast<float *>(p.view), 1, 1);
+    r->stream_floats = off;
+    CK(cudaMallocHost(&r->h_graph, std::max<size_t>(off, 1) * sizeof(float)));
+    init_stream_shadow(r.get());
+  }
   CK(cudaStreamSynchronize(r->stream));
 
   r->kernels_per_call = (C > 0) + (p.H > 0) + (p.N > 0) + 4;
@@ -762,6 +813,7 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
   return guarded(r, [&] {
+    r->shadow_valid = false;   // the single-period graph path has to see all tables again
     Layout &p = r->lay;
     if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
     if (!output) throw InvalidArgument{"output must not be NULL"};
@@ -802,6 +854,89 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
   });
 }
 
+// One period through the captured graph.  Returns false when the call has to take the plain path:
+// tables prepared on the device, profiling on, a NULL port while the host copy of the tables is stale,
+// or graphs unavailable.  Argument errors throw before anything is queued.
+static bool stream_call_as_graph(bear_cuda_renderer *r, const float *const *objects_input,
+                                 const float *const *direct_speakers_input, const float *const *hoa_input,
+                                 const bear_cuda_block_tables *tables, float *const *output)
+{
+  Layout &p = r->lay;
+  const size_t B = p.B;
+  if (!r->graph_ok || !tables || r->profiling || !r->h_graph) return false;
+  const float *host[8] = {tables->direct_gains, tables->diffuse_gains, tables->direct_delays,
+                          tables->direct_speakers_gains, tables->direct_speakers_delays, tables->static_delays,
+                          tables->hoa_gains, nullptr};
+  float *dev[8] = {p.g_dir, p.g_dif, p.d_dir, p.g_ds, p.d_ds, p.d_stat, p.g_hoa, reinterpret_cast<float *>(p.view)};
+  const bool have_view = tables->brir_index && tables->brir_index[0] >= 0;
+  if (have_view && tables->brir_index[0] >= p.V) throw InvalidArgument{"brir_index out of range"};
+  host[7] = have_view ? reinterpret_cast<const float *>(tables->brir_index) : nullptr;
+  if (!r->shadow_valid)
+    for (auto &sl : r->stream_slots)
+      for (int i = 0; i < 8; i++)
+        if (dev[i] == sl.dev && !host[i]) return false;
+  // audio
+  int row = 0;
+  auto gather = [&](const float *const *ptrs, int count, const char *name) {
+    if (count && !ptrs) throw InvalidArgument{std::string(name) + " input must not be NULL"};
+    for (int i = 0; i < count; i++)
+      if (!ptrs[i]) throw InvalidArgument{std::string(name) + " channel pointer is NULL"};
+    for (int i = 0; i < count; i++, row++) std::memcpy(r->h_graph + (size_t)row * B, ptrs[i], B * sizeof(float));
+  };
+  gather(objects_input, p.N, "objects");
+  gather(direct_speakers_input, p.M, "direct_speakers");
+  gather(hoa_input, p.H, "hoa");
+  for (auto &sl : r->stream_slots)
+    for (int i = 0; i < 8; i++)
+      if (dev[i] == sl.dev && host[i]) std::memcpy(r->h_graph + sl.off, host[i], sl.count * sizeof(float));
+  r->shadow_valid = true;
+
+  if (!r->graph_exec) {
+    // capture once: upload, scatter, the kernels of one period, read-back
+    UnpackPlan plan{};
+    plan.audio = r->d_pack;
+    plan.rows = row;
+    for (auto &sl : r->stream_slots) {
+      float *dst = sl.dev + sl.slot * sl.count;
+      plan.item[plan.n++] = UnpackItem{r->d_pack + sl.off, dst, (int)sl.count};
+    }
+    const uint64_t launches0 = r->launches;
+    cudaGraph_t g = nullptr;
+    bool ok = cudaStreamBeginCapture(r->stream, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
+    if (ok) {
+      try {
+        CK(cudaMemcpyAsync(r->d_pack, r->h_graph, r->stream_floats * sizeof(float), cudaMemcpyHostToDevice, r->stream));
+        launch_unpack(p, plan, r->stream);
+        r->launches++;
+        run_pipeline(r, 1);
+        CK(cudaMemcpy2DAsync(r->h_out, B * sizeof(float), p.out, p.os * sizeof(float), B * sizeof(float), 2,
+                             cudaMemcpyDeviceToHost, r->stream));
+      } catch (...) {
+        ok = false;
+      }
+      if (cudaStreamEndCapture(r->stream, &g) != cudaSuccess) ok = false;
+    }
+    if (ok && cudaGraphInstantiate(&r->graph_exec, g, 0) != cudaSuccess) ok = false;
+    r->graph_launch_count = r->launches - launches0;
+    r->launches = launches0;
+    if (!ok) {   // no graphs here: stay on the plain path for good
+      if (g) cudaGraphDestroy(g);
+      r->graph_exec = nullptr;
+      r->graph_ok = false;
+      r->shadow_valid = false;
+      cudaGetLastError();
+      return false;
+    }
+    r->graph = g;
+  }
+  CK(cudaGraphLaunch(r->graph_exec, r->stream));
+  r->launches += r->graph_launch_count;
+  CK(cudaStreamSynchronize(r->stream));
+  std::memcpy(output[0], r->h_out, B * sizeof(float));
+  std::memcpy(output[1], r->h_out + B, B * sizeof(float));
+  return true;
+}
+
 int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
                       const float *const *direct_speakers_input, const float *const *hoa_input,
                       const bear_cuda_block_tables *tables, float *const *output)
@@ -811,6 +946,8 @@ int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
     Layout &p = r->lay;
     if (!output || !output[0] || !output[1]) throw InvalidArgument{"output must not be NULL"};
     const size_t B = p.B;
+    if (stream_call_as_graph(r, objects_input, direct_speakers_input, hoa_input, tables, output)) return;
+    r->shadow_valid = false;   // this call goes the plain way: the graph path's host copy of the tables goes stale
     int row = 0;
     auto gather = [&](const float *const *ptrs, int count, const char *name) {
       if (count && !ptrs) throw InvalidArgument{std::string(name) + " input must not be NULL"};
@@ -872,6 +1009,7 @@ int bear_cuda_control_tables(bear_cuda_renderer *r, uint32_t T, const float *obj
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
   return guarded(r, [&] {
+    r->shadow_valid = false;   // the single-period graph path has to see all tables again
     Layout &p = r->lay;
     cudaStream_t st = r->stream;
     if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
@@ -930,6 +1068,7 @@ int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T)
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
   return guarded(r, [&] {
+    r->shadow_valid = false;   // the single-period graph path has to see all tables again
     if (T == 0 || (int)T > r->lay.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
     run_pipeline(r, (int)T);
   });
@@ -939,6 +1078,7 @@ int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T)
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
   return guarded(r, [&] {
+    r->shadow_valid = false;   // the single-period graph path has to see all tables again
     Layout &p = r->lay;
     if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
     const size_t need = (size_t)T * 2 * 2 * p.KS * p.B * sizeof(float2);

@@ -170,6 +170,45 @@ def test_calls_of_irregular_length(oracle, small_data):
     check(out, ref, "irregular calls")
 
 
+def test_single_period_calls_mixed_with_batch_calls(oracle, small_data):
+    """Single-period calls run as one captured graph that keeps a host copy of the tables so that a
+    port passed as NULL means "unchanged"; a batch call in between makes that copy stale, after which
+    NULL ports must still mean "as in the previous period" (the batch call's last one)."""
+    from bear_b200.renderer import Renderer
+    B, T = 128, 26
+    ctl = control.HostControl(small_data)
+    rng = np.random.default_rng(33)
+    yaw = np.repeat(30.0 * rng.integers(0, 6, size=T // 2), 2)          # the view changes every other period
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, 2)), obj_diffuse=[0.2, .8], ds_speakers=[3],
+                    hoa_gains=np.eye(16, 4, dtype=np.float32), H=4, yaw_deg=yaw)
+    obj, ds, hoa = (control.synth_audio(c, T * B, s) for c, s in ((2, 0), (1, 100), (4, 200)))
+    ref = ref_render(oracle, small_data, 2, 1, 4, B, tb, obj, ds, hoa)
+    out = np.empty((2, T * B), np.float32)
+
+    def single(r, k):
+        t = tb.block(k)
+        if k > 0 and tb["brir_index"][k] == tb["brir_index"][k - 1]:     # ports the reference writes on change only
+            t["brir_index"], t["static_delays"] = -1, None
+        if k > 0:
+            t["hoa_gains"] = None
+        s = slice(k * B, (k + 1) * B)
+        out[:, s] = r.process(obj[:, s], ds[:, s], hoa[:, s], t)
+
+    with Renderer(small_data, 2, 1, 4, B, max_batch_blocks=8) as r:
+        k = 0
+        for kind, n in [("single", 5), ("batch", 7), ("single", 6), ("batch", 3), ("single", 5)]:
+            if kind == "single":
+                for _ in range(n):
+                    single(r, k)
+                    k += 1
+            else:
+                a, b = k * B, (k + n) * B
+                out[:, a:b] = r.process_batch(obj[:, a:b], ds[:, a:b], hoa[:, a:b], tb.slice(k, k + n))
+                k += n
+        assert k == T
+    check(out, ref, "single-period and batch calls mixed")
+
+
 def test_more_views_than_the_grouping_table_holds(oracle):
     """A data file with more views than the grouping kernel's histogram (2560) renders through the
     ungrouped kernel; an out-of-range brir_index is still refused."""
