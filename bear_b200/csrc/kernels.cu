@@ -1440,6 +1440,58 @@ void launch_unpack(const Layout &p, const UnpackPlan &plan, cudaStream_t st)
   unpack_kernel<<<32, 256, 0, st>>>(p, plan);
 }
 
+// ----------------------------------------------------------------------------------------------
+// frames_kernel: interleaved file frames (float32 or PCM, frame = one sample of every file channel)
+// -> the planar float input rows.  tracks[i] = file channel of input row i (objects, DirectSpeakers,
+// HOA in that order), -1 = silence.  A CTA turns a tile of 64 frames x 32 rows through shared memory:
+// reads run along the frame (consecutive rows are mostly consecutive file channels), writes along time.
+// PCM scaling: sample / 2^(bits-1).   grid: (ceil(frames/64), ceil(rows/32)); block: 256.
+// ----------------------------------------------------------------------------------------------
+__device__ __forceinline__ float frame_sample(const unsigned char *frames, size_t index, int format)
+{
+  switch (format) {
+    case 1: return (float)reinterpret_cast<const short *>(frames)[index] * (1.0f / 32768.0f);
+    case 2: {
+      const unsigned char *b = frames + 3 * index;
+      const int v = (int)((unsigned)b[0] << 8 | (unsigned)b[1] << 16 | (unsigned)b[2] << 24) >> 8;   // sign-extended
+      return (float)v * (1.0f / 8388608.0f);
+    }
+    case 3: return (float)reinterpret_cast<const int *>(frames)[index] * (1.0f / 2147483648.0f);
+    default: return reinterpret_cast<const float *>(frames)[index];
+  }
+}
+
+__global__ void __launch_bounds__(256) frames_kernel(Layout p, const unsigned char *frames, int format, int frame_channels,
+                                                     const int *tracks, int rows, int first_frame, int nframes)
+{
+  __shared__ float tile[32][65];
+  const int f0 = blockIdx.x * 64, r0 = blockIdx.y * 32;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = r0 + lane;
+  const int ch = row < rows ? tracks[row] : -1;
+  for (int f = warp; f < 64; f += 8) {
+    float v = 0.f;
+    if (ch >= 0 && f0 + f < nframes) v = frame_sample(frames, (size_t)(first_frame + f0 + f) * frame_channels + ch, format);
+    tile[lane][f] = v;
+  }
+  __syncthreads();
+  for (int rr = warp; rr < 32; rr += 8) {
+    if (r0 + rr >= rows) break;
+    float *dst = p.xin + (size_t)(r0 + rr) * p.xs + p.hist + first_frame + f0;
+    for (int f = lane; f < 64; f += 32)
+      if (f0 + f < nframes) dst[f] = tile[rr][f];
+  }
+}
+
+void launch_frames(const Layout &p, const void *frames, int format, int frame_channels, const int *tracks, int rows,
+                   int first_frame, int nframes, cudaStream_t st)
+{
+  if (rows <= 0 || nframes <= 0) return;
+  dim3 grid((nframes + 63) / 64, (rows + 31) / 32);
+  frames_kernel<<<grid, 256, 0, st>>>(p, static_cast<const unsigned char *>(frames), format, frame_channels, tracks, rows,
+                                      first_frame, nframes);
+}
+
 void launch_carry(const CarryPlan &plan, cudaStream_t st)
 {
   const long long cols = (long long)plan.fdl_channels * plan.fdl_B;

@@ -103,6 +103,9 @@ constexpr int kMaxUnpack = 10;
 struct UnpackPlan { UnpackItem item[kMaxUnpack]; int n; const float *audio; int rows; };
 void launch_unpack(const Layout &p, const UnpackPlan &plan, cudaStream_t st);
 void launch_control(const Layout &p, int T, cudaStream_t st);
+// interleaved file frames (format: 0 f32, 1 s16, 2 packed s24, 3 s32) -> planar input rows
+void launch_frames(const Layout &p, const void *frames, int format, int frame_channels, const int *tracks, int rows,
+                   int first_frame, int nframes, cudaStream_t st);
 cudaError_t configure_kernels(int B);
 cudaError_t configure_mix(int hist, int B);
 

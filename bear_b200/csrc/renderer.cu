@@ -109,6 +109,10 @@ struct bear_cuda_renderer {
   // parameter of a one-period call is constant, only the contents of h_graph change.  h_graph holds
   // the audio and ALL tables of the period at fixed offsets; a port passed as NULL keeps last period's
   // values there, which is valid as long as the last call went through this path (shadow_valid).
+  // offline rendering from interleaved file frames: raw frames of one call and the track map (grown on demand)
+  unsigned char *d_frames = nullptr;
+  size_t d_frames_bytes = 0;
+  int *d_tracks = nullptr;
   float *h_graph = nullptr;
   struct StreamSlot { size_t off, count; float *dev; size_t slot; };
   std::vector<StreamSlot> stream_slots;    // direct gains, diffuse gains, ..., view (order of bear_cuda_process)
@@ -142,6 +146,8 @@ struct bear_cuda_renderer {
     for (auto &c : ev_pending)
       for (cudaEvent_t e : c) cudaEventDestroy(e);
     for (cudaEvent_t e : ev_free) cudaEventDestroy(e);
+    if (d_frames) cudaFree(d_frames);
+    if (d_tracks) cudaFree(d_tracks);
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
     if (graph) cudaGraphDestroy(graph);
     if (h_graph) cudaFreeHost(h_graph);
@@ -365,8 +371,10 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   p.R = p.Tmax + p.P;
   r->chunk = (int)cfg.chunk_blocks;
   // host-buffer path: upload in ~12 chunks (at least 16 periods each) so copies overlap the kernels
-  r->h2d_chunk = cfg.chunk_blocks ? (int)cfg.chunk_blocks : std::max(16, (p.Tmax + 11) / 12);
-  r->h2d_events.resize((p.Tmax + r->h2d_chunk - 1) / r->h2d_chunk);
+  // host-buffer paths upload in chunks: chunk_blocks periods if configured, else sized per call by
+  // host_chunk_periods() (at least 16 periods)
+  r->h2d_chunk = cfg.chunk_blocks ? (int)cfg.chunk_blocks : 0;
+  r->h2d_events.resize((p.Tmax + (r->h2d_chunk ? r->h2d_chunk : 16) - 1) / (r->h2d_chunk ? r->h2d_chunk : 16));
   r->done_events.resize(r->h2d_events.size());
   for (cudaEvent_t &e : r->h2d_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
   for (cudaEvent_t &e : r->done_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -484,6 +492,21 @@ static std::vector<int> uniform_chunks(int T, int chunk)
   for (int k0 = 0; k0 < T; k0 += chunk) v.push_back(std::min(chunk, T - k0));
   return v;
 }
+// Periods per upload chunk of a host-buffer call whose period takes bytes_per_period on the bus.
+// A chunk of any size needs ~0.15 ms to pass through the six kernels, so a chunk should take at least
+// that long to upload (~11 MB at the 55 GB/s measured on PCIe 5 x16), or the kernels, not the bus,
+// pace the call.
+static int host_chunk_periods(const bear_cuda_renderer *r, int T, size_t bytes_per_period)
+{
+  if (r->h2d_chunk) return r->h2d_chunk;
+  const size_t want = (11u << 20) / std::max<size_t>(bytes_per_period, 1) + 1;
+  return (int)std::min<size_t>((size_t)T, std::max<size_t>(16, want));
+}
+static size_t table_bytes_per_period(const Layout &p)
+{
+  return sizeof(float) * ((size_t)2 * p.L * p.N + 2 * p.N + (size_t)p.L * p.M + 2 * p.M + 2 * p.L + (size_t)p.A * p.H + 1);
+}
+
 // Queue the kernels for T blocks whose audio and tables are already in the staging areas.
 // A call may be issued in chunks (all kernels of chunk c, then chunk c+1, ...): every intermediate
 // buffer is indexed by the period number within the call, so later chunks just read earlier
@@ -820,13 +843,14 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
     if (p.N && !objects) throw InvalidArgument{"objects input must not be NULL"};
     if (p.M && !direct_speakers) throw InvalidArgument{"direct_speakers input must not be NULL"};
     if (p.H && !hoa) throw InvalidArgument{"hoa input must not be NULL"};
-    // Uploads go to their own stream in chunks of h2d_chunk periods, the render stream waits for
+    // Uploads go to their own stream in chunks of periods, the render stream waits for
     // chunk c before it queues the kernels of chunk c: copies of later chunks overlap the kernels.
     cudaStream_t cs = r->copy_stream;
     upload_tables(r, (int)T, tables, false, cs);
     // (Shorter chunks towards the end do not pay: a chunk of a few periods still takes ~0.1 ms to
     // go through the six kernels, longer than its upload.)
-    const std::vector<int> chunks = uniform_chunks((int)T, r->h2d_chunk);
+    const std::vector<int> chunks = uniform_chunks(
+        (int)T, host_chunk_periods(r, (int)T, (size_t)(p.N + p.M + p.H) * p.B * sizeof(float) + table_bytes_per_period(p)));
     for (int k0 = 0, c = 0; k0 < (int)T; k0 += chunks[c], c++) {
       const size_t col = (size_t)k0 * p.B, width = (size_t)chunks[c] * p.B * sizeof(float);
       auto up_audio = [&](int row0, int rows, const float *host, size_t stride) {
@@ -842,6 +866,67 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
     // finished chunks are read back on a third stream while later chunks still upload and render
     run_pipeline(
         r, (int)T, chunks, [&](int c, int, int) { CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0)); },
+        [&](int c, int k0, int n) {
+          CK(cudaEventRecord(r->done_events[c], r->stream));
+          CK(cudaStreamWaitEvent(r->d2h_stream, r->done_events[c], 0));
+          CK(cudaMemcpy2DAsync(output + (size_t)k0 * p.B, out_stride * sizeof(float), p.out + (size_t)k0 * p.B,
+                               p.os * sizeof(float), (size_t)n * p.B * sizeof(float), 2, cudaMemcpyDeviceToHost,
+                               r->d2h_stream));
+        });
+    CK(cudaStreamSynchronize(r->d2h_stream));
+    CK(cudaStreamSynchronize(r->stream));
+  });
+}
+
+int bear_cuda_process_batch_frames(bear_cuda_renderer *r, uint32_t T, const void *frames, uint32_t format,
+                                   uint32_t frame_channels, const int32_t *tracks,
+                                   const bear_cuda_block_tables *tables, float *output, size_t out_stride)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    r->shadow_valid = false;
+    Layout &p = r->lay;
+    const int rows = p.N + p.M + p.H;
+    if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
+    if (!output) throw InvalidArgument{"output must not be NULL"};
+    if (format > BEAR_CUDA_FRAMES_S32) throw InvalidArgument{"unknown frame format"};
+    if (rows && (!frames || !tracks || frame_channels == 0)) throw InvalidArgument{"frames and tracks must not be NULL"};
+    for (int i = 0; i < rows; i++)
+      if (tracks[i] < -1 || tracks[i] >= (int)frame_channels) throw InvalidArgument{"track index out of range"};
+    static const size_t bytes_per_sample[4] = {4, 2, 3, 4};
+    const size_t frame_bytes = (size_t)frame_channels * bytes_per_sample[format];
+    const size_t total = (size_t)T * p.B * frame_bytes;
+    if (rows) {
+      if (total > r->d_frames_bytes) {   // first call (or a wider file than before): grow the staging buffer
+        CK(cudaStreamSynchronize(r->stream));
+        if (r->d_frames) { cudaFree(r->d_frames); r->device_bytes -= r->d_frames_bytes; }
+        r->d_frames = nullptr;
+        r->d_frames_bytes = 0;
+        CK(cudaMalloc(&r->d_frames, total));
+        r->d_frames_bytes = total;
+        r->device_bytes += total;
+      }
+      if (!r->d_tracks) CK(cudaMalloc(&r->d_tracks, (size_t)rows * sizeof(int)));
+    }
+    cudaStream_t cs = r->copy_stream;
+    if (rows) CK(cudaMemcpyAsync(r->d_tracks, tracks, (size_t)rows * sizeof(int), cudaMemcpyHostToDevice, cs));
+    upload_tables(r, (int)T, tables, false, cs);
+    const std::vector<int> chunks =
+        uniform_chunks((int)T, host_chunk_periods(r, (int)T, (size_t)p.B * frame_bytes + table_bytes_per_period(p)));
+    for (int k0 = 0, c = 0; k0 < (int)T; k0 += chunks[c], c++) {
+      const size_t off = (size_t)k0 * p.B * frame_bytes, bytes = (size_t)chunks[c] * p.B * frame_bytes;
+      if (rows)
+        CK(cudaMemcpyAsync(r->d_frames + off, static_cast<const unsigned char *>(frames) + off, bytes,
+                           cudaMemcpyHostToDevice, cs));
+      CK(cudaEventRecord(r->h2d_events[c], cs));
+    }
+    run_pipeline(
+        r, (int)T, chunks,
+        [&](int c, int k0, int n) {
+          CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0));
+          launch_frames(p, r->d_frames, (int)format, (int)frame_channels, r->d_tracks, rows, k0 * p.B, n * p.B, r->stream);
+          if (rows) r->launches++;
+        },
         [&](int c, int k0, int n) {
           CK(cudaEventRecord(r->done_events[c], r->stream));
           CK(cudaStreamWaitEvent(r->d2h_stream, r->done_events[c], 0));

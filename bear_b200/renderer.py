@@ -92,7 +92,7 @@ EXPORTS = (
     "bear_cuda_host_alloc", "bear_cuda_host_free", "bear_cuda_read_data_file_info",
     "bear_cuda_tenf_read_f32", "bear_cuda_set_profiling", "bear_cuda_get_profile",
     "bear_cuda_process_device_static_scratch", "bear_cuda_control_tables", "bear_cuda_reset",
-    "bear_cuda_create_shared",
+    "bear_cuda_create_shared", "bear_cuda_process_batch_frames",
 )
 STATIC_SCRATCH_BYTES = 4 << 20
 NUM_KERNELS = 8
@@ -129,6 +129,7 @@ def lib():
         l.bear_cuda_last_error.restype = C.c_char_p
         l.bear_cuda_process.argtypes = [vp, vp, vp, vp, C.POINTER(Tables), vp]
         l.bear_cuda_process_batch.argtypes = [vp, u32, vp, sz, vp, sz, vp, sz, C.POINTER(Tables), vp, sz]
+        l.bear_cuda_process_batch_frames.argtypes = [vp, u32, vp, u32, u32, _i32p, C.POINTER(Tables), vp, sz]
         l.bear_cuda_get_device_io.argtypes = [vp, C.POINTER(DeviceIO)]
         l.bear_cuda_process_device.argtypes = [vp, u32]
         l.bear_cuda_process_device_static_scratch.argtypes = [vp, u32]
@@ -354,6 +355,32 @@ class Renderer:
         self._check(self._l.bear_cuda_process_batch(self._h, T, o, os_, d, ds_, h, hs_,
                                                     None if tables is None else C.byref(t),
                                                     C.c_void_p(out.ctypes.data), out.strides[0] // 4))
+        return out
+
+    FRAME_FORMATS = {"f32": 0, "s16": 1, "s24": 2, "s32": 3}
+
+    def process_batch_frames(self, frames, tracks, tables, fmt=None, frame_channels=None, output=None):
+        """T periods straight from a file's interleaved frames: `frames` is [T*B, channels] float32 /
+        int16 / int32, or a flat uint8 array of packed 3-byte samples with fmt="s24" and
+        frame_channels given; `tracks` [N+M+H] = file channel of every input (-1 = silence)."""
+        frames = np.ascontiguousarray(frames)
+        if fmt is None:
+            fmt = {np.dtype(np.float32): "f32", np.dtype(np.int16): "s16", np.dtype(np.int32): "s32"}[frames.dtype]
+        if frame_channels is None:
+            frame_channels = frames.shape[1]
+        T = int(np.asarray(tables["brir_index"]).shape[0])
+        bps = {"f32": 4, "s16": 2, "s24": 3, "s32": 4}[fmt]
+        if frames.nbytes < T * self.B * frame_channels * bps:
+            raise ValueError("frames hold fewer than %d periods" % T)
+        tr = np.ascontiguousarray(tracks, dtype=np.int32)
+        if tr.shape != (self.N + self.M + self.H,):
+            raise ValueError("tracks must have one entry per input channel")
+        keep = [frames, tr]
+        out = np.empty((2, T * self.B), np.float32) if output is None else output
+        t = self._tables_struct(tables, keep)
+        self._check(self._l.bear_cuda_process_batch_frames(
+            self._h, T, C.c_void_p(frames.ctypes.data), self.FRAME_FORMATS[fmt], int(frame_channels),
+            tr.ctypes.data_as(_i32p), C.byref(t), C.c_void_p(out.ctypes.data), out.strides[0] // 4))
         return out
 
     def render(self, objects, direct_speakers, hoa, tables, batch=None):

@@ -314,6 +314,23 @@ def run_ours(args, rank, world, local_rank):
     step_copy()
     ms_copy = timed(step_copy, e2e_steps) / e2e_steps
 
+    # ---- the same call fed with the file's interleaved frames (float and 16-bit PCM): what a file
+    # renderer holds after reading a block of a BW64 file; de-interleaving / PCM decoding on the device
+    frames_res = {}
+    if world == 1:
+        tracks = np.arange(N, dtype=np.int32)
+        for fmt, dt, scale in (("f32", np.float32, 1.0), ("s16", np.int16, 32768.0)):
+            h_frames = pinned_empty((T * B, N), dt)
+            h_frames[...] = np.clip(np.round(audio.T * scale), -scale, scale - 1) if fmt != "f32" else audio.T
+
+            def step_frames():
+                r.process_batch_frames(h_frames, tracks, h_tb, output=h_out)
+
+            step_frames()
+            ms_f = timed(step_frames, e2e_steps) / e2e_steps
+            frames_res[fmt] = {"ms_per_step": ms_f, "h2d_bytes_per_step": int(h_frames.nbytes + h2d - audio.nbytes),
+                               "value": N * audio_s_of(T, B) / (ms_f * 1e-3)}
+
     # ---- real-time use: one period per call through bear_cuda_process (host pointers), wall clock ----
     stream_ms = None
     stream_kernels = None
@@ -477,6 +494,9 @@ def run_ours(args, rank, world, local_rank):
                     "h2d_copy_only_ms": ms_copy, "h2d_copy_only_gbs": h2d / ms_copy * 1e-6,
                     "api": "bear_cuda_process_batch (pinned host buffers)" if world == 1 else
                            "bear_cuda_process_batch (pinned host buffers) -> NCCL all-reduce of the partial mixes -> pinned host"},
+            "e2e_file_frames": dict(frames_res, note="bear_cuda_process_batch_frames: interleaved frames as read from "
+                                                     "the file (pinned), same tables; not the headline e2e (that is the "
+                                                     "reference-facing float call above)") if frames_res else None,
             "gpu_launches": int(launches),
             "many_objects": many,
             "control_tail": control_ms,
@@ -506,6 +526,10 @@ def emit(line):
     else:
         sys.stdout.write(data.decode())
         sys.stdout.flush()
+
+
+def audio_s_of(T, B):
+    return T * B / FS
 
 
 def main():

@@ -136,6 +136,23 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
                             size_t hoa_stride, const bear_cuda_block_tables *tables, float *output,
                             size_t out_stride);
 
+/* The same straight from a file's interleaved sample frames (frame f = one sample of each of the
+ * file's frame_channels channels), the form in which bear-render holds a block it has read from
+ * the BW64 file before it slices it per track (bear/render_cli.py:205-213; the slicing and the
+ * PCM decoding happen in ear.fileio / the Python wrapper, which are not in the reference tree, so
+ * this entry point has no single counterpart there).  frames: [T*B][frame_channels] samples of
+ * `format`; tracks: [N+M+H] file channel of every input in the order objects, DirectSpeakers,
+ * HOA, -1 = silence.  PCM samples are scaled by 2^-(bits-1); S24 is packed 3-byte little-endian.
+ * De-interleaving and conversion run on the device, so a 16-bit file costs half the upload of its
+ * float form.  Equal, bit for bit, to bear_cuda_process_batch on the converted samples. */
+#define BEAR_CUDA_FRAMES_F32 0u
+#define BEAR_CUDA_FRAMES_S16 1u
+#define BEAR_CUDA_FRAMES_S24 2u
+#define BEAR_CUDA_FRAMES_S32 3u
+int bear_cuda_process_batch_frames(bear_cuda_renderer *r, uint32_t T, const void *frames, uint32_t format,
+                                   uint32_t frame_channels, const int32_t *tracks,
+                                   const bear_cuda_block_tables *tables, float *output, size_t out_stride);
+
 /* ---- control tail on the device ----------------------------------------
 
  * Replaces, for T periods at once, the table producers that sit between the gain calculators and

@@ -209,6 +209,49 @@ def test_single_period_calls_mixed_with_batch_calls(oracle, small_data):
     check(out, ref, "single-period and batch calls mixed")
 
 
+@pytest.mark.parametrize("fmt", ["f32", "s16", "s24", "s32"])
+def test_interleaved_file_frames(small_data, fmt):
+    """bear_cuda_process_batch_frames: interleaved file frames (float or PCM), a track map with gaps,
+    a silent input and a permutation; bit-equal to the planar float call on the decoded samples."""
+    from bear_b200.renderer import Renderer
+    B, T, C_file = 256, 19, 11                      # 19 periods: chunked upload with a ragged last chunk
+    N, M, H = 4, 2, 4
+    tracks = np.array([7, 0, -1, 3, 10, 9, 1, 2, 4, 5], np.int32)
+    ctl = control.HostControl(small_data)
+    rng = np.random.default_rng(5)
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, N)), obj_diffuse=[0, .4, 1, .1], ds_speakers=[2, 6],
+                    hoa_gains=np.eye(16, 4, dtype=np.float32), H=4, yaw_deg=30.0 * rng.integers(0, 4, size=T))
+    x = 0.25 * rng.standard_normal((T * B, C_file))
+    if fmt == "f32":
+        frames, decoded = x.astype(np.float32), x.astype(np.float32)
+        kw = {}
+    elif fmt == "s16":
+        frames = np.clip(np.round(x * 32768.0), -32768, 32767).astype(np.int16)
+        decoded, kw = frames.astype(np.float32) / np.float32(32768.0), {}
+    elif fmt == "s32":
+        frames = np.clip(np.round(x * 2147483648.0), -2**31, 2**31 - 1).astype(np.int32)
+        decoded, kw = (frames.astype(np.float64) / 2147483648.0).astype(np.float32), {}
+        decoded = frames.astype(np.float32) * np.float32(1.0 / 2147483648.0)   # int -> float rounds, then exact scaling
+    else:
+        v = np.clip(np.round(x * 8388608.0), -2**23, 2**23 - 1).astype(np.int32)
+        b = np.empty((T * B, C_file, 3), np.uint8)
+        b[..., 0], b[..., 1], b[..., 2] = v & 0xFF, (v >> 8) & 0xFF, (v >> 16) & 0xFF
+        frames, decoded = b.reshape(-1), v.astype(np.float32) / np.float32(8388608.0)
+        kw = {"fmt": "s24", "frame_channels": C_file}
+    planar = np.zeros((N + M + H, T * B), np.float32)
+    for i, c in enumerate(tracks):
+        if c >= 0:
+            planar[i] = decoded[:, c]
+    with Renderer(small_data, N, M, H, B, max_batch_blocks=T) as r:
+        want = r.process_batch(planar[:N], planar[N:N + M], planar[N + M:], tb)
+    with Renderer(small_data, N, M, H, B, max_batch_blocks=T) as r:
+        got = r.process_batch_frames(frames, tracks, tb, **kw)
+        assert np.abs(want).max() > 0.02
+        np.testing.assert_array_equal(got, want)
+        with pytest.raises(ValueError, match="track"):
+            r.process_batch_frames(frames, np.where(tracks == 10, 11, tracks), tb, **kw)
+
+
 def test_more_views_than_the_grouping_table_holds(oracle):
     """A data file with more views than the grouping kernel's histogram (2560) renders through the
     ungrouped kernel; an out-of-range brir_index is still refused."""
