@@ -104,8 +104,11 @@ int bear_cuda_create_from_file(const bear_cuda_config *config, const char *data_
  * allocations instead of the transform of all V*2L BRIRs -- what DynamicRenderer's background thread
  * exists to hide in the reference (constructor_thread.cpp) -- and N instances for a batch of files
  * hold one copy of the 212 MB table. */
+/* (No counterpart in the reference: every bear::Renderer loads and transforms its own tables,
+ * api.cpp:238-251.) */
 int bear_cuda_create_shared(const bear_cuda_config *config, const bear_cuda_renderer *share_with, bear_cuda_renderer **out);
 
+/* Replaces bear::Renderer::~Renderer (api.cpp:285). */
 void bear_cuda_destroy(bear_cuda_renderer *r);
 
 /* Put the renderer back into the state of a freshly constructed one (all histories, the frequency-
@@ -115,7 +118,9 @@ void bear_cuda_destroy(bear_cuda_renderer *r);
 int bear_cuda_reset(bear_cuda_renderer *r);
 
 /* Message of the last failure on this renderer (or, with r == NULL, of the last failed create on
- * this thread).  Valid until the next call on the same renderer/thread. */
+ * this thread).  Valid until the next call on the same renderer/thread.  Stands in for the what()
+ * of the exceptions the reference throws (std::invalid_argument api.cpp:68-72,158-159;
+ * std::runtime_error data_file.cpp:16-20, panner.cpp:43-46): no exception crosses the C ABI. */
 const char *bear_cuda_last_error(const bear_cuda_renderer *r);
 
 /* ---- per-period processing: replaces what flow.process() does for the DSP atoms -------------- */
@@ -190,9 +195,12 @@ typedef struct bear_cuda_device_io {
   void *stream;            /* cudaStream_t all work of this renderer is ordered on */
 } bear_cuda_device_io;
 
+/* No counterpart in the reference (its ports are host memory, dsp.hpp:46-71): the same port tables
+ * and audio rows as bear_cuda_process_batch, already on the device. */
 int bear_cuda_get_device_io(bear_cuda_renderer *r, bear_cuda_device_io *io);
 
-/* Render T periods from the staging areas; asynchronous on io.stream. */
+/* Render T periods from the staging areas; asynchronous on io.stream.  What flow.process() does
+ * (api.cpp:151-153) for T periods, with nothing crossing PCIe. */
 int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T);
 
 /* No counterpart in the reference (its DSP graph owns ordinary heap buffers).
@@ -218,7 +226,8 @@ int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T);
 #define BEAR_CUDA_STATIC_SCRATCH_BYTES (4u << 20)
 int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T);
 
-/* Block until all work queued on the renderer's stream has finished. */
+/* Block until all work queued on the renderer's stream has finished (no counterpart: the
+ * reference's process() is synchronous). */
 int bear_cuda_synchronize(bear_cuda_renderer *r);
 
 /* ---- introspection --------------------------------------------------------------------------- */
@@ -237,10 +246,13 @@ typedef struct bear_cuda_info {
   uint32_t cmac_items_last, cmac_splits_last;
 } bear_cuda_info;
 
+/* No counterpart in the reference (num_partitions is what rbbl::CoreConvolverUniform derives from
+ * the filter length, dsp.cpp:73-87; the default delays are panner.cpp:172-186). */
 int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
 
 /* Per-kernel device timing (CUDA events on the renderer's stream, recorded around every kernel
- * while enabled).  bear_cuda_get_profile synchronises the stream and fills
+ * while enabled); no counterpart in the reference (its benchmark times whole process() calls,
+ * visr_bear/test/benchmark.cpp:97-201).  bear_cuda_get_profile synchronises the stream and fills
  * BEAR_CUDA_NUM_KERNELS entries, indexed by the BEAR_CUDA_KERNEL_* ids. */
 #define BEAR_CUDA_KERNEL_MIX 0
 #define BEAR_CUDA_KERNEL_HOA_MIX 1
@@ -283,7 +295,8 @@ int bear_cuda_read_data_file_info(const char *data_path, bear_cuda_data_file_inf
 int bear_cuda_tenf_read_f32(const char *path, const char *key, float *out, size_t capacity, size_t *count,
                             uint32_t *shape, uint32_t *ndim);
 
-/* Pinned host memory helpers for callers that want true asynchronous copies. */
+/* Pinned host memory helpers for callers that want true asynchronous copies (no counterpart in the
+ * reference: its buffers never leave the host). */
 void *bear_cuda_host_alloc(size_t bytes);
 void bear_cuda_host_free(void *p);
 
