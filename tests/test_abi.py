@@ -47,3 +47,21 @@ def test_argument_errors_before_device(small_data):
         renderer.Renderer("", 1, 0, 0, 512)
     with pytest.raises(renderer.BearCudaError, match="power of two"):
         renderer.Renderer(small_data, 1, 0, 0, 500)
+
+
+def test_every_entry_point_names_its_reference_counterpart():
+    """include/bear_cuda.h: the comment in front of every exported function cites the reference
+    interface it replaces (file:line) or says that there is none."""
+    import re
+    lines = (ROOT / "include" / "bear_cuda.h").read_text().split("\n")
+    for name in renderer.EXPORTS:
+        at = [i for i, l in enumerate(lines) if re.search(r"\b%s\(" % name, l) and not l.lstrip().startswith("*")]
+        assert at, name
+        i, doc = at[0], ""
+        while not doc.strip() and i > 0:   # declarations that follow each other share one comment
+            j = i
+            while j > 0 and not re.search(r"\bbear_cuda_\w+\([^)]*\)?.*;\s*$|^#ifdef __cplusplus", lines[j - 1]):
+                j -= 1                     # back to the end of the previous declaration
+            doc = "\n".join(lines[j:i])
+            i = j - 1
+        assert re.search(r"\w+\.(cpp|hpp|py):\d+", doc) or "ounterpart" in doc, name
