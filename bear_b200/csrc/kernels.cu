@@ -187,8 +187,12 @@ __device__ __forceinline__ void fft_first_pass_reg(float2 (&v)[8], float2 *out, 
 // the padded index of element j + r*stride is padi(j) + r*(stride + stride/8), a constant offset
 // from one base address per butterfly instead of eight index computations.
 // FIRST = 1: the first radix-8 pass has been done by fft_first_pass_reg (its output is in `a`).
-template <bool INV, int LOGM, int NTHR, int FIRST = 0>
-__device__ __forceinline__ float2 *fft_shared_c(float2 *a, float2 *b, const float2 *__restrict__ tw, int tid)
+// UPPER_OUT: the last pass stores elements M/2 .. M-1 of the result to upper_out[0 .. M/2) (global
+// memory, consecutive threads consecutive elements) instead of shared memory -- the overlap-save
+// output of an inverse transform, whose lower half is discarded.
+template <bool INV, int LOGM, int NTHR, int FIRST = 0, bool UPPER_OUT = false>
+__device__ __forceinline__ float2 *fft_shared_c(float2 *a, float2 *b, const float2 *__restrict__ tw, int tid,
+                                                float2 *__restrict__ upper_out = nullptr)
 {
   constexpr int M = 1 << LOGM, Q = M >> 3, QP = Q + (Q >> 3);
   constexpr int NP = LOGM / 3, REM = LOGM % 3;
@@ -225,7 +229,13 @@ __device__ __forceinline__ float2 *fft_shared_c(float2 *a, float2 *b, const floa
         dft8<INV>(v);
         float2 *bp = b + padi(((j - k) << 3) + k);
 #pragma unroll
-        for (int r = 0; r < 8; r++) bp[pass == 0 ? r : r * NsP] = v[r];   // pass 0: padi(8j + r) = 9j + r
+        for (int r = 0; r < 8; r++) {
+          if (UPPER_OUT && REM == 0 && pass == NP - 1) {   // last pass: Ns = M/8, element j + r M/8
+            if (r >= 4) upper_out[j + (r - 4) * Q] = v[r];
+          } else {
+            bp[pass == 0 ? r : r * NsP] = v[r];            // pass 0: padi(8j + r) = 9j + r
+          }
+        }
       }
     }
     float2 *t = a; a = b; b = t;
@@ -246,7 +256,11 @@ __device__ __forceinline__ float2 *fft_shared_c(float2 *a, float2 *b, const floa
         float2 x0, x1, x2, x3;
         dft4<INV>(v0, v1, v2, v3, x0, x1, x2, x3);
         float2 *bp = b + padi(((j - k) << 2) + k);
-        bp[0] = x0; bp[NsP] = x1; bp[2 * NsP] = x2; bp[3 * NsP] = x3;
+        if (UPPER_OUT) {                                   // last pass: Ns = M/4, element j + r M/4
+          upper_out[j] = x2; upper_out[j + Q4] = x3;
+        } else {
+          bp[0] = x0; bp[NsP] = x1; bp[2 * NsP] = x2; bp[3 * NsP] = x3;
+        }
       }
     }
     float2 *t = a; a = b; b = t;
@@ -262,8 +276,12 @@ __device__ __forceinline__ float2 *fft_shared_c(float2 *a, float2 *b, const floa
         const float2 v0 = ap[0];
         const float2 v1 = twid<INV>(ap[HhP], ldtw(tw, k << (LOGM - ls), M));
         float2 *bp = b + padi(((j - k) << 1) + k);
-        bp[0] = cadd(v0, v1);
-        bp[NsP] = csub(v0, v1);
+        if (UPPER_OUT) {                                   // last pass: Ns = M/2, element j + r M/2
+          upper_out[j] = csub(v0, v1);
+        } else {
+          bp[0] = cadd(v0, v1);
+          bp[NsP] = csub(v0, v1);
+        }
       }
     }
     float2 *t = a; a = b; b = t;
@@ -724,9 +742,9 @@ __global__ void decorrelate_kernel(Layout p, int T)
       o[padi(M - kk)] = zm;
     }
   }
-  float2 *y = fft_shared_c<true, LOGB, NTHR>(o, z, p.tw, tid);
+  // inverse transform; its last pass writes the kept half (the last B samples) straight to the row
   float2 *dst = reinterpret_cast<float2 *>(p.w + (size_t)l * p.ws + p.B + p.hist + (size_t)k * p.B);
-  for (int n = tid; n < M / 2; n += nthr) dst[n] = y[padi(M / 2 + n)];
+  fft_shared_c<true, LOGB, NTHR, 0, true>(o, z, p.tw, tid, dst);
 }
 
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
