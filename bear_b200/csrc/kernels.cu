@@ -441,203 +441,287 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 }
 
 // ----------------------------------------------------------------------------------------------
-// mix_kernel: objects + DirectSpeakers onto the 2L direct bus and the L diffuse bus.
-// grid: (T*B/kMixTile, S); block: kMixTile.  One output sample per thread, all 3*24 outputs in
-// registers; the gains of kMixChunk channels are staged in shared memory with their per-block
-// deltas so the inner loop is one FMA for the ramped gain + one FMA per ear.
+// mix_prep_kernel: one record per (period, channel) for mix_kernel -- the per-ear delay ramp in
+// samples (validated against the history length, then clamped) and the channel's NON-ZERO gains as
+// short lists of (loudspeaker, start value, per-period delta).  Panning gains are sparse: a point
+// source feeds 2-4 of the 24 loudspeakers, so mix_kernel walks these lists instead of the dense
+// [L x N] tables of rcl::GainMatrix (per_ear_delay.cpp:31-36, dsp.cpp:127-129); terms it skips would
+// have added exact zeros.  A channel with more than kMixK non-zero gains (extent, "dense") is marked
+// and takes the table-driven path of mix_kernel.
+// Record (24 words): [d0L, ddL, d0R, ddR | nd + 256 nq, 4 direct speakers (bytes), 4 diffuse
+// speakers, - | 4 x (g0, dg) direct | 4 x (q0, dq) diffuse]; nd / nq = 255: dense.
+// grid: (ceil((N+M)/128), periods); block 128; one thread per channel (coalesced table reads).
 // ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
+{
+  const int c = blockIdx.x * 128 + threadIdx.x, k = p.k0 + blockIdx.y;
+  const int C = p.N + p.M, L = p.L;
+  if (c >= C) return;
+  const bool obj = c < p.N;
+  const int ci = obj ? c : c - p.N, ld = obj ? p.N : p.M;
+  float *rec = p.mix_recs + ((size_t)k * C + c) * kMixRecWords;
+  // delays of periods k-1 (slot k) and k (slot k+1), seconds -> samples
+  const float *ds = (obj ? p.d_dir : p.d_ds) + (size_t)k * 2 * ld + 2 * ci;
+  const float dmax = (float)(p.hist - 4);
+  float4 dl;
+  {
+    float a0 = ds[0] * p.fs, a1 = ds[2 * ld] * p.fs, b0 = ds[1] * p.fs, b1 = ds[2 * ld + 1] * p.fs;
+    // a table delay outside [0, history - 4] cannot be rendered (the reference allows up to 1 s,
+    // per_ear_delay.cpp:25): flagged, reported by the call, and clamped so that no read leaves the tile
+    if (!(a1 >= 0.f && a1 <= dmax) || !(b1 >= 0.f && b1 <= dmax)) atomicOr(p.err_flag, kErrDelayRange);
+    a0 = fminf(fmaxf(a0, 0.f), dmax); a1 = fminf(fmaxf(a1, 0.f), dmax);
+    b0 = fminf(fmaxf(b0, 0.f), dmax); b1 = fminf(fmaxf(b1, 0.f), dmax);
+    dl = make_float4(a0, a1 - a0, b0, b1 - b0);
+  }
+  unsigned cnt[2] = {0u, 0u}, spk[2] = {0u, 0u};
+  const int nlists = obj ? 2 : 1;
+  for (int w = 0; w < nlists; w++) {
+    const float *g = (w ? p.g_dif : (obj ? p.g_dir : p.g_ds)) + (size_t)k * L * ld + ci;
+    float2 *dst = reinterpret_cast<float2 *>(rec + 8 + 8 * w);
+    for (int l = 0; l < L; l++) {
+      const float g0 = g[(size_t)l * ld], g1 = g[(size_t)(L + l) * ld];
+      if (g0 != 0.f || g1 != 0.f) {
+        if (cnt[w] < (unsigned)kMixK) {
+          dst[cnt[w]] = make_float2(g0, g1 - g0);
+          spk[w] |= (unsigned)l << (8 * cnt[w]);
+        }
+        cnt[w]++;
+      }
+    }
+    if (cnt[w] > (unsigned)kMixK) cnt[w] = 255u;
+  }
+  reinterpret_cast<float4 *>(rec)[0] = dl;
+  reinterpret_cast<uint4 *>(rec)[1] = make_uint4(cnt[0] | cnt[1] << 8, spk[0], spk[1], 0u);
+}
+
+// ----------------------------------------------------------------------------------------------
+// mix_kernel: objects + DirectSpeakers onto the 2L direct bus and the L diffuse bus.
+//   cdir[2l+e][t] = sum_c g_c,l(t) * D[x_c, tau_c,e(t)](t)      (per_ear_delay.cpp:22-56)
+//   qdif[l][t]    = sum_c q_c,l(t) * x_c(t)                     (dsp.cpp:127-129)
+// grid: (periods * B / kMixTile, S); block: kMixTile.  One output sample per thread; the 24 (left,
+// right) direct-bus accumulators are packed pairs, so one FFMA2 adds a channel to both ears of a
+// loudspeaker.  The CTA walks its channels in chunks of kMixChunk: input rows (history + tile) and
+// the chunk's records arrive by bulk copies (TMA, 1-D) on an mbarrier, double buffered, so the copies
+// of chunk i+1 run under the arithmetic of chunk i.  Per channel: two Lagrange-3 reads at the ramped
+// per-ear delays, then one ramped-gain FMA + one FFMA2 per non-zero loudspeaker.  Which accumulator a
+// list entry feeds is the same for all threads (the lists are per channel and period), so the
+// dispatch is a CTA-uniform switch.
+// ----------------------------------------------------------------------------------------------
+#define BEAR_CASES24(M) M(0) M(1) M(2) M(3) M(4) M(5) M(6) M(7) M(8) M(9) M(10) M(11) M(12) M(13) M(14) M(15) M(16) \
+  M(17) M(18) M(19) M(20) M(21) M(22) M(23)
+
+__device__ __forceinline__ void mix_add_direct(f32x2 (&acc)[kMaxSpeakers], unsigned l, f32x2 g2, f32x2 x2)
+{
+#define BEAR_CASE(i) case i: acc[i] = fma2(g2, x2, acc[i]); break;
+  switch (l) { BEAR_CASES24(BEAR_CASE) default: break; }
+#undef BEAR_CASE
+}
+__device__ __forceinline__ void mix_add_diffuse(float (&acc)[kMaxSpeakers], unsigned l, float g, float x)
+{
+#define BEAR_CASE(i) case i: acc[i] = fmaf(g, x, acc[i]); break;
+  switch (l) { BEAR_CASES24(BEAR_CASE) default: break; }
+#undef BEAR_CASE
+}
+
+__device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
+{
+  unsigned done;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(done) : "r"(bar_addr), "r"(parity) : "memory");
+  } while (!done);
+}
+
 __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
 {
-  // row = one channel: [g0 | dg | q0 | dq] x 24 speakers, padded by 4 floats so that accesses to
-  // consecutive channels at the same speaker spread over 8 banks instead of 1
-  __shared__ __align__(16) float sg[kMixChunk][4 * kMaxSpeakers + 4];
-  __shared__ float sd[kMixChunk][4];
-  // bit g of smask[ii][0/1]: some direct / diffuse gain of speakers 4g..4g+3 is non-zero in this
-  // period.  Panning gains are sparse (a point source feeds <= 3 of 24 loudspeakers), all-zero
-  // groups are skipped with a CTA-uniform branch; skipped terms would have added exact zeros.
-  __shared__ unsigned smask[kMixChunk][2];
-  // input rows of the staged channels: [hist history samples | kMixTile samples of this tile],
-  // filled by one bulk copy per row so that the per-ear fractional-delay reads are shared-memory
-  // reads (the reads themselves are unaligned 4-tap gathers, which made the kernel wait on L2)
-  extern __shared__ __align__(16) float xt[];
+  extern __shared__ __align__(16) float smx[];
   const int XW = p.hist + kMixTile;
+  float *const xt0 = smx;                                    // [2][kMixChunk][XW] input rows
+  float *const rc0 = smx + 2 * kMixChunk * XW;               // [2][kMixChunk][kMixRecWords] records
+  __shared__ __align__(8) unsigned long long bars[2];
   const int tid = threadIdx.x;
   const int t = p.k0 * p.B + blockIdx.x * kMixTile + tid;
   const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
   const int n = t - k * p.B;
   const int s = blockIdx.y;
-  const int C = p.N + p.M;
+  const int C = p.N + p.M, L = p.L;
   const int per = (C + p.S - 1) / p.S;
   const int c0 = s * per, c1 = min(C, c0 + per);
   const float invB = 1.0f / (float)p.B;
   const float rg = (float)(n + p.goff) * invB;
   const float rd = (float)(n + p.doff) * invB;
-  const int L = p.L;
-  const f32x2 rg2 = pack2(rg, rg);
 
-  f32x2 accL[kMaxSpeakers / 2], accR[kMaxSpeakers / 2], accQ[kMaxSpeakers / 2];
+  f32x2 acc[kMaxSpeakers];     // (left, right) of loudspeaker l
+  float accQ[kMaxSpeakers];    // diffuse bus
 #pragma unroll
-  for (int l = 0; l < kMaxSpeakers / 2; l++) accL[l] = accR[l] = accQ[l] = 0ull;
+  for (int l = 0; l < kMaxSpeakers; l++) { acc[l] = 0ull; accQ[l] = 0.f; }
 
-  __shared__ __align__(8) unsigned long long xbar;   // completion of the bulk copies into xt
-  const unsigned xbar_addr = (unsigned)__cvta_generic_to_shared(&xbar);
-  unsigned xphase = 0;
+  const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
   if (tid == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(xbar_addr) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  for (int cb = c0; cb < c1; cb += kMixChunk) {
-    const int cnt = min(kMixChunk, c1 - cb);
-    __syncthreads();
-    if (tid < 2 * kMixChunk) smask[tid >> 1][tid & 1] = 0u;
-    if (tid < 32) {
-      // one bulk copy (TMA, 1-D) per input row, issued by the lanes of warp 0; the rows land on xbar
-      if (tid == 0)
-        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(xbar_addr), "r"(cnt * XW * 4) : "memory");
-      __syncwarp();
-      if (tid < cnt) {
-        const float *src = p.xin + (size_t)(cb + tid) * p.xs + (t - tid);   // column (hist + t0) - hist
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(xt + tid * XW);
-        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                     ::"r"(dst), "l"(src), "r"(XW * 4), "r"(xbar_addr) : "memory");
-      }
+  __syncthreads();
+  const int nchunks = (c1 - c0 + kMixChunk - 1) / kMixChunk;
+  // warp 0 requests chunk ci: one bulk copy per input row (lane = row) and one for the records
+  auto request = [&](int ci) {
+    const int cb = c0 + ci * kMixChunk, cnt = min(kMixChunk, c1 - cb), st = ci & 1;
+    const unsigned bar = bar0 + 8 * st;
+    if (tid == 0)
+      asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
+                   ::"r"(bar), "r"(cnt * (XW + kMixRecWords) * 4) : "memory");
+    __syncwarp();
+    if (tid < cnt) {
+      const float *src = p.xin + (size_t)(cb + tid) * p.xs + (t - tid);   // column (hist + t0) - hist
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(xt0 + (st * kMixChunk + tid) * XW);
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst), "l"(src), "r"(XW * 4), "r"(bar) : "memory");
     }
-    // gain tables of periods k-1 (slot k) and k (slot k+1) straight into the rows of sg with 4-byte
-    // cp.async (consecutive threads consecutive channels: coalesced reads); deltas are formed below
-#pragma unroll
-    for (int it = 0; it < kMixChunk * kMaxSpeakers / kMixTile; it++) {
-      const int idx = it * kMixTile + tid;
-      const int l = idx / kMixChunk, ii = idx % kMixChunk, c = cb + ii;
-      if (ii < cnt) {
-        float *row = sg[ii];
-        if (l < L) {
-          const float *a0, *a1;
-          if (c < p.N) {
-            a0 = p.g_dir + ((size_t)k * L + l) * p.N + c;
-            a1 = a0 + (size_t)L * p.N;
-            const float *b0 = p.g_dif + ((size_t)k * L + l) * p.N + c;
-            const float *b1 = b0 + (size_t)L * p.N;
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + 2 * kMaxSpeakers + l)), "l"(b0));
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + 3 * kMaxSpeakers + l)), "l"(b1));
-          } else {
-            a0 = p.g_ds + ((size_t)k * L + l) * p.M + (c - p.N);
-            a1 = a0 + (size_t)L * p.M;
-            row[2 * kMaxSpeakers + l] = 0.f; row[3 * kMaxSpeakers + l] = 0.f;
-          }
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + l)), "l"(a0));
-          asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(row + kMaxSpeakers + l)), "l"(a1));
-        } else {
-          row[l] = 0.f; row[kMaxSpeakers + l] = 0.f; row[2 * kMaxSpeakers + l] = 0.f; row[3 * kMaxSpeakers + l] = 0.f;
-        }
-      }
+    if (tid == 0) {
+      const float *src = p.mix_recs + ((size_t)k * C + cb) * kMixRecWords;
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(rc0 + st * kMixChunk * kMixRecWords);
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   ::"r"(dst), "l"(src), "r"(cnt * kMixRecWords * 4), "r"(bar) : "memory");
     }
-    asm volatile("cp.async.commit_group;");
-    for (int idx = tid; idx < cnt * 2; idx += kMixTile) {
-      const int ii = idx >> 1, e = idx & 1, c = cb + ii;
-      float d0, d1;
-      if (c < p.N) {
-        d0 = p.d_dir[(size_t)k * 2 * p.N + 2 * c + e];
-        d1 = p.d_dir[(size_t)(k + 1) * 2 * p.N + 2 * c + e];
-      } else {
-        const int j = c - p.N;
-        d0 = p.d_ds[(size_t)k * 2 * p.M + 2 * j + e];
-        d1 = p.d_ds[(size_t)(k + 1) * 2 * p.M + 2 * j + e];
-      }
-      d0 *= p.fs; d1 *= p.fs;
-      sd[ii][2 * e] = d0; sd[ii][2 * e + 1] = d1 - d0;
-    }
-    asm volatile("cp.async.wait_group 0;");
-    {  // wait for the input rows of this chunk (phase bit flips per use of the barrier)
-      unsigned done;
-      do {
-        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                     : "=r"(done) : "r"(xbar_addr), "r"(xphase) : "memory");
-      } while (!done);
-      xphase ^= 1u;
-    }
-    __syncthreads();
-    // deltas and sparsity masks; consecutive threads consecutive speakers of one channel (conflict-free)
-    for (int idx = tid; idx < cnt * kMaxSpeakers; idx += kMixTile) {
-      const int ii = idx / kMaxSpeakers, l = idx - ii * kMaxSpeakers;
-      float *row = sg[ii];
-      const float g0 = row[l], g1 = row[kMaxSpeakers + l], q0 = row[2 * kMaxSpeakers + l], q1 = row[3 * kMaxSpeakers + l];
-      row[kMaxSpeakers + l] = g1 - g0;
-      row[3 * kMaxSpeakers + l] = q1 - q0;
-      if (g0 != 0.f || g1 != 0.f) atomicOr(&smask[ii][0], 1u << (l >> 2));
-      if (q0 != 0.f || q1 != 0.f) atomicOr(&smask[ii][1], 1u << (l >> 2));
-    }
-    __syncthreads();
-    const float dmax = (float)(p.hist - 4);
-    // Channels are taken two at a time: both channels' fractional-delay gathers (two independent
-    // dependency chains per ear) are issued before either channel's accumulation, which gives the
-    // scheduler work to overlap at the low occupancy the 72 accumulators allow.
-    constexpr int UC = 4;   // channels whose delayed reads are issued together
-    for (int ii = 0; ii < cnt; ii += UC) {
-      float xl2[UC], xR2[UC], x02[UC];
+  };
+  if (tid < 32 && nchunks > 0) request(0);
+  for (int ci = 0; ci < nchunks; ci++) {
+    const int st = ci & 1;
+    if (tid < 32 && ci + 1 < nchunks) request(ci + 1);   // its buffer was released by the barrier below
+    mbar_wait(bar0 + 8 * st, (ci >> 1) & 1);
+    const int cb = c0 + ci * kMixChunk, cnt = min(kMixChunk, c1 - cb);
+    const float *xrow = xt0 + st * kMixChunk * XW + p.hist + tid;
+    const float *recs = rc0 + st * kMixChunk * kMixRecWords;
+    // channels two at a time: both channels' delayed reads are issued before either's accumulation
+    constexpr int UC = 2;
+    for (int j0 = 0; j0 < cnt; j0 += UC) {
+      f32x2 x2[UC];
 #pragma unroll
       for (int u = 0; u < UC; u++) {
-        const int j = min(ii + u, cnt - 1);
-        const float *xr = xt + j * XW + p.hist + tid;
-        unpack2(delayed_read2(xr, fminf(ramped_delay(sd[j][0], sd[j][1], rd), dmax),
-                              xr, fminf(ramped_delay(sd[j][2], sd[j][3], rd), dmax)), xl2[u], xR2[u]);
-        x02[u] = xr[0];
+        const int j = min(j0 + u, cnt - 1);
+        const float4 dl = *reinterpret_cast<const float4 *>(recs + j * kMixRecWords);
+        const float *xr = xrow + j * XW;
+        x2[u] = delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
       }
 #pragma unroll
       for (int u = 0; u < UC; u++) {
-        const int j = ii + u;
+        const int j = j0 + u;
         if (j >= cnt) break;
-        const unsigned md = smask[j][0], mq = smask[j][1];
-        const ulonglong2 *g0v = reinterpret_cast<const ulonglong2 *>(sg[j]);
-        const ulonglong2 *dgv = g0v + kMaxSpeakers / 4;
-        const ulonglong2 *q0v = g0v + 2 * kMaxSpeakers / 4;
-        const ulonglong2 *dqv = g0v + 3 * kMaxSpeakers / 4;
-        const f32x2 xl = pack2(xl2[u], xl2[u]), xR = pack2(xR2[u], xR2[u]), x0 = pack2(x02[u], x02[u]);
-        if (md) {
-#pragma unroll
-          for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
-            if (md & (1u << l4)) {
-              const ulonglong2 g0 = g0v[l4], dg = dgv[l4];
-              const f32x2 ga = fma2(rg2, dg.x, g0.x), gb = fma2(rg2, dg.y, g0.y);
-              accL[2 * l4] = fma2(ga, xl, accL[2 * l4]);         accR[2 * l4] = fma2(ga, xR, accR[2 * l4]);
-              accL[2 * l4 + 1] = fma2(gb, xl, accL[2 * l4 + 1]); accR[2 * l4 + 1] = fma2(gb, xR, accR[2 * l4 + 1]);
-            }
+        const float *rec = recs + j * kMixRecWords;
+        const uint4 meta = *reinterpret_cast<const uint4 *>(rec + 4);
+        const unsigned nd = meta.x & 0xffu, nq = meta.x >> 8;
+        if (nd <= (unsigned)kMixK) {
+          unsigned spk = meta.y;
+#pragma unroll 1
+          for (unsigned i = 0; i < nd; i++, spk >>= 8) {
+            const float2 gd = *reinterpret_cast<const float2 *>(rec + 8 + 2 * i);
+            mix_add_direct(acc, spk & 0xffu, splat2(fmaf(rg, gd.y, gd.x)), x2[u]);
           }
-        }
-        if (mq) {
+        } else {   // dense gains: the table itself, every thread the same address
+          const int c = cb + j;
+          const bool obj = c < p.N;
+          const int ld = obj ? p.N : p.M;
+          const float *g = (obj ? p.g_dir + (size_t)k * L * ld + c : p.g_ds + (size_t)k * L * ld + (c - p.N));
 #pragma unroll
-          for (int l4 = 0; l4 < kMaxSpeakers / 4; l4++) {
-            if (mq & (1u << l4)) {
-              const ulonglong2 q0 = q0v[l4], dq = dqv[l4];
-              accQ[2 * l4] = fma2(fma2(rg2, dq.x, q0.x), x0, accQ[2 * l4]);
-              accQ[2 * l4 + 1] = fma2(fma2(rg2, dq.y, q0.y), x0, accQ[2 * l4 + 1]);
+          for (int l = 0; l < kMaxSpeakers; l++)
+            if (l < L) {
+              const float g0 = __ldg(g + (size_t)l * ld), g1 = __ldg(g + (size_t)(L + l) * ld);
+              acc[l] = fma2(splat2(fmaf(rg, g1 - g0, g0)), x2[u], acc[l]);
             }
+        }
+        if (nq) {
+          const float x0 = xrow[j * XW];
+          if (nq <= (unsigned)kMixK) {
+            unsigned spk = meta.z;
+#pragma unroll 1
+            for (unsigned i = 0; i < nq; i++, spk >>= 8) {
+              const float2 qd = *reinterpret_cast<const float2 *>(rec + 16 + 2 * i);
+              mix_add_diffuse(accQ, spk & 0xffu, fmaf(rg, qd.y, qd.x), x0);
+            }
+          } else {
+            const int c = cb + j;
+            const float *g = p.g_dif + (size_t)k * L * p.N + c;
+#pragma unroll
+            for (int l = 0; l < kMaxSpeakers; l++)
+              if (l < L) {
+                const float g0 = __ldg(g + (size_t)l * p.N), g1 = __ldg(g + (size_t)(L + l) * p.N);
+                accQ[l] = fmaf(fmaf(rg, g1 - g0, g0), x0, accQ[l]);
+              }
           }
         }
       }
     }
+    __syncthreads();   // every thread is done with buffer st before warp 0 requests chunk ci + 2 into it
   }
-  const size_t col = (size_t)p.B + t;
+  // split 0 writes the bus rows themselves, the other splits their partial sums (bus_sum_kernel adds them)
+  float *od, *oq;
+  size_t os;
+  if (s == 0) {
+    od = p.cdir + (size_t)p.B + t; oq = p.qdif + (size_t)p.B + t; os = p.cs;
+  } else {
+    od = p.bus_part + (size_t)(s - 1) * 3 * L * p.bps + (t - p.k0 * p.B); oq = od + (size_t)2 * L * p.bps; os = p.bps;
+  }
 #pragma unroll
-  for (int l2 = 0; l2 < kMaxSpeakers / 2; l2++) {
-    float vL[2], vR[2], vQ[2];
-    unpack2(accL[l2], vL[0], vL[1]); unpack2(accR[l2], vR[0], vR[1]); unpack2(accQ[l2], vQ[0], vQ[1]);
-#pragma unroll
-    for (int h = 0; h < 2; h++) {
-      const int l = 2 * l2 + h;
-      if (l < L) {
-        p.cdir[((size_t)s * 2 * L + 2 * l) * p.cs + col] = vL[h];
-        p.cdir[((size_t)s * 2 * L + 2 * l + 1) * p.cs + col] = vR[h];
-        p.qdif[((size_t)s * L + l) * p.cs + col] = vQ[h];
-      }
+  for (int l = 0; l < kMaxSpeakers; l++) {
+    if (l < L) {
+      float vL, vR;
+      unpack2(acc[l], vL, vR);
+      od[(size_t)(2 * l) * os] = vL;
+      od[(size_t)(2 * l + 1) * os] = vR;
+      oq[(size_t)l * os] = accQ[l];
     }
   }
 }
 
+// bus_sum_kernel: bus row += the partial sums of object splits 1..S-1, in split order (launches that
+// are too short to fill the GPU with one CTA per tile split their channels over several CTAs).
+// grid: (ceil(periods * B / 1024), 3L); block 256; four samples per thread.
+__global__ void __launch_bounds__(256) bus_sum_kernel(Layout p, int T)
+{
+  const int row = blockIdx.y, L = p.L;
+  const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
+  if (i >= (size_t)T * p.B) return;
+  float *dst = (row < 2 * L ? p.cdir + (size_t)row * p.cs : p.qdif + (size_t)(row - 2 * L) * p.cs) + (size_t)(p.k0 + 1) * p.B + i;
+  float4 v = *reinterpret_cast<float4 *>(dst);
+  for (int s = 1; s < p.S; s++) {
+    const float4 a = *reinterpret_cast<const float4 *>(p.bus_part + ((size_t)(s - 1) * 3 * L + row) * p.bps + i);
+    v.x += a.x; v.y += a.y; v.z += a.z; v.w += a.w;
+  }
+  *reinterpret_cast<float4 *>(dst) = v;
+}
+
 size_t mix_smem_bytes(int hist);
+void launch_mix_prep(const Layout &p, int T, cudaStream_t st)
+{
+  mix_prep_kernel<<<dim3((p.N + p.M + 127) / 128, T), 128, 0, st>>>(p, T);
+}
 void launch_mix(const Layout &p, int T, cudaStream_t st)
 {
   dim3 grid(T * p.B / kMixTile, p.S);
   mix_kernel<<<grid, kMixTile, mix_smem_bytes(p.hist), st>>>(p, T);
+}
+void launch_bus_sum(const Layout &p, int T, cudaStream_t st)   // only launches with S > 1
+{
+  bus_sum_kernel<<<dim3((T * p.B + 1023) / 1024, 3 * p.L), 256, 0, st>>>(p, T);
+}
+
+// validate_views_kernel: tables written by a device-side producer are not seen by the host, so the
+// view indices of a device-resident call are checked here: out-of-range ones raise the error flag and
+// are replaced by view 0, so that no later kernel indexes the filter table out of bounds.
+__global__ void __launch_bounds__(256) validate_views_kernel(Layout p, int T)
+{
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= T) return;
+  const int v = p.view[1 + i];
+  if (v < 0 || v >= p.V) {
+    atomicOr(p.err_flag, kErrViewRange);
+    p.view[1 + i] = 0;
+  }
+}
+void launch_validate_views(const Layout &p, int T, cudaStream_t st)
+{
+  validate_views_kernel<<<(T + 255) / 256, 256, 0, st>>>(p, T);
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -703,7 +787,8 @@ __global__ void decorrelate_kernel(Layout p, int T)
   extern __shared__ float2 sm[];
   constexpr int M = 1 << LOGB, NTHR = (M >> 3) < 32 ? 32 : (M >> 3);
   float2 *a = sm, *b = sm + M + (M >> 3);
-  const int l = blockIdx.x % p.L, k = p.k0 + blockIdx.x / p.L;
+  const int nl = p.l1 - p.l0;                                  // loudspeakers this rank convolves
+  const int l = p.l0 + blockIdx.x % nl, k = p.k0 + blockIdx.x / nl;
   const int tid = threadIdx.x;
   constexpr int nthr = NTHR;
   // window [block k-1 | block k] of the diffuse bus (sum of the partials) straight into the registers
@@ -713,8 +798,10 @@ __global__ void decorrelate_kernel(Layout p, int T)
 #pragma unroll
   for (int r = 0; r < 8; r++) v0[r] = make_float2(0.f, 0.f);
   if (tid < Q) {
-    for (int s = 0; s < p.S; s++) {
-      const float2 *src = reinterpret_cast<const float2 *>(p.qdif + ((size_t)s * p.L + l) * p.cs + (size_t)k * p.B) + tid;
+    // the diffuse bus is the sum of every rank's object group (one rank: its own row); peer rows are
+    // read straight from the peers' memory over NVLink with ordinary loads
+    for (int w = 0; w < p.W; w++) {
+      const float2 *src = reinterpret_cast<const float2 *>(p.peer_qdif[w] + (size_t)l * p.cs + (size_t)k * p.B) + tid;
       float2 v[8];
 #pragma unroll
       for (int r = 0; r < 8; r++) v[r] = src[r * Q];
@@ -751,7 +838,7 @@ void launch_decorrelate(const Layout &p, int T, cudaStream_t st)
 {
   const int threads = p.B / 8 < 32 ? 32 : p.B / 8;
   const size_t smem = fft_smem_floats2(p.B) * sizeof(float2);
-  dispatch_logb(p.logB, [&](auto lb) { decorrelate_kernel<decltype(lb)::value><<<T * p.L, threads, smem, st>>>(p, T); });
+  dispatch_logb(p.logB, [&](auto lb) { decorrelate_kernel<decltype(lb)::value><<<T * (p.l1 - p.l0), threads, smem, st>>>(p, T); });
 }
 
 // ----------------------------------------------------------------------------------------------
@@ -783,8 +870,10 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
   float *cwin = rows + 2 * RW;                                       // [2][2M] direct-bus windows (S == 1)
   const float invB = 1.0f / (float)p.B;
   const int L2 = 2 * p.L;
-  const bool bus = unit < p.L;
-  const int ch = bus ? 2 * unit + g : L2 + 2 * (unit - p.L) + g;
+  const int nl = p.l1 - p.l0;                                        // loudspeakers this rank convolves
+  const bool bus = unit < nl;
+  const int spk = p.l0 + unit, hu = unit - nl;                       // loudspeaker / HOA channel pair
+  const int ch = bus ? 2 * spk + g : L2 + 2 * hu + g;
   const bool active = bus || ch < L2 + p.A;                          // odd A: last group idles
 
   // static delays at the ends of blocks k-2, k-1, k (table slot = block + 2); loaded before the
@@ -794,6 +883,10 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
     ta = p.d_stat[(size_t)k * L2 + ch] * p.fs;
     tb = p.d_stat[(size_t)(k + 1) * L2 + ch] * p.fs;
     tc = p.d_stat[(size_t)(k + 2) * L2 + ch] * p.fs;
+    // same rule as the per-channel delays (mix_prep_kernel): flag, then clamp to what the staged row holds
+    const float dmax = (float)(p.hist - 4);
+    if (tid == 0 && !(tc >= 0.f && tc <= dmax)) atomicOr(p.err_flag, kErrDelayRange);
+    ta = fminf(fmaxf(ta, 0.f), dmax); tb = fminf(fmaxf(tb, 0.f), dmax); tc = fminf(fmaxf(tc, 0.f), dmax);
   }
   // stage the source rows -- columns [k*B, k*B + hist + 2B) of the (B + hist)-prefixed row -- and, for
   // bus units, both ears' direct-bus windows [block k-1 | block k]: one bulk copy (TMA, 1-D) each,
@@ -805,17 +898,17 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
     asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(sbar_addr) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     const unsigned row_bytes = (unsigned)RW * 4u, win_bytes = 2u * M * 4u;
-    const int nrows = bus ? (p.N > 0 ? 1 : 0) : min(2, p.A - 2 * (unit - p.L));
+    const int nrows = bus ? (p.dif ? 1 : 0) : min(2, p.A - 2 * hu);
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;"
                  ::"r"(sbar_addr), "r"(nrows * row_bytes + (cstaged ? 2u * win_bytes : 0u)) : "memory");
     for (int r = 0; r < nrows; r++) {
-      const float *src = (bus ? p.w + (size_t)unit * p.ws : p.amb + (size_t)(2 * (unit - p.L) + r) * p.ws) + (size_t)k * p.B;
+      const float *src = (bus ? p.w + (size_t)spk * p.ws : p.amb + (size_t)(2 * hu + r) * p.ws) + (size_t)k * p.B;
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                    ::"r"((unsigned)__cvta_generic_to_shared(rows + r * RW)), "l"(src), "r"(row_bytes), "r"(sbar_addr) : "memory");
     }
     if (cstaged)
       for (int r = 0; r < 2; r++) {
-        const float *src = p.cdir + (size_t)(2 * unit + r) * p.cs + (size_t)k * p.B;
+        const float *src = p.cdir + (size_t)(2 * spk + r) * p.cs + (size_t)k * p.B;
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"((unsigned)__cvta_generic_to_shared(cwin + r * 2 * M)), "l"(src), "r"(win_bytes), "r"(sbar_addr) : "memory");
       }
@@ -836,7 +929,7 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
   if (active) {
     if (bus) {
       const float *wrow = rows + p.hist;    // window sample 0
-      const bool dif = p.N > 0;
+      const bool dif = p.dif != 0;
       const float dda = tb - ta, ddb = tc - tb;
       const float2 *cw = reinterpret_cast<const float2 *>(cwin + g * 2 * M);
       if (tid < Q) {
@@ -846,9 +939,9 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
           float2 v = make_float2(0.f, 0.f);
           if (cstaged) {
             v = cw[n];
-          } else {
-            for (int s = 0; s < p.S; s++) {
-              const float2 c = reinterpret_cast<const float2 *>(p.cdir + ((size_t)s * L2 + ch) * p.cs + (size_t)k * p.B)[n];
+          } else {   // every rank's object group; peer rows are read over NVLink with ordinary loads
+            for (int w = 0; w < p.W; w++) {
+              const float2 c = reinterpret_cast<const float2 *>(p.peer_cdir[w] + (size_t)ch * p.cs + (size_t)k * p.B)[n];
               v.x += c.x; v.y += c.y;
             }
           }
@@ -895,23 +988,25 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
 
 // shared memory of bus_fdl_kernel; the direct-bus windows are staged only when there is a single
 // partial (S == 1) and everything still fits (it does up to B = 2048)
-static bool bus_fdl_stage_direct(int B, int hist, int S)
+// (bulk copies only ever read this GPU's own rows: with peers, W > 1, the windows are summed by loads)
+static bool bus_fdl_stage_direct(int B, int hist, int W)
 {
   const size_t base = (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float);
-  return S == 1 && base + (size_t)2 * 2 * B * sizeof(float) <= 200 * 1024;
+  return W == 1 && base + (size_t)2 * 2 * B * sizeof(float) <= 200 * 1024;
 }
-static size_t bus_fdl_smem_bytes(int B, int hist, int S)
+static size_t bus_fdl_smem_bytes(int B, int hist, int W)
 {
   return (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float) +
-         (bus_fdl_stage_direct(B, hist, S) ? (size_t)2 * 2 * B * sizeof(float) : 0);
+         (bus_fdl_stage_direct(B, hist, W) ? (size_t)2 * 2 * B * sizeof(float) : 0);
 }
 
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
 {
   const int threads = 2 * (p.B / 8 < 32 ? 32 : p.B / 8);
-  const int nunits = p.L + (p.H > 0 ? (p.A + 1) / 2 : 0);
-  const size_t smem = bus_fdl_smem_bytes(p.B, p.hist, p.S);
-  const int stage = bus_fdl_stage_direct(p.B, p.hist, p.S) ? 1 : 0;
+  const int nunits = (p.l1 - p.l0) + (p.H > 0 ? (p.A + 1) / 2 : 0);
+  if (nunits == 0) return;
+  const size_t smem = bus_fdl_smem_bytes(p.B, p.hist, p.W);
+  const int stage = bus_fdl_stage_direct(p.B, p.hist, p.W) ? 1 : 0;
   dispatch_logb(p.logB, [&](auto lb) {
     bus_fdl_kernel<decltype(lb)::value><<<T * nunits, threads, smem, st>>>(p, T, nunits, stage);
   });
@@ -963,7 +1058,8 @@ __device__ __forceinline__ void cmac_item(const Layout &p, const int (&j)[kCmacG
                                           int T, unsigned maskA, unsigned maskB)
 {
   const int B = p.B, P = p.P, L = p.L, R = p.R;
-  const int nunits = L + (p.H > 0 ? 1 : 0);
+  const int nl = p.l1 - p.l0;                              // units: this rank's loudspeakers, then the HOA decode terms
+  const int nunits = nl + (p.H > 0 ? 1 : 0);
   const int per = (nunits + p.KS - 1) / p.KS;
   const int u0 = ks * per, u1 = min(nunits, u0 + per);
   const bool packed0 = pair == 0;
@@ -978,8 +1074,8 @@ __device__ __forceinline__ void cmac_item(const Layout &p, const int (&j)[kCmacG
   }
   const float4 *fdl4 = reinterpret_cast<const float4 *>(p.fdl) + pair;
   for (int u = u0; u < u1; u++) {
-    if (u < L) {
-      const int ch = 2 * u + e;
+    if (u < nl) {
+      const int ch = 2 * (p.l0 + u) + e;
       const float4 *x = fdl4 + (size_t)ch * R * hB;
       const float4 *h = reinterpret_cast<const float4 *>(p.h_brir) + ((size_t)(v * 2 * L + ch) * P) * hB + pair;
       float4 xb[HAS_B ? CNT : 1];
@@ -1068,9 +1164,10 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
   constexpr int RS = kCmacRingStride;
   constexpr unsigned kStageBytes = W * RS * sizeof(float4);
   const int B = p.B, P = p.P, L = p.L, R = p.R;
-  const int nunits = L + (p.H > 0 ? 1 : 0);
+  const int nl = p.l1 - p.l0;
+  const int nunits = nl + (p.H > 0 ? 1 : 0);
   const int per = (nunits + KS - 1) / KS;
-  const int u0 = ks * per, u1 = min(nunits, u0 + per), ub = min(u1, L);   // [u0, ub): BRIR units
+  const int u0 = ks * per, u1 = min(nunits, u0 + per), ub = min(u1, nl);  // [u0, ub): BRIR units
   const bool packed0 = pair == 0;
   const bool scalar_warp = blockIdx.x == 0 && threadIdx.x < 32;           // the warp with packed bin 0
   const int hB = B >> 1;
@@ -1094,8 +1191,8 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
   for (int g = 0; g < CNT; g++) {
     poff[g] = (HAS_B ? slotA[g] + 1 : slotA[g]) * hB;
   }
-  const float4 *px = fdl4 + (size_t)(2 * u0 + e) * ringlen;
-  const float4 *ph = reinterpret_cast<const float4 *>(p.h_brir) + ((size_t)(v * 2 * L + 2 * u0 + e) * P) * hB + pair;
+  const float4 *px = fdl4 + (size_t)(2 * (p.l0 + u0) + e) * ringlen;
+  const float4 *ph = reinterpret_cast<const float4 *>(p.h_brir) + ((size_t)(v * 2 * L + 2 * (p.l0 + u0) + e) * P) * hB + pair;
   const unsigned ring0 = (unsigned)__cvta_generic_to_shared(ring + threadIdx.x);
   unsigned pdst = ring0;
   int pstage = 0, ppart = first_part, pt = 0;
@@ -1156,7 +1253,7 @@ __device__ __forceinline__ void cmac_item_pipe(const Layout &p, const int (&j)[k
     if (++cstage == S) { cstage = 0; csrc = ring + threadIdx.x; }
   }
   asm volatile("cp.async.wait_group 0;" ::: "memory");
-  if (u0 <= L && L < u1) {   // the HOA decode unit (index L) is in this split
+  if (p.H > 0 && u0 <= nl && nl < u1) {   // the HOA decode unit (index nl) is in this split
     for (int am = 0; am < p.A; am++) {
       const float4 *x = fdl4 + (size_t)(2 * L + am) * ringlen;
       const float4 hv = __ldg(reinterpret_cast<const float4 *>(p.h_hoa) + ((size_t)am * 2 + e) * hB + pair);
@@ -1283,7 +1380,7 @@ __global__ void __launch_bounds__(1024) view_group_kernel(Layout p, int n)
     const int nitems = scanB[1023];
     const int threads = p.B / 2 < 128 ? p.B / 2 : 128;
     const int base = (p.B / 2 / threads) * 2 * max(nitems, 1);
-    const int nunits = p.L + (p.H > 0 ? 1 : 0);
+    const int nunits = (p.l1 - p.l0) + (p.H > 0 ? 1 : 0);
     p.grp_count[0] = nitems;
     p.grp_count[1] = max(1, min(min((12 * 148 + base - 1) / base, nunits), p.KS));
   }
@@ -1669,7 +1766,7 @@ cudaError_t static_scratch_pointer(float2 **out)
   return cudaSuccess;
 }
 
-size_t mix_smem_bytes(int hist) { return (size_t)kMixChunk * (hist + kMixTile) * sizeof(float); }
+size_t mix_smem_bytes(int hist) { return (size_t)2 * kMixChunk * (hist + kMixTile + kMixRecWords) * sizeof(float); }
 
 static int ilog2(int v)
 {

@@ -7,7 +7,13 @@ namespace bearcuda {
 
 constexpr int kMaxSpeakers = 24;  // accumulator tile of the mix kernel (L <= 24)
 constexpr int kMixTile = 128;     // samples per CTA in the mix kernels
-constexpr int kMixChunk = 32;     // channels staged in shared memory per pass
+constexpr int kMixChunk = 16;     // channels staged in shared memory per pass (two passes in flight)
+constexpr int kMixRecWords = 24;  // words of one (period, channel) record of mix_prep_kernel
+constexpr int kMixK = 4;          // non-zero gains a record lists; channels with more take the dense path
+constexpr int kMaxRanks = 8;      // GPUs that can share one scene (bear_cuda_comm_connect)
+// bits of Layout::err_flag (checked by the host after a call has finished)
+constexpr int kErrDelayRange = 1; // a table delay is negative or beyond history_samples - 4
+constexpr int kErrViewRange = 2;  // a brir_index on the device-resident path is outside [0, V)
 constexpr int kCmacGroup = 6;     // periods of one view that share a filter load in the cMAC kernel
 
 // Everything a kernel needs to find its data.  Passed by value (fits the 4 KB param space).
@@ -21,7 +27,7 @@ struct Layout {
   int V;              // views
   int Tmax;           // max blocks per call
   int hist;           // time-domain history (samples) kept in front of every delayed signal
-  int S;              // object splits (partial bus buffers)
+  int S;              // object splits of this launch: mix_kernel CTAs that share a tile
   int KS;             // cMAC splits (partial spectra)
   int R;              // FDL slots per channel (P + Tmax)
   int goff, doff, xoff;  // ramp offsets
@@ -39,8 +45,10 @@ struct Layout {
   float *d_stat;          // [Tmax+2][2L]  slots 0,1 = blocks -2,-1
   int32_t *view;          // [Tmax+1]
   // time-domain intermediates (row stride, prefix)
-  float *cdir;  size_t cs;   // [S][2L][cs]   prefix B
-  float *qdif;               // [S][L][cs]    prefix B
+  float *cdir;  size_t cs;   // [2L][cs]      prefix B   direct bus
+  float *qdif;               // [L][cs]       prefix B   diffuse bus
+  // partial sums of object splits 1..S-1 of one launch, added to cdir/qdif by bus_sum_kernel:
+  float *bus_part; size_t bps;   // [S-1][3L][bps], columns relative to the launch; rows 0..2L-1 direct, 2L..3L-1 diffuse
   float *w;     size_t ws;   // [L][ws]       prefix B+hist  (decorrelator outputs)
   float *amb;                // [A][ws]       prefix B+hist  (HOA decoder inputs)
   // spectra (packed: bin 0 = (DC, Nyquist), bins 1..B-1 complex)
@@ -64,6 +72,13 @@ struct Layout {
   int *grp_sorted;           // [Tmax + 1] period indices relative to k0 - 1, sorted by view
   int2 *grp_items;           // [Tmax + 1] (first, count) into grp_sorted
   int *grp_count;            // [2] number of items, cMAC splits in use (<= KS)
+  // one scene shared by W GPUs (bear_cuda_comm_connect; W = 1: this renderer alone): every rank mixes its
+  // own channels onto its own bus rows, and convolves loudspeakers [l0, l1) of the SUM of all ranks' rows
+  int W, rank, l0, l1;
+  int dif;                   // some rank has objects: the diffuse path runs
+  const float *peer_cdir[kMaxRanks], *peer_qdif[kMaxRanks];   // every rank's bus rows (entry `rank` = own)
+  float *mix_recs;           // [Tmax][N+M][kMixRecWords] records of mix_prep_kernel
+  int *err_flag;             // error bits raised by kernels
   int ks_dev;                // this launch's number of splits is grp_count[1] (grouped launch), not KS
   int k0;                    // first period of this launch (a call may be issued in chunks)
 };
@@ -88,7 +103,10 @@ struct CarryPlan {
 
 void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, int logB, int P, const float2 *tw,
                        float2 *out, float scale, cudaStream_t st);
+void launch_mix_prep(const Layout &p, int T, cudaStream_t st);
 void launch_mix(const Layout &p, int T, cudaStream_t st);
+void launch_bus_sum(const Layout &p, int T, cudaStream_t st);
+void launch_validate_views(const Layout &p, int T, cudaStream_t st);
 void launch_hoa_mix(const Layout &p, int T, cudaStream_t st);
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st);
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st);
