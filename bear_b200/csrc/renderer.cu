@@ -1,6 +1,7 @@
 // Host side of libbear_cuda.so: device state of one renderer and the C ABI of include/bear_cuda.h.
 // Replaces the construction and per-period work of bear::DSP (visr_bear/src/dsp.cpp:7-236).
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <cmath>
@@ -34,7 +35,72 @@ struct InvalidArgument { std::string msg; };
 struct Unsupported { std::string msg; };
 
 size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
-bool mix_hist_too_large(int hist) { return (size_t)kMixChunk * (hist + kMixTile) * sizeof(float) > 160 * 1024; }
+bool mix_hist_too_large(int hist)
+{
+  return (size_t)2 * kMixChunk * (hist + kMixTile + kMixRecWords) * sizeof(float) > 200 * 1024;
+}
+
+// ---- NCCL, bound at run time -------------------------------------------------------------------
+// The library has no link-time dependency on NCCL: a renderer that is never connected to peers needs
+// none, and an embedder that already has NCCL loaded (PyTorch brings its own copy) must not get a
+// second one.  dlopen("libnccl.so.2") returns the copy that is already in the process, else the
+// system's.  Only what the render path uses is bound; the constants are NCCL 2.x ABI (nccl.h).
+struct NcclUniqueId { char internal[128]; };
+typedef void *NcclComm;
+struct NcclApi {
+  void *handle = nullptr;
+  int (*GetVersion)(int *) = nullptr;
+  int (*GetUniqueId)(NcclUniqueId *) = nullptr;
+  int (*CommInitRank)(NcclComm *, int, NcclUniqueId, int) = nullptr;
+  int (*CommDestroy)(NcclComm) = nullptr;
+  int (*AllReduce)(const void *, void *, size_t, int, int, NcclComm, cudaStream_t) = nullptr;
+  int (*Reduce)(const void *, void *, size_t, int, int, int, NcclComm, cudaStream_t) = nullptr;
+  int (*GroupStart)() = nullptr;
+  int (*GroupEnd)() = nullptr;
+  const char *(*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclInt32 = 2, kNcclFloat32 = 7, kNcclSum = 0;
+
+const NcclApi &nccl()
+{
+  static NcclApi api = [] {
+    NcclApi a;
+    a.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!a.handle) throw CudaFail{std::string("NCCL is not available: ") + dlerror()};
+    auto sym = [&](const char *name) {
+      void *f = dlsym(a.handle, name);
+      if (!f) throw CudaFail{std::string("NCCL symbol missing: ") + name};
+      return f;
+    };
+    a.GetVersion = reinterpret_cast<decltype(a.GetVersion)>(sym("ncclGetVersion"));
+    a.GetUniqueId = reinterpret_cast<decltype(a.GetUniqueId)>(sym("ncclGetUniqueId"));
+    a.CommInitRank = reinterpret_cast<decltype(a.CommInitRank)>(sym("ncclCommInitRank"));
+    a.CommDestroy = reinterpret_cast<decltype(a.CommDestroy)>(sym("ncclCommDestroy"));
+    a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(sym("ncclAllReduce"));
+    a.Reduce = reinterpret_cast<decltype(a.Reduce)>(sym("ncclReduce"));
+    a.GroupStart = reinterpret_cast<decltype(a.GroupStart)>(sym("ncclGroupStart"));
+    a.GroupEnd = reinterpret_cast<decltype(a.GroupEnd)>(sym("ncclGroupEnd"));
+    a.GetErrorString = reinterpret_cast<decltype(a.GetErrorString)>(sym("ncclGetErrorString"));
+    return a;
+  }();
+  return api;
+}
+#define NCK(expr)                                                                                         \
+  do {                                                                                                    \
+    int e__ = (expr);                                                                                     \
+    if (e__ != 0) throw CudaFail{std::string(#expr) + ": NCCL error " + nccl().GetErrorString(e__)};      \
+  } while (0)
+
+// What the ranks of one scene tell each other before the first period (bear_cuda_comm_blob).
+struct CommBlob {
+  uint32_t magic, B, Tmax, L;
+  uint64_t cs;
+  uint32_t N, M, H, rank;
+  cudaIpcMemHandle_t bus;
+  NcclUniqueId id;       // rank 0's is the one that counts
+};
+static_assert(sizeof(CommBlob) <= BEAR_CUDA_COMM_BLOB_BYTES, "blob too large");
+constexpr uint32_t kCommMagic = 0x42454152u;   // "BEAR"
 
 }  // namespace
 
@@ -82,6 +148,18 @@ struct bear_cuda_renderer {
   std::vector<cudaEvent_t> h2d_events;     // one per upload chunk
   std::vector<cudaEvent_t> done_events;    // one per rendered chunk
   bool tables_on_device = false;           // bear_cuda_control_tables filled the staging tables
+  int s_cfg = 0;                           // configured object splits (0 = per launch)
+  float *bus[2] = {nullptr, nullptr};      // direct + diffuse bus rows [3L][cs]; [1] only while sharing a scene
+  int parity = 0;                          // which of the two the current call writes
+  int *h_err = nullptr;                    // pinned copy of the kernels' error flags
+  cudaEvent_t ev_order = nullptr;          // orders the copy stream behind the render stream
+  float2 *static_scratch = nullptr;        // device address of the library's built-in scratch array
+  uint64_t calls = 0;                      // process calls since creation / reset
+  // one scene shared with other GPUs (bear_cuda_comm_connect)
+  NcclComm comm = nullptr;
+  int comm_root = -1;                      // rank that receives the mix, -1 = every rank
+  float *peer_bus[kMaxRanks][2] = {};      // every rank's bus rows (cudaIpc mappings), [rank] = own
+  int *d_barrier = nullptr;                // payload of the cross-rank barrier
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -146,6 +224,11 @@ struct bear_cuda_renderer {
     for (auto &c : ev_pending)
       for (cudaEvent_t e : c) cudaEventDestroy(e);
     for (cudaEvent_t e : ev_free) cudaEventDestroy(e);
+    if (comm) nccl().CommDestroy(comm);
+    for (int w = 0; w < kMaxRanks; w++)
+      if (peer_bus[w][0] && w != lay.rank) cudaIpcCloseMemHandle(peer_bus[w][0]);
+    if (h_err) cudaFreeHost(h_err);
+    if (ev_order) cudaEventDestroy(ev_order);
     if (d_frames) cudaFree(d_frames);
     if (d_tracks) cudaFree(d_tracks);
     if (graph_exec) cudaGraphExecDestroy(graph_exec);
@@ -312,6 +395,7 @@ std::shared_ptr<FilterBank> build_bank(const bear_cuda_config &cfg, const bear_c
 }
 
 int cmac_splits_for(const bear_cuda_renderer *r, int n);
+int object_splits_for(const bear_cuda_renderer *r, int n);
 
 bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_ptr<FilterBank> bank)
 {
@@ -350,13 +434,9 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   if (k.hoa_delay + 4 > p.hist) throw Unsupported{"hoa delay exceeds max_delay_samples"};
 
   const int C = p.N + p.M;
-  {
-    const int tiles = p.Tmax * p.B / kMixTile;
-    int S = cfg.object_splits;
-    if (S == 0) S = (2 * 148 + tiles - 1) / tiles;
-    const int maxS = C > 0 ? (C + kMixChunk - 1) / kMixChunk : 1;
-    p.S = std::max(1, std::min(std::min(S, maxS), 16));
-  }
+  r->s_cfg = (int)cfg.object_splits;
+  p.S = 1;
+  p.W = 1; p.rank = 0; p.l0 = 0; p.l1 = p.L; p.dif = p.N > 0;
   {
     // cMAC work units: one per loudspeaker (P partition terms each) + one for the HOA decode terms
     const int nunits = p.L + (p.H > 0 ? 1 : 0);
@@ -393,8 +473,29 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   p.d_stat = r->dalloc<float>((T1 + 1) * 2 * p.L);
   p.view = r->dalloc<int32_t>(T1);
   p.cs = round_up(p.B + TB, 4);
-  p.cdir = r->dalloc<float>((size_t)p.S * 2 * p.L * p.cs);
-  p.qdif = r->dalloc<float>((size_t)p.S * p.L * p.cs);
+  // both bus-row sets in one allocation: a renderer that shares a scene alternates between them from
+  // call to call (its peers read the rows over NVLink), a renderer on its own uses the first
+  r->bus[0] = r->dalloc<float>((size_t)2 * 3 * p.L * p.cs);
+  r->bus[1] = r->bus[0] + (size_t)3 * p.L * p.cs;
+  p.cdir = r->bus[0];
+  p.qdif = r->bus[0] + (size_t)2 * p.L * p.cs;
+  p.peer_cdir[0] = p.cdir; p.peer_qdif[0] = p.qdif;
+  {  // partial sums of the object splits of one launch; sized for the worst launch
+    size_t cap = 0;
+    for (int n = 1; n <= p.Tmax; n++) cap = std::max(cap, (size_t)(object_splits_for(r.get(), n) - 1) * n);
+    p.bps = round_up(std::max<size_t>(cap, 1) * p.B, 4);
+    p.bus_part = r->dalloc<float>((size_t)3 * p.L * p.bps, false);
+  }
+  p.mix_recs = r->dalloc<float>((size_t)p.Tmax * std::max(1, C) * kMixRecWords, false);
+  p.err_flag = r->dalloc<int>(4);
+  CK(cudaMallocHost(&r->h_err, 4 * sizeof(int)));
+  r->h_err[0] = 0;
+  CK(cudaEventCreateWithFlags(&r->ev_order, cudaEventDisableTiming));
+  {  // the library's built-in scratch array, looked up once per renderer with its device current
+    float2 *ss = nullptr;
+    CK(static_scratch_pointer(&ss));
+    r->static_scratch = ss;
+  }
   p.ws = round_up(p.B + p.hist + TB, 4);
   p.w = r->dalloc<float>((size_t)p.L * p.ws);
   p.amb = r->dalloc<float>((size_t)std::max(1, p.A) * p.ws);
@@ -456,7 +557,8 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   }
   CK(cudaStreamSynchronize(r->stream));
 
-  r->kernels_per_call = (C > 0) + (p.H > 0) + (p.N > 0) + 4;
+  r->kernels_per_call = 2 * (C > 0) + (p.H > 0) + (p.N > 0) + 4;   // long launch: one object split, ungrouped cMAC
+  r->error.reserve(512);   // so that reporting an argument error allocates nothing
   return r.release();
 }
 
@@ -484,13 +586,18 @@ int cmac_splits_for(const bear_cuda_renderer *r, int n)
   return std::max(r->ks_cfg, std::min((4 * 148 + base - 1) / base, r->ks_units));
 }
 
-// Chunk sizes of a call of T periods issued `chunk` periods at a time (chunk <= 0: all at once).
-static std::vector<int> uniform_chunks(int T, int chunk)
+// Object splits of a launch of n periods: mix_kernel runs one CTA per (tile of kMixTile samples, split),
+// each walking its share of the channels; a launch with few tiles splits the channels so that there
+// are about two waves of CTAs (4 per SM) -- a 16-period upload chunk of a 1024-object scene is
+// otherwise 32 CTAs that each walk 1024 channels.  The partial sums cost one small extra kernel.
+int object_splits_for(const bear_cuda_renderer *r, int n)
 {
-  std::vector<int> v;
-  if (chunk <= 0 || chunk > T) chunk = T;
-  for (int k0 = 0; k0 < T; k0 += chunk) v.push_back(std::min(chunk, T - k0));
-  return v;
+  const Layout &p = r->lay;
+  const int C = p.N + p.M;
+  const int maxS = std::min(32, C > 0 ? (C + kMixChunk - 1) / kMixChunk : 1);
+  if (r->s_cfg) return std::max(1, std::min(r->s_cfg, maxS));
+  const int tiles = std::max(1, n * p.B / kMixTile);
+  return std::max(1, std::min((2 * 4 * 148 + tiles - 1) / tiles, maxS));
 }
 // Periods per upload chunk of a host-buffer call whose period takes bytes_per_period on the bus.
 // A chunk of any size needs ~0.15 ms to pass through the six kernels, so a chunk should take at least
@@ -508,13 +615,14 @@ static size_t table_bytes_per_period(const Layout &p)
 }
 
 // Queue the kernels for T blocks whose audio and tables are already in the staging areas.
-// A call may be issued in chunks (all kernels of chunk c, then chunk c+1, ...): every intermediate
-// buffer is indexed by the period number within the call, so later chunks just read earlier
-// columns.  `before_chunk(c, k0, n)` runs on the host before chunk c is queued (the host-buffer path
-// uses it to make the stream wait for that chunk's upload), `after_chunk(c, k0, n)` after it.
+// A call may be issued in chunks of `chunk` periods (all kernels of chunk c, then chunk c+1, ...;
+// chunk <= 0: all at once): every intermediate buffer is indexed by the period number within the
+// call, so later chunks just read earlier columns.  `before_chunk(c, k0, n)` runs on the host before
+// chunk c is queued (the host-buffer path uses it to make the stream wait for that chunk's upload),
+// `after_chunk(c, k0, n)` after it.  Nothing here allocates unless per-kernel profiling is on.
 template <class Before, class After>
-void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, Before &&before_chunk,
-                  After &&after_chunk)
+void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk, After &&after_chunk,
+                  bool device_tables = false)
 {
   Layout &p = r->lay;
   cudaStream_t st = r->stream;
@@ -529,21 +637,60 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
     chain.push_back(e);
     if (kernel_id >= 0) ids.push_back(kernel_id);
   };
-  int nchunks = 0, extra_launches = 0;
+  if (chunk <= 0 || chunk > T) chunk = T;
+  const bool shared_scene = p.W > 1;
+  // bus rows of this call; a renderer that shares a scene alternates between its two sets, so that a
+  // peer still reading the previous call's rows is never overwritten (one barrier per chunk suffices)
+  float *const bus = r->bus[r->parity];
+  p.cdir = bus;
+  p.qdif = bus + (size_t)2 * p.L * p.cs;
+  for (int w = 0; w < p.W; w++) {
+    const float *pb = shared_scene ? r->peer_bus[w][r->parity] : bus;
+    p.peer_cdir[w] = pb;
+    p.peer_qdif[w] = pb + (size_t)2 * p.L * p.cs;
+  }
+  p.S = object_splits_for(r, chunk);     // one value per call: chunk c+1 reads the last period of chunk c
+  uint64_t launches = 0;
+  if (device_tables) { launch_validate_views(p, T, st); launches++; }
+  int nchunks = 0;
   for (int k0 = 0; k0 < T; nchunks++) {
-    const int n = chunks[nchunks];
+    const int n = std::min(chunk, T - k0);
     before_chunk(nchunks, k0, n);
     p.k0 = k0;
-    if (p.N + p.M > 0) { mark(BEAR_CUDA_KERNEL_MIX); launch_mix(p, n, st); }
-    if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, n, st); }
-    if (p.N > 0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, st); }
-    mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, st);
+    if (p.N + p.M > 0) {
+      mark(BEAR_CUDA_KERNEL_MIX_AUX); launch_mix_prep(p, n, st);
+      mark(BEAR_CUDA_KERNEL_MIX); launch_mix(p, n, st);
+      launches += 2;
+      if (p.S > 1) { mark(BEAR_CUDA_KERNEL_MIX_AUX); launch_bus_sum(p, n, st); launches++; }
+    }
+    if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, n, st); launches++; }
+    if (shared_scene) {
+      // every rank's bus rows of this chunk are complete before anyone reads them
+      mark(BEAR_CUDA_KERNEL_EXCHANGE);
+      NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, st));
+    }
+    if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, st); launches++; }
+    if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, st); launches++; }
     p.KS = cmac_splits_for(r, n);
     p.ks_dev = cmac_groups_by_view(p, n);
-    mark(BEAR_CUDA_KERNEL_CMAC); extra_launches += launch_cmac(p, n, st) - 1;
-    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, st);
+    mark(BEAR_CUDA_KERNEL_CMAC); launches += launch_cmac(p, n, st);
+    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, st); launches++;
     p.KS = r->ks_cfg;
     p.ks_dev = 0;
+    if (shared_scene) {
+      // the stereo partial mixes of the ranks are summed (north_star: "only per-block stereo partial
+      // mixes are summed with NCCL"), chunk by chunk so that the sum of chunk c runs under chunk c+1
+      mark(BEAR_CUDA_KERNEL_EXCHANGE);
+      NCK(nccl().GroupStart());
+      for (int e = 0; e < 2; e++) {
+        float *row = p.out + (size_t)e * p.os + (size_t)k0 * p.B;
+        if (r->comm_root >= 0)
+          NCK(nccl().Reduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm_root, r->comm, st));
+        else
+          NCK(nccl().AllReduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm, st));
+      }
+      NCK(nccl().GroupEnd());
+    }
     after_chunk(nchunks, k0, n);
     k0 += n;
   }
@@ -561,11 +708,14 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
   };
   const long long TB = (long long)T * p.B;
   add(p.xin, p.N + p.M + p.H, (long long)p.xs, p.hist, TB);
-  if (p.N + p.M > 0) add(p.cdir, p.S * 2 * p.L, (long long)p.cs, p.B, TB);
-  if (p.N > 0) {
-    add(p.qdif, p.S * p.L, (long long)p.cs, p.B, TB);
-    add(p.w, p.L, (long long)p.ws, p.B + p.hist, TB);
+  {
+    // the last period of the bus rows becomes the prefix of the rows the NEXT call writes
+    float *next = shared_scene ? r->bus[r->parity ^ 1] : bus;
+    const long long from = (long long)(bus - next) + TB;
+    if (p.N + p.M > 0) add(next, 2 * p.L, (long long)p.cs, p.B, from);
+    if (p.N > 0) add(next + (size_t)2 * p.L * p.cs, p.L, (long long)p.cs, p.B, from);
   }
+  if (p.dif) add(p.w, p.L, (long long)p.ws, p.B + p.hist, TB);
   if (p.H > 0) {
     add(p.amb, p.A, (long long)p.ws, p.B + p.hist, TB);
     add(p.g_hoa, 1, 0, p.A * p.H, (long long)T * p.A * p.H);
@@ -590,18 +740,37 @@ void run_pipeline(bear_cuda_renderer *r, int T, const std::vector<int> &chunks, 
   plan.fdl_P = p.P;
   plan.fdl_T = T;
   launch_carry(plan, st);
+  launches++;
   mark(-1);
   if (r->profiling) {
     r->ev_pending.push_back(std::move(chain));
     r->ev_kernel.push_back(std::move(ids));
   }
   CK(cudaGetLastError());
-  r->launches += (uint64_t)(r->kernels_per_call - 1) * nchunks + 1 + extra_launches;
+  r->launches += launches;
+  r->calls++;
+  if (shared_scene) r->parity ^= 1;
 }
 
-void run_pipeline(bear_cuda_renderer *r, int T)
+void run_pipeline(bear_cuda_renderer *r, int T, bool device_tables = false)
 {
-  run_pipeline(r, T, uniform_chunks(T, r->chunk), [](int, int, int) {}, [](int, int, int) {});
+  run_pipeline(r, T, r->chunk, [](int, int, int) {}, [](int, int, int) {}, device_tables);
+}
+
+// Error bits raised by the kernels of the calls queued so far (a table delay out of range, a view
+// index out of range on the device-resident path); synchronises the render stream.
+void fetch_kernel_errors(bear_cuda_renderer *r)
+{
+  CK(cudaMemcpyAsync(r->h_err, r->lay.err_flag, sizeof(int), cudaMemcpyDeviceToHost, r->stream));
+  CK(cudaStreamSynchronize(r->stream));
+  const int bits = r->h_err[0];
+  if (!bits) return;
+  CK(cudaMemsetAsync(r->lay.err_flag, 0, sizeof(int), r->stream));
+  r->h_err[0] = 0;
+  if (bits & kErrViewRange) throw InvalidArgument{"brir_index out of range (device tables); view 0 was rendered instead"};
+  throw InvalidArgument{"a table delay is negative or longer than history_samples - 4 samples (" +
+                        std::to_string(r->lay.hist - 4) + "); it was clamped for this call -- create the renderer "
+                        "with a larger max_delay_samples"};
 }
 
 template <class F>

@@ -39,8 +39,11 @@ typedef struct bear_cuda_config {
   uint32_t sample_rate;                  /* informational; the data file's fs converts delays */
   uint32_t max_batch_blocks;             /* largest T accepted by the *_batch calls (>=1) */
   int32_t device;                        /* CUDA device ordinal */
-  uint32_t max_delay_samples;            /* largest table delay in samples (0 -> 256) */
-  uint32_t object_splits;                /* 0 = choose from N and max_batch_blocks */
+  uint32_t max_delay_samples;            /* largest table delay in samples; 0 = the longest delay the data
+                                          * file can produce (max loudspeaker delay + decorrelation delay, or
+                                          * the HOA delay).  A table delay outside [0, history_samples - 4]
+                                          * makes the call fail with BEAR_CUDA_ERR_INVALID_ARGUMENT. */
+  uint32_t object_splits;                /* 0 = chosen per launch from N and the launch length */
   uint32_t cmac_splits;                  /* 0 = choose from B and max_batch_blocks */
   /* Ramp end-point conventions of the VISR atoms, ramp[n] = (n + offset)/B, offset 0 or 1
    * (the VISR source is not in the reference tree; see DESIGN.md "Oracle pinning"). */
@@ -55,9 +58,9 @@ typedef struct bear_cuda_config {
  * accessors :250-263,:408-412).  Dense, C order, host memory. */
 typedef struct bear_cuda_data {
   uint32_t num_views;                /* V */
-  uint32_t num_virtual_loudspeakers; /* L (<= 32) */
-  uint32_t brir_length;
-  uint32_t decorrelator_length;      /* <= period_size partitions handled: any length */
+  uint32_t num_virtual_loudspeakers; /* L (<= 24) */
+  uint32_t brir_length;              /* any length: cut into ceil(brir_length / period_size) partitions */
+  uint32_t decorrelator_length;      /* <= period_size (one partition), like hoa_ir_length */
   uint32_t num_hoa_decoder_channels; /* A = (order+1)^2 (<= 64) */
   uint32_t hoa_ir_length;
   const float *brirs;                /* [V][L][2][brir_length] */
@@ -209,16 +212,18 @@ int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T);
  * the renderer from a place where nothing may be allocated: the audio callback of a plug-in host or
  * sound-card driver thread, where a device allocation can take driver-wide locks and stall the
  * period deadline, or an embedder whose device memory is handed out once at start-up.  This call
- * performs no cudaMalloc/cudaFree and uses no allocating library routine; the one piece of
- * per-call scratch the pipeline needs (the partial output spectra between the multiply-accumulate
- * and the inverse transform) is taken from an array of BEAR_CUDA_STATIC_SCRATCH_BYTES that is part
- * of the library image on every GPU that loads it, instead of from renderer-owned memory.
+ * performs no cudaMalloc/cudaFree and uses no allocating library routine, on the device or on the
+ * host heap (argument errors are reported from a buffer reserved at creation; only the report of a
+ * CUDA runtime failure may allocate); the one piece of per-call scratch the pipeline needs (the
+ * partial output spectra between the multiply-accumulate and the inverse transform) is taken from
+ * an array of BEAR_CUDA_STATIC_SCRATCH_BYTES that is part of the library image on every GPU that
+ * loads it, instead of from renderer-owned memory.  Per-kernel profiling is off during the call.
  *
  *  - Limit: T * 2 ears * 2 views * cmac_splits * period_size * 8 bytes must fit the array
  *    (bear_cuda_get_info reports cmac_splits); otherwise BEAR_CUDA_ERR_UNSUPPORTED with the numbers
  *    in bear_cuda_last_error and nothing is launched.
- *  - The first call on each device looks up the array's device address (a one-off set-up step with
- *    that device current); make that first call before starting any stream capture.
+ *  - The array's device address is looked up when the renderer is created (with its device
+ *    current), so the render call itself does no set-up.
  *  - The array is shared by every renderer and every call on the device and keeps whatever the last
  *    call wrote.  Nothing needs clearing (all that is read was written in the same call), but two
  *    calls whose kernels overlap on the GPU - different renderers on different streams - would
@@ -227,8 +232,42 @@ int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T);
 int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T);
 
 /* Block until all work queued on the renderer's stream has finished (no counterpart: the
- * reference's process() is synchronous). */
+ * reference's process() is synchronous).  Also reports what the kernels of the asynchronous calls
+ * found wrong with device-resident tables (a delay outside [0, history_samples - 4], a brir_index
+ * outside [0, V)): BEAR_CUDA_ERR_INVALID_ARGUMENT, once; the offending values were clamped / replaced by
+ * view 0 for that call, so no memory outside the renderer's buffers was touched. */
 int bear_cuda_synchronize(bear_cuda_renderer *r);
+
+/* ---- one scene on several GPUs ---------------------------------------------
+ *
+ * No counterpart in the reference (it has no distributed code); the property relied on is that a
+ * render is linear in its inputs, which the reference pins in visr_bear/test/test_changes.py:341-361.
+ * One process per GPU, each with its own renderer for ITS share of the scene's objects /
+ * DirectSpeakers / HOA channels (any split, counts may differ) and the same listener tables.  After
+ * bear_cuda_comm_connect the renderers work as one:
+ *   - every rank mixes its channels onto its own copy of the 2L + L bus rows (per-ear delays, gain
+ *     ramps: the part whose cost grows with the object count);
+ *   - rank g then runs decorrelators, static delays, FFTs and the partitioned BRIR multiply-accumulate
+ *     for loudspeakers [g L / W, (g+1) L / W) only, on the SUM of all ranks' rows, which its kernels
+ *     read from the peers' memory over NVLink while they assemble the FFT windows (cudaIpc mappings,
+ *     ordinary loads; a one-word NCCL all-reduce orders the ranks before the rows are read);
+ *   - the stereo partial mixes are summed with NCCL (ncclReduce to `root`, or ncclAllReduce when root
+ *     is negative) on the renderer's stream, per chunk of periods, so `output` / audio_out of the root
+ *     (of every rank) holds the whole scene's render.  On other ranks the process calls accept
+ *     output == NULL.
+ * Every rank must make the same sequence of process calls (same T, same chunking).  NCCL is bound at
+ * run time (dlopen of libnccl.so.2: the copy already in the process, e.g. PyTorch's, else the
+ * system's); a renderer that is never connected does not need it.
+ *
+ * Protocol: each rank fills a blob (bear_cuda_comm_blob; rank 0's carries the NCCL unique id), the
+ * host gathers the blobs of all ranks by whatever means it has (torch.distributed, MPI, a file) and
+ * hands every rank the concatenation, ordered by rank.  Connect before the first process call. */
+#define BEAR_CUDA_COMM_BLOB_BYTES 256
+int bear_cuda_comm_blob(bear_cuda_renderer *r, uint32_t rank, void *blob);
+int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world, const void *blobs, int32_t root);
+/* Which loudspeakers rank `rank` of `world` convolves (host only, no GPU needed). */
+void bear_cuda_comm_speaker_range(uint32_t rank, uint32_t world, uint32_t num_virtual_loudspeakers,
+                                  uint32_t *begin, uint32_t *end);
 
 /* ---- introspection --------------------------------------------------------------------------- */
 
@@ -244,6 +283,9 @@ typedef struct bear_cuda_info {
   /* the most recent launch whose periods were grouped by BRIR view (>= 8 periods): number of
    * (view, <= 6 periods) work items and of partial spectra per period the device chose; 0 if none yet */
   uint32_t cmac_items_last, cmac_splits_last;
+  /* scene sharing (bear_cuda_comm_connect): number of ranks, this rank, and the virtual loudspeakers
+   * [speakers_begin, speakers_end) whose convolution this rank runs; 1, 0, 0, L when not connected */
+  uint32_t world, rank, speakers_begin, speakers_end;
 } bear_cuda_info;
 
 /* No counterpart in the reference (num_partitions is what rbbl::CoreConvolverUniform derives from
@@ -262,7 +304,9 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
 #define BEAR_CUDA_KERNEL_IFFT_OUT 5
 #define BEAR_CUDA_KERNEL_CARRY 6
 #define BEAR_CUDA_KERNEL_CONTROL 7
-#define BEAR_CUDA_NUM_KERNELS 8
+#define BEAR_CUDA_KERNEL_MIX_AUX 8   /* mix_prep_kernel (+ bus_sum_kernel in short launches) */
+#define BEAR_CUDA_KERNEL_EXCHANGE 9  /* cross-GPU barrier and stereo reduce of a shared scene (NCCL) */
+#define BEAR_CUDA_NUM_KERNELS 10
 
 typedef struct bear_cuda_kernel_profile {
   char name[32];
