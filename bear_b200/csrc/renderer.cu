@@ -904,6 +904,9 @@ struct LoadedData {
   }
 };
 
+// On the ranks of a shared scene that do not receive the mix, the process calls take no output buffer.
+bool output_optional(const bear_cuda_renderer *r) { return r->lay.W > 1 && r->comm_root >= 0 && r->comm_root != r->lay.rank; }
+
 }  // namespace
 
 // ================================================================================================
@@ -1008,20 +1011,22 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
     r->shadow_valid = false;   // the single-period graph path has to see all tables again
     Layout &p = r->lay;
     if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
-    if (!output) throw InvalidArgument{"output must not be NULL"};
+    if (!output && !output_optional(r)) throw InvalidArgument{"output must not be NULL"};
     if (p.N && !objects) throw InvalidArgument{"objects input must not be NULL"};
     if (p.M && !direct_speakers) throw InvalidArgument{"direct_speakers input must not be NULL"};
     if (p.H && !hoa) throw InvalidArgument{"hoa input must not be NULL"};
     // Uploads go to their own stream in chunks of periods, the render stream waits for
     // chunk c before it queues the kernels of chunk c: copies of later chunks overlap the kernels.
     cudaStream_t cs = r->copy_stream;
+    // the staging areas may still be in use by an earlier asynchronous call (bear_cuda_process_device)
+    CK(cudaEventRecord(r->ev_order, r->stream));
+    CK(cudaStreamWaitEvent(cs, r->ev_order, 0));
     upload_tables(r, (int)T, tables, false, cs);
     // (Shorter chunks towards the end do not pay: a chunk of a few periods still takes ~0.1 ms to
     // go through the six kernels, longer than its upload.)
-    const std::vector<int> chunks = uniform_chunks(
-        (int)T, host_chunk_periods(r, (int)T, (size_t)(p.N + p.M + p.H) * p.B * sizeof(float) + table_bytes_per_period(p)));
-    for (int k0 = 0, c = 0; k0 < (int)T; k0 += chunks[c], c++) {
-      const size_t col = (size_t)k0 * p.B, width = (size_t)chunks[c] * p.B * sizeof(float);
+    const int chunk = host_chunk_periods(r, (int)T, (size_t)(p.N + p.M + p.H) * p.B * sizeof(float) + table_bytes_per_period(p));
+    for (int k0 = 0, c = 0; k0 < (int)T; k0 += chunk, c++) {
+      const size_t col = (size_t)k0 * p.B, width = (size_t)std::min(chunk, (int)T - k0) * p.B * sizeof(float);
       auto up_audio = [&](int row0, int rows, const float *host, size_t stride) {
         if (rows)
           CK(cudaMemcpy2DAsync(p.xin + (size_t)row0 * p.xs + p.hist + col, p.xs * sizeof(float), host + col,
@@ -1034,8 +1039,9 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
     }
     // finished chunks are read back on a third stream while later chunks still upload and render
     run_pipeline(
-        r, (int)T, chunks, [&](int c, int, int) { CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0)); },
+        r, (int)T, chunk, [&](int c, int, int) { CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0)); },
         [&](int c, int k0, int n) {
+          if (!output) return;
           CK(cudaEventRecord(r->done_events[c], r->stream));
           CK(cudaStreamWaitEvent(r->d2h_stream, r->done_events[c], 0));
           CK(cudaMemcpy2DAsync(output + (size_t)k0 * p.B, out_stride * sizeof(float), p.out + (size_t)k0 * p.B,
@@ -1043,7 +1049,7 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
                                r->d2h_stream));
         });
     CK(cudaStreamSynchronize(r->d2h_stream));
-    CK(cudaStreamSynchronize(r->stream));
+    fetch_kernel_errors(r);
   });
 }
 
@@ -1057,7 +1063,7 @@ int bear_cuda_process_batch_frames(bear_cuda_renderer *r, uint32_t T, const void
     Layout &p = r->lay;
     const int rows = p.N + p.M + p.H;
     if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
-    if (!output) throw InvalidArgument{"output must not be NULL"};
+    if (!output && !output_optional(r)) throw InvalidArgument{"output must not be NULL"};
     if (format > BEAR_CUDA_FRAMES_S32) throw InvalidArgument{"unknown frame format"};
     if (rows && (!frames || !tracks || frame_channels == 0)) throw InvalidArgument{"frames and tracks must not be NULL"};
     for (int i = 0; i < rows; i++)
@@ -1078,25 +1084,27 @@ int bear_cuda_process_batch_frames(bear_cuda_renderer *r, uint32_t T, const void
       if (!r->d_tracks) CK(cudaMalloc(&r->d_tracks, (size_t)rows * sizeof(int)));
     }
     cudaStream_t cs = r->copy_stream;
+    CK(cudaEventRecord(r->ev_order, r->stream));
+    CK(cudaStreamWaitEvent(cs, r->ev_order, 0));
     if (rows) CK(cudaMemcpyAsync(r->d_tracks, tracks, (size_t)rows * sizeof(int), cudaMemcpyHostToDevice, cs));
     upload_tables(r, (int)T, tables, false, cs);
-    const std::vector<int> chunks =
-        uniform_chunks((int)T, host_chunk_periods(r, (int)T, (size_t)p.B * frame_bytes + table_bytes_per_period(p)));
-    for (int k0 = 0, c = 0; k0 < (int)T; k0 += chunks[c], c++) {
-      const size_t off = (size_t)k0 * p.B * frame_bytes, bytes = (size_t)chunks[c] * p.B * frame_bytes;
+    const int chunk = host_chunk_periods(r, (int)T, (size_t)p.B * frame_bytes + table_bytes_per_period(p));
+    for (int k0 = 0, c = 0; k0 < (int)T; k0 += chunk, c++) {
+      const size_t off = (size_t)k0 * p.B * frame_bytes, bytes = (size_t)std::min(chunk, (int)T - k0) * p.B * frame_bytes;
       if (rows)
         CK(cudaMemcpyAsync(r->d_frames + off, static_cast<const unsigned char *>(frames) + off, bytes,
                            cudaMemcpyHostToDevice, cs));
       CK(cudaEventRecord(r->h2d_events[c], cs));
     }
     run_pipeline(
-        r, (int)T, chunks,
+        r, (int)T, chunk,
         [&](int c, int k0, int n) {
           CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0));
           launch_frames(p, r->d_frames, (int)format, (int)frame_channels, r->d_tracks, rows, k0 * p.B, n * p.B, r->stream);
           if (rows) r->launches++;
         },
         [&](int c, int k0, int n) {
+          if (!output) return;
           CK(cudaEventRecord(r->done_events[c], r->stream));
           CK(cudaStreamWaitEvent(r->d2h_stream, r->done_events[c], 0));
           CK(cudaMemcpy2DAsync(output + (size_t)k0 * p.B, out_stride * sizeof(float), p.out + (size_t)k0 * p.B,
@@ -1104,7 +1112,7 @@ int bear_cuda_process_batch_frames(bear_cuda_renderer *r, uint32_t T, const void
                                r->d2h_stream));
         });
     CK(cudaStreamSynchronize(r->d2h_stream));
-    CK(cudaStreamSynchronize(r->stream));
+    fetch_kernel_errors(r);
   });
 }
 
@@ -1117,7 +1125,7 @@ static bool stream_call_as_graph(bear_cuda_renderer *r, const float *const *obje
 {
   Layout &p = r->lay;
   const size_t B = p.B;
-  if (!r->graph_ok || !tables || r->profiling || !r->h_graph) return false;
+  if (!r->graph_ok || !tables || r->profiling || !r->h_graph || r->lay.W > 1) return false;
   const float *host[8] = {tables->direct_gains, tables->diffuse_gains, tables->direct_delays,
                           tables->direct_speakers_gains, tables->direct_speakers_delays, tables->static_delays,
                           tables->hoa_gains, nullptr};
@@ -1165,6 +1173,7 @@ static bool stream_call_as_graph(bear_cuda_renderer *r, const float *const *obje
         run_pipeline(r, 1);
         CK(cudaMemcpy2DAsync(r->h_out, B * sizeof(float), p.out, p.os * sizeof(float), B * sizeof(float), 2,
                              cudaMemcpyDeviceToHost, r->stream));
+        CK(cudaMemcpyAsync(r->h_err, p.err_flag, sizeof(int), cudaMemcpyDeviceToHost, r->stream));
       } catch (...) {
         ok = false;
       }
@@ -1185,7 +1194,9 @@ static bool stream_call_as_graph(bear_cuda_renderer *r, const float *const *obje
   }
   CK(cudaGraphLaunch(r->graph_exec, r->stream));
   r->launches += r->graph_launch_count;
+  r->calls++;
   CK(cudaStreamSynchronize(r->stream));
+  if (r->h_err[0]) fetch_kernel_errors(r);   // the graph ends with a copy of the kernels' error bits
   std::memcpy(output[0], r->h_out, B * sizeof(float));
   std::memcpy(output[1], r->h_out + B, B * sizeof(float));
   return true;
@@ -1252,7 +1263,7 @@ int bear_cuda_process(bear_cuda_renderer *r, const float *const *objects_input,
     run_pipeline(r, 1);
     CK(cudaMemcpy2DAsync(r->h_out, B * sizeof(float), p.out, p.os * sizeof(float), B * sizeof(float), 2,
                          cudaMemcpyDeviceToHost, r->stream));
-    CK(cudaStreamSynchronize(r->stream));
+    fetch_kernel_errors(r);
     std::memcpy(output[0], r->h_out, B * sizeof(float));
     std::memcpy(output[1], r->h_out + B, B * sizeof(float));
   });
@@ -1324,35 +1335,46 @@ int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T)
   return guarded(r, [&] {
     r->shadow_valid = false;   // the single-period graph path has to see all tables again
     if (T == 0 || (int)T > r->lay.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
-    run_pipeline(r, (int)T);
+    run_pipeline(r, (int)T, true);
   });
 }
 
 int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T)
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  Layout &p = r->lay;
+  // Argument errors are reported without the exception path of the other entry points (an exception
+  // object owns a heap string): the text goes into the buffer reserved when the renderer was created.
+  char msg[384];
+  if (T == 0 || (int)T > p.Tmax) {
+    r->error.assign("T must be in 1..max_batch_blocks");
+    return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  }
+  if (p.W > 1) {
+    r->error.assign("a renderer that shares a scene with other GPUs cannot use the static scratch variant");
+    return BEAR_CUDA_ERR_UNSUPPORTED;
+  }
+  const size_t need = (size_t)T * 2 * 2 * r->ks_cfg * p.B * sizeof(float2);
+  if (need > kStaticScratchBytes) {
+    std::snprintf(msg, sizeof msg,
+                  "static scratch too small: %u periods need %zu bytes of partial spectra (2 ears x 2 views x %d splits x "
+                  "%d bins), the built-in array holds %zu; use fewer periods per call or bear_cuda_process_device",
+                  T, need, r->ks_cfg, p.B, (size_t)kStaticScratchBytes);
+    r->error.assign(msg);
+    return BEAR_CUDA_ERR_UNSUPPORTED;
+  }
   return guarded(r, [&] {
     r->shadow_valid = false;   // the single-period graph path has to see all tables again
-    Layout &p = r->lay;
-    if (T == 0 || (int)T > p.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
-    const size_t need = (size_t)T * 2 * 2 * p.KS * p.B * sizeof(float2);
-    if (need > kStaticScratchBytes)
-      throw Unsupported{"static scratch too small: " + std::to_string(T) + " periods need " + std::to_string(need) +
-                        " bytes of partial spectra (2 ears x 2 views x " + std::to_string(p.KS) + " splits x " +
-                        std::to_string(p.B) + " bins), the built-in array holds " +
-                        std::to_string(kStaticScratchBytes) + "; use fewer periods per call or bear_cuda_process_device"};
-    float2 *scratch = nullptr;
-    CK(static_scratch_pointer(&scratch));  // first call on a device resolves the symbol address
     // Same kernels, same state; only the partial spectra go to the built-in array.  Nothing in it has
     // to start at zero: cmac_kernel writes every partial spectrum that ifft_out_kernel reads in the
     // same call, so whatever an earlier call (of any renderer) left behind is never read.
     float2 *own = p.ypart;
     const bool prof = r->profiling;
-    p.ypart = scratch;
+    p.ypart = r->static_scratch;   // looked up at creation (cudaGetSymbolAddress with the device current)
     r->profiling = false;  // the event pool may grow; this entry point must not create anything
     r->ks_dynamic = false; // the size check above is for the configured number of splits
     try {
-      run_pipeline(r, (int)T);
+      run_pipeline(r, (int)T, true);
     } catch (...) {
       p.ypart = own;
       r->profiling = prof;
@@ -1371,6 +1393,8 @@ int bear_cuda_reset(bear_cuda_renderer *r)
   return guarded(r, [&] {
     CK(cudaStreamSynchronize(r->stream));
     for (auto &a : r->state_allocs) CK(cudaMemsetAsync(a.first, 0, a.second, r->stream));
+    r->parity = 0;
+    r->calls = 0;
     set_initial_state(r);
     CK(cudaStreamSynchronize(r->stream));
   });
@@ -1379,7 +1403,7 @@ int bear_cuda_reset(bear_cuda_renderer *r)
 int bear_cuda_synchronize(bear_cuda_renderer *r)
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
-  return guarded(r, [&] { CK(cudaStreamSynchronize(r->stream)); });
+  return guarded(r, [&] { fetch_kernel_errors(r); });
 }
 
 int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info)
@@ -1401,6 +1425,8 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info)
   info->launches_total = r->launches;
   info->default_direct_delay = r->default_direct_delay;
   info->default_static_delay = r->default_static_delay;
+  info->world = (uint32_t)r->lay.W; info->rank = (uint32_t)r->lay.rank;
+  info->speakers_begin = (uint32_t)r->lay.l0; info->speakers_end = (uint32_t)r->lay.l1;
   return BEAR_CUDA_OK;
 }
 
@@ -1430,13 +1456,87 @@ int bear_cuda_get_profile(bear_cuda_renderer *r, bear_cuda_kernel_profile *out, 
     r->ev_kernel.clear();
     static const char *names[BEAR_CUDA_NUM_KERNELS] = {"mix_kernel", "hoa_mix_kernel", "decorrelate_kernel",
                                                        "bus_fdl_kernel", "cmac_kernel", "ifft_out_kernel",
-                                                       "carry_kernel", "control_kernel"};
+                                                       "carry_kernel", "control_kernel", "mix_aux_kernels",
+                                                       "exchange"};
     for (int k = 0; k < BEAR_CUDA_NUM_KERNELS; k++) {
       std::snprintf(out[k].name, sizeof(out[k].name), "%s", names[k]);
       out[k].total_ms = r->prof_ms[k];
       out[k].launches = r->prof_n[k];
       if (reset) { r->prof_ms[k] = 0; r->prof_n[k] = 0; }
     }
+  });
+}
+
+void bear_cuda_comm_speaker_range(uint32_t rank, uint32_t world, uint32_t L, uint32_t *begin, uint32_t *end)
+{
+  if (world == 0) world = 1;
+  if (begin) *begin = (uint32_t)((uint64_t)rank * L / world);
+  if (end) *end = (uint32_t)((uint64_t)(rank + 1) * L / world);
+}
+
+int bear_cuda_comm_blob(bear_cuda_renderer *r, uint32_t rank, void *blob)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    if (!blob) throw InvalidArgument{"blob must not be NULL"};
+    const Layout &p = r->lay;
+    std::memset(blob, 0, BEAR_CUDA_COMM_BLOB_BYTES);
+    CommBlob b{};
+    b.magic = kCommMagic; b.B = (uint32_t)p.B; b.Tmax = (uint32_t)p.Tmax; b.L = (uint32_t)p.L;
+    b.cs = p.cs;
+    b.N = (uint32_t)p.N; b.M = (uint32_t)p.M; b.H = (uint32_t)p.H; b.rank = rank;
+    CK(cudaIpcGetMemHandle(&b.bus, r->bus[0]));
+    if (rank == 0) NCK(nccl().GetUniqueId(&b.id));
+    std::memcpy(blob, &b, sizeof b);
+  });
+}
+
+int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world, const void *blobs, int32_t root)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    Layout &p = r->lay;
+    if (!blobs) throw InvalidArgument{"blobs must not be NULL"};
+    if (world < 1 || world > (uint32_t)kMaxRanks) throw InvalidArgument{"world must be in 1..8"};
+    if (rank >= world) throw InvalidArgument{"rank must be below world"};
+    if (root >= (int32_t)world) throw InvalidArgument{"root must be below world (or negative: every rank)"};
+    if (r->calls != 0) throw InvalidArgument{"connect before the first process call (or after bear_cuda_reset)"};
+    if (r->comm) throw InvalidArgument{"already connected"};
+    if (world == 1) return;
+    const unsigned char *bytes = static_cast<const unsigned char *>(blobs);
+    CommBlob bl[kMaxRanks];
+    bool any_objects = false;
+    for (uint32_t w = 0; w < world; w++) {
+      std::memcpy(&bl[w], bytes + (size_t)w * BEAR_CUDA_COMM_BLOB_BYTES, sizeof(CommBlob));
+      if (bl[w].magic != kCommMagic || bl[w].rank != w) throw InvalidArgument{"blobs are not ordered by rank"};
+      if (bl[w].B != (uint32_t)p.B || bl[w].Tmax != (uint32_t)p.Tmax || bl[w].L != (uint32_t)p.L || bl[w].cs != p.cs)
+        throw InvalidArgument{"all ranks must use the same period size, max_batch_blocks and data file"};
+      any_objects = any_objects || bl[w].N > 0;
+    }
+    CK(cudaStreamSynchronize(r->stream));
+    // the peers' bus rows, mapped into this process (read with ordinary loads by decorrelate_kernel and
+    // bus_fdl_kernel; nothing here is ever the source of a bulk or multicast copy)
+    for (uint32_t w = 0; w < world; w++) {
+      if (w == rank) {
+        r->peer_bus[w][0] = r->bus[0];
+      } else {
+        void *base = nullptr;
+        CK(cudaIpcOpenMemHandle(&base, bl[w].bus, cudaIpcMemLazyEnablePeerAccess));
+        r->peer_bus[w][0] = static_cast<float *>(base);
+      }
+      r->peer_bus[w][1] = r->peer_bus[w][0] + (size_t)3 * p.L * p.cs;
+    }
+    NCK(nccl().CommInitRank(&r->comm, (int)world, bl[0].id, (int)rank));
+    r->d_barrier = r->dalloc<int>(4);
+    r->comm_root = root;
+    uint32_t l0 = 0, l1 = 0;
+    bear_cuda_comm_speaker_range(rank, world, (uint32_t)p.L, &l0, &l1);
+    p.W = (int)world; p.rank = (int)rank; p.l0 = (int)l0; p.l1 = (int)l1;
+    p.dif = any_objects;
+    r->ks_units = std::max(1, (p.l1 - p.l0) + (p.H > 0 ? 1 : 0));
+    r->ks_cfg = std::max(1, std::min(r->ks_cfg, r->ks_units));
+    p.KS = r->ks_cfg;
+    CK(cudaStreamSynchronize(r->stream));
   });
 }
 
