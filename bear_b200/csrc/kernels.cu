@@ -387,14 +387,18 @@ __device__ __forceinline__ f32x2 delayed_read2(const float *__restrict__ xa, flo
   const f32x2 d = pack2(da, db);
   float ha, hb;
   unpack2(add2(d, splat2(0.5f)), ha, hb);
-  const float fa = floorf(ha), fb = floorf(hb);
+  // floor(h) for 0 <= h < 2^23 without the conversion unit: h + 2^23 rounded towards minus infinity
+  // is exactly 2^23 + floor(h); its low mantissa bits are the integer, subtracting 2^23 back the float
+  const float ua = __fadd_rd(ha, 8388608.0f), ub = __fadd_rd(hb, 8388608.0f);
+  const float fa = ua - 8388608.0f, fb = ub - 8388608.0f;
+  const int ia = __float_as_int(ua) - 0x4B000000, ib = __float_as_int(ub) - 0x4B000000;
   const f32x2 s = add2(splat2(1.5f), sub2(d, pack2(fa, fb)));
   const f32x2 s1 = add2(s, splat2(-1.0f)), s2 = add2(s, splat2(-2.0f)), s3 = add2(s, splat2(-3.0f));
   const f32x2 c0 = mul2(mul2(mul2(s1, s2), s3), splat2(-1.0f / 6.0f));
   const f32x2 c1 = mul2(mul2(mul2(s, s2), s3), splat2(0.5f));
   const f32x2 c2 = mul2(mul2(mul2(s, s1), s3), splat2(-0.5f));
   const f32x2 c3 = mul2(mul2(mul2(s, s1), s2), splat2(1.0f / 6.0f));
-  const float *qa = xa - (int)fa, *qb = xb - (int)fb;
+  const float *qa = xa - ia, *qb = xb - ib;
   f32x2 acc = mul2(c0, pack2(qa[0], qb[0]));
   acc = fma2(c1, pack2(qa[-1], qb[-1]), acc);
   acc = fma2(c2, pack2(qa[-2], qb[-2]), acc);
@@ -510,18 +514,78 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
 #define BEAR_CASES24(M) M(0) M(1) M(2) M(3) M(4) M(5) M(6) M(7) M(8) M(9) M(10) M(11) M(12) M(13) M(14) M(15) M(16) \
   M(17) M(18) M(19) M(20) M(21) M(22) M(23)
 
+// acc[l] += g * x for a loudspeaker index that is the same in all threads of the CTA: an indexed
+// branch (brx.idx.uni -> SASS BRX through a jump table) into 24 one-instruction cases.  A C++ switch
+// compiles to a compare-and-branch tree of ~12 instructions per call here.
 __device__ __forceinline__ void mix_add_direct(f32x2 (&acc)[kMaxSpeakers], unsigned l, f32x2 g2, f32x2 x2)
 {
-#define BEAR_CASE(i) case i: acc[i] = fma2(g2, x2, acc[i]); break;
-  switch (l) { BEAR_CASES24(BEAR_CASE) default: break; }
-#undef BEAR_CASE
+  asm volatile(
+      "{\n\t"
+      "ts: .branchtargets C0, C1, C2, C3, C4, C5, C6, C7, C8, C9, C10, C11, C12, C13, C14, C15, C16, C17, C18, C19, C20, C21, C22, C23;\n\t"
+      "brx.idx.uni %26, ts;\n\t"
+      "C0: fma.rn.f32x2 %0, %24, %25, %0;\n\t bra.uni E;\n\t"
+      "C1: fma.rn.f32x2 %1, %24, %25, %1;\n\t bra.uni E;\n\t"
+      "C2: fma.rn.f32x2 %2, %24, %25, %2;\n\t bra.uni E;\n\t"
+      "C3: fma.rn.f32x2 %3, %24, %25, %3;\n\t bra.uni E;\n\t"
+      "C4: fma.rn.f32x2 %4, %24, %25, %4;\n\t bra.uni E;\n\t"
+      "C5: fma.rn.f32x2 %5, %24, %25, %5;\n\t bra.uni E;\n\t"
+      "C6: fma.rn.f32x2 %6, %24, %25, %6;\n\t bra.uni E;\n\t"
+      "C7: fma.rn.f32x2 %7, %24, %25, %7;\n\t bra.uni E;\n\t"
+      "C8: fma.rn.f32x2 %8, %24, %25, %8;\n\t bra.uni E;\n\t"
+      "C9: fma.rn.f32x2 %9, %24, %25, %9;\n\t bra.uni E;\n\t"
+      "C10: fma.rn.f32x2 %10, %24, %25, %10;\n\t bra.uni E;\n\t"
+      "C11: fma.rn.f32x2 %11, %24, %25, %11;\n\t bra.uni E;\n\t"
+      "C12: fma.rn.f32x2 %12, %24, %25, %12;\n\t bra.uni E;\n\t"
+      "C13: fma.rn.f32x2 %13, %24, %25, %13;\n\t bra.uni E;\n\t"
+      "C14: fma.rn.f32x2 %14, %24, %25, %14;\n\t bra.uni E;\n\t"
+      "C15: fma.rn.f32x2 %15, %24, %25, %15;\n\t bra.uni E;\n\t"
+      "C16: fma.rn.f32x2 %16, %24, %25, %16;\n\t bra.uni E;\n\t"
+      "C17: fma.rn.f32x2 %17, %24, %25, %17;\n\t bra.uni E;\n\t"
+      "C18: fma.rn.f32x2 %18, %24, %25, %18;\n\t bra.uni E;\n\t"
+      "C19: fma.rn.f32x2 %19, %24, %25, %19;\n\t bra.uni E;\n\t"
+      "C20: fma.rn.f32x2 %20, %24, %25, %20;\n\t bra.uni E;\n\t"
+      "C21: fma.rn.f32x2 %21, %24, %25, %21;\n\t bra.uni E;\n\t"
+      "C22: fma.rn.f32x2 %22, %24, %25, %22;\n\t bra.uni E;\n\t"
+      "C23: fma.rn.f32x2 %23, %24, %25, %23;\n\t bra.uni E;\n\t"
+      "E:\n\t}"
+      : "+l"(acc[0]), "+l"(acc[1]), "+l"(acc[2]), "+l"(acc[3]), "+l"(acc[4]), "+l"(acc[5]), "+l"(acc[6]), "+l"(acc[7]), "+l"(acc[8]), "+l"(acc[9]), "+l"(acc[10]), "+l"(acc[11]), "+l"(acc[12]), "+l"(acc[13]), "+l"(acc[14]), "+l"(acc[15]), "+l"(acc[16]), "+l"(acc[17]), "+l"(acc[18]), "+l"(acc[19]), "+l"(acc[20]), "+l"(acc[21]), "+l"(acc[22]), "+l"(acc[23])
+      : "l"(g2), "l"(x2), "r"(l));
 }
 __device__ __forceinline__ void mix_add_diffuse(float (&acc)[kMaxSpeakers], unsigned l, float g, float x)
 {
-#define BEAR_CASE(i) case i: acc[i] = fmaf(g, x, acc[i]); break;
-  switch (l) { BEAR_CASES24(BEAR_CASE) default: break; }
-#undef BEAR_CASE
+  asm volatile(
+      "{\n\t"
+      "ts: .branchtargets C0, C1, C2, C3, C4, C5, C6, C7, C8, C9, C10, C11, C12, C13, C14, C15, C16, C17, C18, C19, C20, C21, C22, C23;\n\t"
+      "brx.idx.uni %26, ts;\n\t"
+      "C0: fma.rn.f32 %0, %24, %25, %0;\n\t bra.uni E;\n\t"
+      "C1: fma.rn.f32 %1, %24, %25, %1;\n\t bra.uni E;\n\t"
+      "C2: fma.rn.f32 %2, %24, %25, %2;\n\t bra.uni E;\n\t"
+      "C3: fma.rn.f32 %3, %24, %25, %3;\n\t bra.uni E;\n\t"
+      "C4: fma.rn.f32 %4, %24, %25, %4;\n\t bra.uni E;\n\t"
+      "C5: fma.rn.f32 %5, %24, %25, %5;\n\t bra.uni E;\n\t"
+      "C6: fma.rn.f32 %6, %24, %25, %6;\n\t bra.uni E;\n\t"
+      "C7: fma.rn.f32 %7, %24, %25, %7;\n\t bra.uni E;\n\t"
+      "C8: fma.rn.f32 %8, %24, %25, %8;\n\t bra.uni E;\n\t"
+      "C9: fma.rn.f32 %9, %24, %25, %9;\n\t bra.uni E;\n\t"
+      "C10: fma.rn.f32 %10, %24, %25, %10;\n\t bra.uni E;\n\t"
+      "C11: fma.rn.f32 %11, %24, %25, %11;\n\t bra.uni E;\n\t"
+      "C12: fma.rn.f32 %12, %24, %25, %12;\n\t bra.uni E;\n\t"
+      "C13: fma.rn.f32 %13, %24, %25, %13;\n\t bra.uni E;\n\t"
+      "C14: fma.rn.f32 %14, %24, %25, %14;\n\t bra.uni E;\n\t"
+      "C15: fma.rn.f32 %15, %24, %25, %15;\n\t bra.uni E;\n\t"
+      "C16: fma.rn.f32 %16, %24, %25, %16;\n\t bra.uni E;\n\t"
+      "C17: fma.rn.f32 %17, %24, %25, %17;\n\t bra.uni E;\n\t"
+      "C18: fma.rn.f32 %18, %24, %25, %18;\n\t bra.uni E;\n\t"
+      "C19: fma.rn.f32 %19, %24, %25, %19;\n\t bra.uni E;\n\t"
+      "C20: fma.rn.f32 %20, %24, %25, %20;\n\t bra.uni E;\n\t"
+      "C21: fma.rn.f32 %21, %24, %25, %21;\n\t bra.uni E;\n\t"
+      "C22: fma.rn.f32 %22, %24, %25, %22;\n\t bra.uni E;\n\t"
+      "C23: fma.rn.f32 %23, %24, %25, %23;\n\t bra.uni E;\n\t"
+      "E:\n\t}"
+      : "+f"(acc[0]), "+f"(acc[1]), "+f"(acc[2]), "+f"(acc[3]), "+f"(acc[4]), "+f"(acc[5]), "+f"(acc[6]), "+f"(acc[7]), "+f"(acc[8]), "+f"(acc[9]), "+f"(acc[10]), "+f"(acc[11]), "+f"(acc[12]), "+f"(acc[13]), "+f"(acc[14]), "+f"(acc[15]), "+f"(acc[16]), "+f"(acc[17]), "+f"(acc[18]), "+f"(acc[19]), "+f"(acc[20]), "+f"(acc[21]), "+f"(acc[22]), "+f"(acc[23])
+      : "f"(g), "f"(x), "r"(l));
 }
+static_assert(kMaxSpeakers == 24, "mix_add_* list 24 cases");
 
 __device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
 {
@@ -612,11 +676,18 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
         const uint4 meta = *reinterpret_cast<const uint4 *>(rec + 4);
         const unsigned nd = meta.x & 0xffu, nq = meta.x >> 8;
         if (nd <= (unsigned)kMixK) {
-          unsigned spk = meta.y;
-#pragma unroll 1
-          for (unsigned i = 0; i < nd; i++, spk >>= 8) {
-            const float2 gd = *reinterpret_cast<const float2 *>(rec + 8 + 2 * i);
-            mix_add_direct(acc, spk & 0xffu, splat2(fmaf(rg, gd.y, gd.x)), x2[u]);
+          const float4 *gd = reinterpret_cast<const float4 *>(rec + 8);
+          if (nd > 0) {
+            const float4 ga = gd[0];
+            mix_add_direct(acc, meta.y & 0xffu, splat2(fmaf(rg, ga.y, ga.x)), x2[u]);
+            if (nd > 1) {
+              mix_add_direct(acc, (meta.y >> 8) & 0xffu, splat2(fmaf(rg, ga.w, ga.z)), x2[u]);
+              if (nd > 2) {
+                const float4 gb = gd[1];
+                mix_add_direct(acc, (meta.y >> 16) & 0xffu, splat2(fmaf(rg, gb.y, gb.x)), x2[u]);
+                if (nd > 3) mix_add_direct(acc, meta.y >> 24, splat2(fmaf(rg, gb.w, gb.z)), x2[u]);
+              }
+            }
           }
         } else {   // dense gains: the table itself, every thread the same address
           const int c = cb + j;
@@ -633,11 +704,16 @@ __global__ void __launch_bounds__(kMixTile, 4) mix_kernel(Layout p, int T)
         if (nq) {
           const float x0 = xrow[j * XW];
           if (nq <= (unsigned)kMixK) {
-            unsigned spk = meta.z;
-#pragma unroll 1
-            for (unsigned i = 0; i < nq; i++, spk >>= 8) {
-              const float2 qd = *reinterpret_cast<const float2 *>(rec + 16 + 2 * i);
-              mix_add_diffuse(accQ, spk & 0xffu, fmaf(rg, qd.y, qd.x), x0);
+            const float4 *qd = reinterpret_cast<const float4 *>(rec + 16);
+            const float4 qa = qd[0];
+            mix_add_diffuse(accQ, meta.z & 0xffu, fmaf(rg, qa.y, qa.x), x0);
+            if (nq > 1) {
+              mix_add_diffuse(accQ, (meta.z >> 8) & 0xffu, fmaf(rg, qa.w, qa.z), x0);
+              if (nq > 2) {
+                const float4 qb = qd[1];
+                mix_add_diffuse(accQ, (meta.z >> 16) & 0xffu, fmaf(rg, qb.y, qb.x), x0);
+                if (nq > 3) mix_add_diffuse(accQ, meta.z >> 24, fmaf(rg, qb.w, qb.z), x0);
+              }
             }
           } else {
             const int c = cb + j;

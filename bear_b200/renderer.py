@@ -71,6 +71,7 @@ class Info(C.Structure):
         ("launches_total", C.c_uint64), ("default_direct_delay", C.c_double),
         ("default_static_delay", C.c_double), ("shared_bytes", C.c_uint64),
         ("cmac_items_last", C.c_uint32), ("cmac_splits_last", C.c_uint32),
+        ("world", C.c_uint32), ("rank", C.c_uint32), ("speakers_begin", C.c_uint32), ("speakers_end", C.c_uint32),
     ]
 
 
@@ -93,9 +94,11 @@ EXPORTS = (
     "bear_cuda_tenf_read_f32", "bear_cuda_set_profiling", "bear_cuda_get_profile",
     "bear_cuda_process_device_static_scratch", "bear_cuda_control_tables", "bear_cuda_reset",
     "bear_cuda_create_shared", "bear_cuda_process_batch_frames",
+    "bear_cuda_comm_blob", "bear_cuda_comm_connect", "bear_cuda_comm_speaker_range",
 )
 STATIC_SCRATCH_BYTES = 4 << 20
-NUM_KERNELS = 8
+NUM_KERNELS = 10
+COMM_BLOB_BYTES = 256
 
 
 class KernelProfile(C.Structure):
@@ -144,6 +147,10 @@ def lib():
         l.bear_cuda_tenf_read_f32.argtypes = [C.c_char_p, C.c_char_p, vp, sz, C.POINTER(sz),
                                               C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
         l.bear_cuda_control_tables.argtypes = [vp, u32, vp, vp, vp, vp]
+        l.bear_cuda_comm_blob.argtypes = [vp, u32, vp]
+        l.bear_cuda_comm_connect.argtypes = [vp, u32, u32, vp, C.c_int32]
+        l.bear_cuda_comm_speaker_range.argtypes = [u32, u32, u32, C.POINTER(u32), C.POINTER(u32)]
+        l.bear_cuda_comm_speaker_range.restype = None
         l.bear_cuda_set_profiling.argtypes = [vp, C.c_int]
         l.bear_cuda_get_profile.argtypes = [vp, C.POINTER(KernelProfile), C.c_int]
         _lib = l
@@ -347,14 +354,18 @@ class Renderer:
             keep.append(x)
             return C.c_void_p(x.ctypes.data), x.strides[0] // 4
 
-        out = np.empty((2, TB), np.float32) if output is None else output
+        if output is False:       # a rank of a shared scene that does not receive the mix
+            out, out_ptr, out_stride = None, None, 0
+        else:
+            out = np.empty((2, TB), np.float32) if output is None else output
+            out_ptr, out_stride = C.c_void_p(out.ctypes.data), out.strides[0] // 4
         o, os_ = arr(objects, self.N)
         d, ds_ = arr(direct_speakers, self.M)
         h, hs_ = arr(hoa, self.H)
         t = self._tables_struct(tables, keep)
         self._check(self._l.bear_cuda_process_batch(self._h, T, o, os_, d, ds_, h, hs_,
                                                     None if tables is None else C.byref(t),
-                                                    C.c_void_p(out.ctypes.data), out.strides[0] // 4))
+                                                    out_ptr, out_stride))
         return out
 
     FRAME_FORMATS = {"f32": 0, "s16": 1, "s24": 2, "s32": 3}
@@ -417,6 +428,23 @@ class Renderer:
         """bear_cuda_process_device without any allocation: partial spectra go to the library's
         built-in device array (see include/bear_cuda.h for the limit and the sharing rules)."""
         self._check(self._l.bear_cuda_process_device_static_scratch(self._h, T))
+
+    # ------------------------------------------------------------------ one scene on several GPUs
+    def comm_blob(self, rank):
+        """bear_cuda_comm_blob: what this rank tells the others (bytes of length COMM_BLOB_BYTES)."""
+        buf = (C.c_ubyte * COMM_BLOB_BYTES)()
+        self._check(self._l.bear_cuda_comm_blob(self._h, rank, buf))
+        return bytes(buf)
+
+    def comm_connect(self, rank, world, blobs, root=0):
+        """bear_cuda_comm_connect: `blobs` = the comm_blob() of every rank, ordered by rank (list of
+        bytes or one bytes object).  root < 0: every rank receives the mix."""
+        data = b"".join(blobs) if not isinstance(blobs, (bytes, bytearray)) else bytes(blobs)
+        if len(data) != world * COMM_BLOB_BYTES:
+            raise ValueError("need one blob of %d bytes per rank" % COMM_BLOB_BYTES)
+        buf = (C.c_ubyte * len(data)).from_buffer_copy(data)
+        self._check(self._l.bear_cuda_comm_connect(self._h, rank, world, buf, root))
+        self.info = self.get_info()
 
     def reset(self):
         """Back to the freshly constructed state (bear_cuda_reset): next file of a batch."""

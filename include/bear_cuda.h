@@ -265,7 +265,8 @@ int bear_cuda_synchronize(bear_cuda_renderer *r);
 #define BEAR_CUDA_COMM_BLOB_BYTES 256
 int bear_cuda_comm_blob(bear_cuda_renderer *r, uint32_t rank, void *blob);
 int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world, const void *blobs, int32_t root);
-/* Which loudspeakers rank `rank` of `world` convolves (host only, no GPU needed). */
+/* Which loudspeakers rank `rank` of `world` convolves (host only, no GPU needed; no counterpart in the
+ * reference). */
 void bear_cuda_comm_speaker_range(uint32_t rank, uint32_t world, uint32_t num_virtual_loudspeakers,
                                   uint32_t *begin, uint32_t *end);
 
