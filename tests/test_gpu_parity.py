@@ -407,6 +407,104 @@ def test_argument_errors(small_data):
         r.process(obj[:, :B], None, None, tb.block(0))
 
 
+def _bad_tables(small_data, T, B, what):
+    ctl = control.HostControl(small_data)
+    tb = ctl.tables(T, obj_az=np.zeros((T, 2)), ds_speakers=[2])
+    if what == "long":
+        tb["direct_delays"][T - 1, 1] = 0.5          # 24000 samples; the reference allows 1 s (per_ear_delay.cpp:25)
+    elif what == "negative":
+        tb["direct_speakers_delays"][0, 0] = -1e-4
+    elif what == "static":
+        tb["static_delays"][1, 5] = 0.25
+    elif what == "nan":
+        tb["direct_delays"][0, 0] = np.nan
+    return tb
+
+
+@pytest.mark.parametrize("what", ["long", "negative", "static", "nan"])
+def test_table_delays_out_of_range_are_reported(small_data, what):
+    """A delay the history buffers cannot hold is an error of the call (it used to be clamped silently);
+    nothing outside the renderer's buffers is touched and the renderer stays usable."""
+    from bear_b200.renderer import Renderer
+    from bear_b200 import device_io
+    B, T = 256, 3
+    tb = _bad_tables(small_data, T, B, what)
+    good = control.HostControl(small_data).tables(T, obj_az=np.zeros((T, 2)), ds_speakers=[2])
+    obj, ds = control.synth_audio(2, T * B, 0), control.synth_audio(1, T * B, 50)
+    with Renderer(small_data, 2, 1, 0, B, max_batch_blocks=T) as r:
+        with pytest.raises(ValueError, match="table delay"):
+            r.process_batch(obj, ds, None, tb)
+        r.reset()
+        r.process_batch(obj, ds, None, good)
+        # one period per call (plain and graph path)
+        r.reset()
+        with pytest.raises(ValueError, match="table delay"):
+            for k in range(T):
+                r.process(obj[:, k * B:(k + 1) * B], ds[:, k * B:(k + 1) * B], None, tb.block(k))
+        # device-resident tables: reported by the next synchronize
+        r.reset()
+        io = device_io.DeviceBuffers(r)
+        io.load_audio(np.concatenate([obj, ds]))
+        io.load_tables(tb)
+        r.process_device(T)
+        with pytest.raises(ValueError, match="table delay"):
+            r.synchronize()
+        r.synchronize()   # reported once
+
+
+def test_view_index_out_of_range_on_the_device_path(small_data):
+    from bear_b200.renderer import Renderer
+    from bear_b200 import device_io
+    B = 256
+    for T in (3, 9):      # plain and view-grouped convolution kernel
+        ctl = control.HostControl(small_data)
+        tb = ctl.tables(T, obj_az=np.zeros((T, 1)))
+        tb["brir_index"][T - 2] = small_data.num_views + 7
+        obj = control.synth_audio(1, T * B, 0)
+        with Renderer(small_data, 1, 0, 0, B, max_batch_blocks=T) as r:
+            io = device_io.DeviceBuffers(r)
+            io.load_audio(obj)
+            io.load_tables(tb)
+            r.process_device(T)
+            with pytest.raises(ValueError, match="brir_index out of range"):
+                r.synchronize()
+            assert np.isfinite(io.read_output(T)).all()
+
+
+def test_dense_and_listed_gain_columns_many_objects(oracle, small_data):
+    """Gain columns of every density in one scene of 70 objects (several staging chunks, two object
+    splits): pair-wise panned (2 non-zeros), 3 and 4 non-zeros (the record lists of mix_prep_kernel),
+    and all 24 non-zero (`extent` objects of the reference benchmark, visr_bear/test/benchmark.cpp:132-139,
+    274-277: the table-driven path), direct and diffuse, changing every period."""
+    B, T, N = 256, 9, 70
+    L = small_data.num_virtual_loudspeakers
+    ctl = control.HostControl(small_data)
+    rng = np.random.default_rng(5)
+    tb = ctl.tables(T, obj_az=rng.uniform(-180, 180, size=(T, N)), obj_diffuse=np.where(np.arange(N) % 3 == 0, .4, 0.),
+                    obj_gain=0.3, ds_speakers=[2, 5], yaw_deg=30.0 * np.arange(T))
+    for i in range(N):
+        kind = i % 5
+        if kind in (1, 2, 3):
+            nnz = {1: 3, 2: 4, 3: L}[kind]
+            for key in ("direct_gains", "diffuse_gains"):
+                g = np.zeros((T, L), np.float32)
+                for k in range(T):
+                    idx = rng.choice(L, size=nnz, replace=False)
+                    g[k, idx] = rng.uniform(-0.3, 0.3, size=nnz)
+                if key == "diffuse_gains" and i % 2:
+                    g[:] = 0
+                tb[key][:, :, i] = g
+    dsg = tb["direct_speakers_gains"]
+    dsg[:, :, 1] = rng.uniform(0, 0.2, size=(T, L))      # a dense DirectSpeakers column as well
+    obj, ds = control.synth_audio(N, T * B, 0), control.synth_audio(2, T * B, 500)
+    ref = ref_render(oracle, small_data, N, 2, 0, B, tb, obj, ds, None)
+    for kw in ({}, {"object_splits": 3}, {"chunk_blocks": 4}):
+        out = gpu_render(small_data, N, 2, 0, B, tb, obj, ds, None, "batch", **kw)
+        check(out, ref, "dense %s" % kw)
+    out = gpu_render(small_data, N, 2, 0, B, tb, obj, ds, None, "stream")
+    check(out, ref, "dense stream")
+
+
 def test_zero_channel_configs(small_data):
     from bear_b200.renderer import Renderer
     B = 128

@@ -10,6 +10,8 @@ shared array and must not be affected by them), and checks the size limit.
 
 Collected last on purpose: a run that stops at the first failure has then run everything else.
 """
+import ctypes
+
 import numpy as np
 import pytest
 
@@ -59,6 +61,57 @@ def test_static_scratch_variant_matches_process_device_twice_in_a_row():
         plain.process_device(T)
         noalloc.process_device(T)
         np.testing.assert_allclose(io_b.read_output(T), io_a.read_output(T), atol=1e-5, rtol=0)
+
+
+class _Mallinfo2(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_size_t) for n in
+                ("arena", "ordblks", "smblks", "hblks", "hblkhd", "usmblks", "fsmblks", "uordblks", "fordblks", "keepcost")]
+
+
+def _host_heap_in_use():
+    libc = ctypes.CDLL(None)
+    libc.mallinfo2.restype = _Mallinfo2
+    m = libc.mallinfo2()
+    return m.uordblks + m.hblkhd
+
+
+@pytest.mark.parametrize("chunk_blocks", [0, 5])
+def test_static_scratch_variant_long_calls_match_the_oracle_and_allocate_nothing(oracle, chunk_blocks):
+    """Calls of 12 periods take the convolution kernel that groups the periods by view (its work-item
+    tables index into the built-in array with the number of splits the device picks); a chunked call
+    reuses the array chunk after chunk.  Checked against the CPU oracle, not only against the other entry
+    point, and the free device memory and the host heap in use must not move across the calls."""
+    import torch
+    from bear_b200 import device_io
+    from bear_b200.renderer import Renderer, STATIC_SCRATCH_BYTES
+    T, B = 12, 512
+    data, N, M, H, tb, audio = _scene(T, B, seed=13)
+    ref_r = oracle.RefRenderer(data, N, M, H, B)
+    with Renderer(data, N, M, H, B, max_batch_blocks=T, cmac_splits=4, chunk_blocks=chunk_blocks) as r:
+        assert T * 2 * 2 * r.info.cmac_splits * B * 8 <= STATIC_SCRATCH_BYTES
+        io = device_io.DeviceBuffers(r)
+        fn = r._l.bear_cuda_process_device_static_scratch
+        for call in range(3):
+            chunk = audio[:, (call % 2) * T * B:((call % 2) + 1) * T * B]
+            io.load_audio(chunk)
+            io.load_tables(tb)
+            r.synchronize()
+            torch.cuda.synchronize()
+            free0, heap0 = torch.cuda.mem_get_info()[0], _host_heap_in_use()
+            rc = fn(r._h, ctypes.c_uint32(T))          # the bare C call: nothing of the Python wrapper in between
+            heap1, free1 = _host_heap_in_use(), torch.cuda.mem_get_info()[0]
+            assert rc == 0
+            if call > 0:                               # (the very first launch of a kernel loads its module)
+                assert free1 == free0, "device memory was allocated or freed by the call"
+                assert heap1 == heap0, "the host heap grew or shrank across the call"
+            r.synchronize()
+            got = io.read_output(T)
+            want = ref_r.render(chunk[:N], chunk[N:N + M], chunk[N + M:], tb.blocks())
+            assert np.abs(want).max() > 0.05
+            assert np.abs(got - want).max() <= 1e-5
+        info = r.get_info()
+        assert info.cmac_items_last > 0 and info.cmac_splits_last <= r.info.cmac_splits   # the grouped kernel ran
+    ref_r.close()
 
 
 def test_static_scratch_variant_rejects_oversize_calls():
