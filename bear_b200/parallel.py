@@ -2,9 +2,11 @@
 
 The render path is linear in its inputs (visr_bear/test/test_changes.py:341-361 pins this for the
 reference at 1e-5), so a scene shards by OBJECT GROUP: rank g runs the full pipeline on its objects
-with the same listener tables, and the only exchange is the sum of the per-call stereo partial mixes
-[2, T*B] (NCCL all-reduce over NVLink on GPUs; gloo in the CPU tests).  DirectSpeakers and HOA
-channels, which are few, stay on rank 0.  Batches of independent files shard BY FILE with no exchange.
+with the same listener tables.  On GPUs the exchange lives in the library (bear_cuda_comm_connect,
+include/bear_cuda.h): each rank mixes its objects onto the 48 + 24 bus rows, then convolves 24 / W of
+the loudspeakers on the sum of all ranks' rows, read from the peers over NVLink, and the stereo
+partial mixes [2, T*B] are summed with NCCL.  The CPU tests (gloo) sum the partial mixes of oracle
+renderers here.  DirectSpeakers and HOA channels, which are few, stay on rank 0.  Batches of independent files shard BY FILE with no exchange.
 The reference has no distributed code at all; this module is new design.
 """
 import numpy as np
@@ -60,23 +62,44 @@ def reduce_partial_mix(partial, group=None):
     return partial
 
 
+def connect_renderers(renderer, rank, world, root=0, group=None):
+    """Make the ranks' CUDA renderers one (bear_cuda_comm_connect): the comm blobs travel through
+    torch.distributed (any backend -- they are 256 bytes of host data); from then on the exchange is
+    the library's own: bus rows read from the peers' memory over NVLink, stereo partial mixes summed
+    with NCCL on the renderers' streams.  root < 0: every rank receives the mix."""
+    import torch.distributed as dist
+    blobs = [None] * world
+    dist.all_gather_object(blobs, renderer.comm_blob(rank), group=group)
+    renderer.comm_connect(rank, world, blobs, root)
+
+
 class ShardedScene:
     """Render one scene across the ranks of a process group.
 
     `make_renderer(n_obj, n_ds, n_hoa)` builds the local renderer (bear_b200.renderer.Renderer on a
     GPU); it must offer `render(obj, ds, hoa, tables)` -> [2, T*B]."""
 
-    def __init__(self, make_renderer, N, M, H, rank, world, group=None):
-        self.rank, self.world, self.group = rank, world, group
+    def __init__(self, make_renderer, N, M, H, rank, world, group=None, root=-1):
+        self.rank, self.world, self.group, self.root = rank, world, group, root
         self.sl = object_group(rank, world, N)
         self.counts = shard_counts(rank, world, N, M, H)
         self.renderer = make_renderer(*self.counts)
+        # a CUDA renderer exchanges inside the library; anything else (the CPU oracle in the gloo
+        # tests) renders its partial mix and the sum is taken here
+        self.connected = world > 1 and hasattr(self.renderer, "comm_connect")
+        if self.connected:
+            connect_renderers(self.renderer, rank, world, root, group)
 
     def render(self, obj, ds, hoa, tables):
+        """The whole scene's render on the root (every rank for root < 0), None elsewhere."""
         tb, sl = shard_tables(tables, self.rank, self.world)
         n, m, h = self.counts
-        partial = self.renderer.render(obj[sl] if n else None, ds if m else None, hoa if h else None, tb)
-        partial = np.ascontiguousarray(partial, dtype=np.float32)
+        args = (obj[sl] if n else None, ds if m else None, hoa if h else None, tb)
+        if self.connected:
+            receives = self.root < 0 or self.root == self.rank
+            out = self.renderer.render(*args, output=None if receives else False)
+            return out if receives else None
+        partial = np.ascontiguousarray(self.renderer.render(*args), dtype=np.float32)
         return reduce_partial_mix(partial, self.group)
 
 

@@ -394,16 +394,19 @@ class Renderer:
             tr.ctypes.data_as(_i32p), C.byref(t), C.c_void_p(out.ctypes.data), out.strides[0] // 4))
         return out
 
-    def render(self, objects, direct_speakers, hoa, tables, batch=None):
-        """Render all blocks of `tables`, `batch` blocks per call (default: max_batch_blocks)."""
+    def render(self, objects, direct_speakers, hoa, tables, batch=None, output=None):
+        """Render all blocks of `tables`, `batch` blocks per call (default: max_batch_blocks).
+        output=False: this rank of a shared scene does not receive the mix (returns None)."""
         T = tables.num_blocks
         batch = batch or self.max_batch_blocks
-        out = np.empty((2, T * self.B), np.float32)
+        out = None if output is False else np.empty((2, T * self.B), np.float32)
         sl = lambda x, a, b: None if x is None or x.shape[0] == 0 else x[:, a * self.B:b * self.B]
         for k0 in range(0, T, batch):
             k1 = min(T, k0 + batch)
-            out[:, k0 * self.B:k1 * self.B] = self.process_batch(
-                sl(objects, k0, k1), sl(direct_speakers, k0, k1), sl(hoa, k0, k1), tables.slice(k0, k1))
+            res = self.process_batch(sl(objects, k0, k1), sl(direct_speakers, k0, k1), sl(hoa, k0, k1),
+                                     tables.slice(k0, k1), output=False if out is None else None)
+            if out is not None:
+                out[:, k0 * self.B:k1 * self.B] = res
         return out
 
     # ------------------------------------------------------------------ device-resident path

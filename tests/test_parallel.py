@@ -23,6 +23,24 @@ def test_object_groups_partition():
     assert sorted(sum((parallel.file_shard(r, 4, 10) for r in range(4)), [])) == list(range(10))
 
 
+def test_loudspeaker_ranges_of_a_shared_scene_partition():
+    """bear_cuda_comm_speaker_range (host only): the ranks' convolution shares tile [0, L)."""
+    import ctypes as C
+    from bear_b200 import renderer
+    lib = renderer.lib()
+    for L in (1, 3, 24):
+        for world in (1, 2, 4, 5, 8):
+            r = []
+            for rank in range(world):
+                b, e = C.c_uint32(), C.c_uint32()
+                lib.bear_cuda_comm_speaker_range(rank, world, L, C.byref(b), C.byref(e))
+                r.append((b.value, e.value))
+            assert r[0][0] == 0 and r[-1][1] == L
+            assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
+            sizes = [e - b for b, e in r]
+            assert max(sizes) - min(sizes) <= 1
+
+
 class _OracleRenderer:
     def __init__(self, data, n, m, h, B):
         from oracle import bear_ref
