@@ -160,6 +160,7 @@ struct bear_cuda_renderer {
   int comm_root = -1;                      // rank that receives the mix, -1 = every rank
   float *peer_bus[kMaxRanks][2] = {};      // every rank's bus rows (cudaIpc mappings), [rank] = own
   int *d_barrier = nullptr;                // payload of the cross-rank barrier
+  size_t comm_bytes_per_period = 0;        // largest upload per period among the ranks (same chunking everywhere)
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -606,6 +607,8 @@ int object_splits_for(const bear_cuda_renderer *r, int n)
 static int host_chunk_periods(const bear_cuda_renderer *r, int T, size_t bytes_per_period)
 {
   if (r->h2d_chunk) return r->h2d_chunk;
+  // ranks that share a scene must cut a call into the same chunks (one barrier per chunk)
+  if (r->lay.W > 1) bytes_per_period = r->comm_bytes_per_period;
   const size_t want = (11u << 20) / std::max<size_t>(bytes_per_period, 1) + 1;
   return (int)std::min<size_t>((size_t)T, std::max<size_t>(16, want));
 }
@@ -1512,6 +1515,10 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
       if (bl[w].B != (uint32_t)p.B || bl[w].Tmax != (uint32_t)p.Tmax || bl[w].L != (uint32_t)p.L || bl[w].cs != p.cs)
         throw InvalidArgument{"all ranks must use the same period size, max_batch_blocks and data file"};
       any_objects = any_objects || bl[w].N > 0;
+      const size_t tbl = sizeof(float) * ((size_t)2 * p.L * bl[w].N + 2 * bl[w].N + (size_t)p.L * bl[w].M + 2 * bl[w].M +
+                                          2 * p.L + (size_t)p.A * bl[w].H + 1);
+      r->comm_bytes_per_period = std::max(r->comm_bytes_per_period,
+                                          (size_t)(bl[w].N + bl[w].M + bl[w].H) * p.B * sizeof(float) + tbl);
     }
     CK(cudaStreamSynchronize(r->stream));
     // the peers' bus rows, mapped into this process (read with ordinary loads by decorrelate_kernel and
