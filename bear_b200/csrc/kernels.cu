@@ -767,6 +767,34 @@ __global__ void __launch_bounds__(256) bus_sum_kernel(Layout p, int T)
   *reinterpret_cast<float4 *>(dst) = v;
 }
 
+// bus_gather_kernel (one scene on W GPUs): the bus rows of this rank's loudspeakers [l0, l1), summed
+// over all ranks' object groups in rank order, for the periods of this launch.  The peers' rows are
+// read from their memory over NVLink with ordinary 16-byte loads (cudaIpc mappings), each sample once;
+// the sum lands in this GPU's memory, which is what decorrelate_kernel and bus_fdl_kernel then read.
+// grid: (ceil(periods * B / 1024), 3 (l1 - l0)); block 256; four samples per thread.
+__global__ void __launch_bounds__(256) bus_gather_kernel(Layout p, int T)
+{
+  const int nl = p.l1 - p.l0, r = blockIdx.y;
+  const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
+  if (i >= (size_t)T * p.B) return;
+  const bool dir = r < 2 * nl;
+  const size_t off = (size_t)(dir ? 2 * p.l0 + r : p.l0 + (r - 2 * nl)) * p.cs + (size_t)(p.k0 + 1) * p.B + i;
+  float4 v[kMaxRanks];
+#pragma unroll
+  for (int w = 0; w < kMaxRanks; w++)
+    if (w < p.W) v[w] = *reinterpret_cast<const float4 *>((dir ? p.peer_cdir[w] : p.peer_qdif[w]) + off);
+  float4 a = v[0];
+#pragma unroll
+  for (int w = 1; w < kMaxRanks; w++)
+    if (w < p.W) { a.x += v[w].x; a.y += v[w].y; a.z += v[w].z; a.w += v[w].w; }
+  *reinterpret_cast<float4 *>(const_cast<float *>(dir ? p.cin : p.qin) + off) = a;
+}
+void launch_bus_gather(const Layout &p, int T, cudaStream_t st)
+{
+  if (p.l1 <= p.l0) return;
+  bus_gather_kernel<<<dim3((T * p.B + 1023) / 1024, 3 * (p.l1 - p.l0)), 256, 0, st>>>(p, T);
+}
+
 size_t mix_smem_bytes(int hist);
 void launch_mix_prep(const Layout &p, int T, cudaStream_t st)
 {
@@ -874,16 +902,9 @@ __global__ void decorrelate_kernel(Layout p, int T)
 #pragma unroll
   for (int r = 0; r < 8; r++) v0[r] = make_float2(0.f, 0.f);
   if (tid < Q) {
-    // the diffuse bus is the sum of every rank's object group (one rank: its own row); peer rows are
-    // read straight from the peers' memory over NVLink with ordinary loads
-    for (int w = 0; w < p.W; w++) {
-      const float2 *src = reinterpret_cast<const float2 *>(p.peer_qdif[w] + (size_t)l * p.cs + (size_t)k * p.B) + tid;
-      float2 v[8];
+    const float2 *src = reinterpret_cast<const float2 *>(p.qin + (size_t)l * p.cs + (size_t)k * p.B) + tid;
 #pragma unroll
-      for (int r = 0; r < 8; r++) v[r] = src[r * Q];
-#pragma unroll
-      for (int r = 0; r < 8; r++) { v0[r].x += v[r].x; v0[r].y += v[r].y; }
-    }
+    for (int r = 0; r < 8; r++) v0[r] = src[r * Q];
   }
   fft_first_pass_reg<false, LOGB>(v0, b, tid);
   float2 *z = fft_shared_c<false, LOGB, NTHR, 1>(b, a, p.tw, tid);
@@ -984,7 +1005,7 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
     }
     if (cstaged)
       for (int r = 0; r < 2; r++) {
-        const float *src = p.cdir + (size_t)(2 * spk + r) * p.cs + (size_t)k * p.B;
+        const float *src = p.cin + (size_t)(2 * spk + r) * p.cs + (size_t)k * p.B;
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"((unsigned)__cvta_generic_to_shared(cwin + r * 2 * M)), "l"(src), "r"(win_bytes), "r"(sbar_addr) : "memory");
       }
@@ -1015,11 +1036,8 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
           float2 v = make_float2(0.f, 0.f);
           if (cstaged) {
             v = cw[n];
-          } else {   // every rank's object group; peer rows are read over NVLink with ordinary loads
-            for (int w = 0; w < p.W; w++) {
-              const float2 c = reinterpret_cast<const float2 *>(p.peer_cdir[w] + (size_t)ch * p.cs + (size_t)k * p.B)[n];
-              v.x += c.x; v.y += c.y;
-            }
+          } else {
+            v = reinterpret_cast<const float2 *>(p.cin + (size_t)ch * p.cs + (size_t)k * p.B)[n];
           }
           if (dif) {
             const int t = 2 * n;            // window sample, both of the pair lie in the same block
@@ -1064,16 +1082,16 @@ __global__ void bus_fdl_kernel(Layout p, int T, int nunits, int stage_direct)
 
 // shared memory of bus_fdl_kernel; the direct-bus windows are staged only when there is a single
 // partial (S == 1) and everything still fits (it does up to B = 2048)
-// (bulk copies only ever read this GPU's own rows: with peers, W > 1, the windows are summed by loads)
-static bool bus_fdl_stage_direct(int B, int hist, int W)
+// (the bulk copies read cin, which is always this GPU's own memory: with peers it is the gathered sum)
+static bool bus_fdl_stage_direct(int B, int hist)
 {
   const size_t base = (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float);
-  return W == 1 && base + (size_t)2 * 2 * B * sizeof(float) <= 200 * 1024;
+  return base + (size_t)2 * 2 * B * sizeof(float) <= 200 * 1024;
 }
-static size_t bus_fdl_smem_bytes(int B, int hist, int W)
+static size_t bus_fdl_smem_bytes(int B, int hist)
 {
   return (size_t)2 * fft_smem_floats2(B) * sizeof(float2) + (size_t)2 * (hist + 2 * B) * sizeof(float) +
-         (bus_fdl_stage_direct(B, hist, W) ? (size_t)2 * 2 * B * sizeof(float) : 0);
+         (bus_fdl_stage_direct(B, hist) ? (size_t)2 * 2 * B * sizeof(float) : 0);
 }
 
 void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
@@ -1081,8 +1099,8 @@ void launch_bus_fdl(const Layout &p, int T, cudaStream_t st)
   const int threads = 2 * (p.B / 8 < 32 ? 32 : p.B / 8);
   const int nunits = (p.l1 - p.l0) + (p.H > 0 ? (p.A + 1) / 2 : 0);
   if (nunits == 0) return;
-  const size_t smem = bus_fdl_smem_bytes(p.B, p.hist, p.W);
-  const int stage = bus_fdl_stage_direct(p.B, p.hist, p.W) ? 1 : 0;
+  const size_t smem = bus_fdl_smem_bytes(p.B, p.hist);
+  const int stage = bus_fdl_stage_direct(p.B, p.hist) ? 1 : 0;
   dispatch_logb(p.logB, [&](auto lb) {
     bus_fdl_kernel<decltype(lb)::value><<<T * nunits, threads, smem, st>>>(p, T, nunits, stage);
   });
@@ -1857,7 +1875,7 @@ cudaError_t configure_mix(int hist, int B)
   if (e != cudaSuccess) return e;
   dispatch_logb(ilog2(B), [&](auto lb) {
     e = cudaFuncSetAttribute(bus_fdl_kernel<decltype(lb)::value>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)bus_fdl_smem_bytes(B, hist, 1));
+                             (int)bus_fdl_smem_bytes(B, hist));
   });
   return e;
 }

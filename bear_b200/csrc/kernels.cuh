@@ -73,9 +73,11 @@ struct Layout {
   int2 *grp_items;           // [Tmax + 1] (first, count) into grp_sorted
   int *grp_count;            // [2] number of items, cMAC splits in use (<= KS)
   // one scene shared by W GPUs (bear_cuda_comm_connect; W = 1: this renderer alone): every rank mixes its
-  // own channels onto its own bus rows, and convolves loudspeakers [l0, l1) of the SUM of all ranks' rows
+  // own channels onto its own bus rows (cdir, qdif), and convolves loudspeakers [l0, l1) of the SUM of all
+  // ranks' rows, which bus_gather_kernel collects into cin / qin (W = 1: cin = cdir, qin = qdif)
   int W, rank, l0, l1;
   int dif;                   // some rank has objects: the diffuse path runs
+  const float *cin, *qin;    // what decorrelate_kernel / bus_fdl_kernel read, same layout as cdir / qdif
   const float *peer_cdir[kMaxRanks], *peer_qdif[kMaxRanks];   // every rank's bus rows (entry `rank` = own)
   float *mix_recs;           // [Tmax][N+M][kMixRecWords] records of mix_prep_kernel
   int *err_flag;             // error bits raised by kernels
@@ -106,6 +108,7 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 void launch_mix_prep(const Layout &p, int T, cudaStream_t st);
 void launch_mix(const Layout &p, int T, cudaStream_t st);
 void launch_bus_sum(const Layout &p, int T, cudaStream_t st);
+void launch_bus_gather(const Layout &p, int T, cudaStream_t st);
 void launch_validate_views(const Layout &p, int T, cudaStream_t st);
 void launch_hoa_mix(const Layout &p, int T, cudaStream_t st);
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st);

@@ -159,6 +159,7 @@ struct bear_cuda_renderer {
   NcclComm comm = nullptr;
   int comm_root = -1;                      // rank that receives the mix, -1 = every rank
   float *peer_bus[kMaxRanks][2] = {};      // every rank's bus rows (cudaIpc mappings), [rank] = own
+  float *bus_sum = nullptr;                // [3L][cs] rows of this rank's loudspeakers summed over the ranks
   int *d_barrier = nullptr;                // payload of the cross-rank barrier
   size_t comm_bytes_per_period = 0;        // largest upload per period among the ranks (same chunking everywhere)
   int chunk = 0;                           // periods per launch group (0 = whole call)
@@ -481,6 +482,7 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   p.cdir = r->bus[0];
   p.qdif = r->bus[0] + (size_t)2 * p.L * p.cs;
   p.peer_cdir[0] = p.cdir; p.peer_qdif[0] = p.qdif;
+  p.cin = p.cdir; p.qin = p.qdif;
   {  // partial sums of the object splits of one launch; sized for the worst launch
     size_t cap = 0;
     for (int n = 1; n <= p.Tmax; n++) cap = std::max(cap, (size_t)(object_splits_for(r.get(), n) - 1) * n);
@@ -652,6 +654,9 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
     p.peer_cdir[w] = pb;
     p.peer_qdif[w] = pb + (size_t)2 * p.L * p.cs;
   }
+  const float *in = shared_scene ? r->bus_sum : bus;
+  p.cin = in;
+  p.qin = in + (size_t)2 * p.L * p.cs;
   p.S = object_splits_for(r, chunk);     // one value per call: chunk c+1 reads the last period of chunk c
   uint64_t launches = 0;
   if (device_tables) { launch_validate_views(p, T, st); launches++; }
@@ -671,6 +676,8 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       // every rank's bus rows of this chunk are complete before anyone reads them
       mark(BEAR_CUDA_KERNEL_EXCHANGE);
       NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, st));
+      launch_bus_gather(p, n, st);
+      if (p.l1 > p.l0) launches++;
     }
     if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, st); launches++; }
     if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, st); launches++; }
@@ -711,12 +718,14 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   };
   const long long TB = (long long)T * p.B;
   add(p.xin, p.N + p.M + p.H, (long long)p.xs, p.hist, TB);
-  {
-    // the last period of the bus rows becomes the prefix of the rows the NEXT call writes
-    float *next = shared_scene ? r->bus[r->parity ^ 1] : bus;
-    const long long from = (long long)(bus - next) + TB;
-    if (p.N + p.M > 0) add(next, 2 * p.L, (long long)p.cs, p.B, from);
-    if (p.N > 0) add(next + (size_t)2 * p.L * p.cs, p.L, (long long)p.cs, p.B, from);
+  if (shared_scene) {
+    // the last period of the gathered rows is the overlap-save prefix of the next call (the rows the
+    // peers read have no history: every call's columns are gathered once)
+    add(r->bus_sum + (size_t)2 * p.l0 * p.cs, 2 * (p.l1 - p.l0), (long long)p.cs, p.B, TB);
+    if (p.dif) add(r->bus_sum + (size_t)(2 * p.L + p.l0) * p.cs, p.l1 - p.l0, (long long)p.cs, p.B, TB);
+  } else {
+    if (p.N + p.M > 0) add(bus, 2 * p.L, (long long)p.cs, p.B, TB);
+    if (p.N > 0) add(bus + (size_t)2 * p.L * p.cs, p.L, (long long)p.cs, p.B, TB);
   }
   if (p.dif) add(p.w, p.L, (long long)p.ws, p.B + p.hist, TB);
   if (p.H > 0) {
@@ -1535,6 +1544,7 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
     }
     NCK(nccl().CommInitRank(&r->comm, (int)world, bl[0].id, (int)rank));
     r->d_barrier = r->dalloc<int>(4);
+    r->bus_sum = r->dalloc<float>((size_t)3 * p.L * p.cs);
     r->comm_root = root;
     uint32_t l0 = 0, l1 = 0;
     bear_cuda_comm_speaker_range(rank, world, (uint32_t)p.L, &l0, &l1);
