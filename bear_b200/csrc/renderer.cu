@@ -483,11 +483,11 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   p.qdif = r->bus[0] + (size_t)2 * p.L * p.cs;
   p.peer_cdir[0] = p.cdir; p.peer_qdif[0] = p.qdif;
   p.cin = p.cdir; p.qin = p.qdif;
-  {  // partial sums of the object splits of one launch; sized for the worst launch
-    size_t cap = 0;
+  {  // partial sums of the object splits of one launch, [S - 1][3L][n B]; sized for the worst launch
+    size_t cap = 1;
     for (int n = 1; n <= p.Tmax; n++) cap = std::max(cap, (size_t)(object_splits_for(r.get(), n) - 1) * n);
-    p.bps = round_up(std::max<size_t>(cap, 1) * p.B, 4);
-    p.bus_part = r->dalloc<float>((size_t)3 * p.L * p.bps, false);
+    p.bps = 0;   // row stride, set per call
+    p.bus_part = r->dalloc<float>((size_t)3 * p.L * cap * p.B, false);
   }
   p.mix_recs = r->dalloc<float>((size_t)p.Tmax * std::max(1, C) * kMixRecWords, false);
   p.err_flag = r->dalloc<int>(4);
@@ -657,7 +657,8 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   const float *in = shared_scene ? r->bus_sum : bus;
   p.cin = in;
   p.qin = in + (size_t)2 * p.L * p.cs;
-  p.S = object_splits_for(r, chunk);     // one value per call: chunk c+1 reads the last period of chunk c
+  p.S = object_splits_for(r, chunk);     // one value per call
+  p.bps = (size_t)chunk * p.B;
   uint64_t launches = 0;
   if (device_tables) { launch_validate_views(p, T, st); launches++; }
   int nchunks = 0;
