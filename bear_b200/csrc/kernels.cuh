@@ -7,9 +7,11 @@ namespace bearcuda {
 
 constexpr int kMaxSpeakers = 24;  // accumulator tile of the mix kernel (L <= 24)
 constexpr int kMixTile = 128;     // samples per CTA in the mix kernels
-constexpr int kMixChunk = 16;     // channels staged in shared memory per pass (two passes in flight)
-constexpr int kMixRecWords = 24;  // words of one (period, channel) record of mix_prep_kernel
-constexpr int kMixK = 4;          // non-zero gains a record lists; channels with more take the dense path
+constexpr int kMixChunk = 8;      // channels staged in shared memory per pass (two passes in flight)
+constexpr int kMixSlots = 8;      // non-zero loudspeakers a record lists; channels with more take the dense path
+constexpr int kMixRecWords = 8 + 4 * kMixSlots;   // words of one (period, channel) record of mix_prep_kernel
+constexpr int kMaxObjectSplits = 32;              // object splits of a launch (mix_counts row length)
+constexpr int kMaxSplitChannels = 4096;           // channels one object split can sort in shared memory
 constexpr int kMaxRanks = 8;      // GPUs that can share one scene (bear_cuda_comm_connect)
 // bits of Layout::err_flag (checked by the host after a call has finished)
 constexpr int kErrDelayRange = 1; // a table delay is negative or beyond history_samples - 4
@@ -80,6 +82,9 @@ struct Layout {
   const float *cin, *qin;    // what decorrelate_kernel / bus_fdl_kernel read, same layout as cdir / qdif
   const float *peer_cdir[kMaxRanks], *peer_qdif[kMaxRanks];   // every rank's bus rows (entry `rank` = own)
   float *mix_recs;           // [Tmax][N+M][kMixRecWords] records of mix_prep_kernel
+  unsigned *mix_keys;        // [Tmax][N+M] sort keys (loudspeaker sets)
+  unsigned *mix_order;       // [Tmax][N+M] channels of every object split sorted by key (mix_order_kernel)
+  int *mix_counts;           // [Tmax][kMaxObjectSplits][2] listed / dense channels of every split
   int *err_flag;             // error bits raised by kernels
   int ks_dev;                // this launch's number of splits is grp_count[1] (grouped launch), not KS
   int k0;                    // first period of this launch (a call may be issued in chunks)

@@ -436,6 +436,7 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   if (k.hoa_delay + 4 > p.hist) throw Unsupported{"hoa delay exceeds max_delay_samples"};
 
   const int C = p.N + p.M;
+  if (C > kMaxSplitChannels * kMaxObjectSplits) throw Unsupported{"more than 131072 object + DirectSpeakers channels"};
   r->s_cfg = (int)cfg.object_splits;
   p.S = 1;
   p.W = 1; p.rank = 0; p.l0 = 0; p.l1 = p.L; p.dif = p.N > 0;
@@ -490,6 +491,9 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
     p.bus_part = r->dalloc<float>((size_t)3 * p.L * cap * p.B, false);
   }
   p.mix_recs = r->dalloc<float>((size_t)p.Tmax * std::max(1, C) * kMixRecWords, false);
+  p.mix_keys = r->dalloc<unsigned>((size_t)p.Tmax * std::max(1, C), false);
+  p.mix_order = r->dalloc<unsigned>((size_t)p.Tmax * std::max(1, C), false);
+  p.mix_counts = r->dalloc<int>((size_t)p.Tmax * kMaxObjectSplits * 2, false);
   p.err_flag = r->dalloc<int>(4);
   CK(cudaMallocHost(&r->h_err, 4 * sizeof(int)));
   r->h_err[0] = 0;
@@ -560,7 +564,7 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   }
   CK(cudaStreamSynchronize(r->stream));
 
-  r->kernels_per_call = 2 * (C > 0) + (p.H > 0) + (p.N > 0) + 4;   // long launch: one object split, ungrouped cMAC
+  r->kernels_per_call = 4 * (C > 0) + (p.H > 0) + (p.N > 0) + 4;   // long launch: one object split, ungrouped cMAC
   r->error.reserve(512);   // so that reporting an argument error allocates nothing
   return r.release();
 }
@@ -597,10 +601,11 @@ int object_splits_for(const bear_cuda_renderer *r, int n)
 {
   const Layout &p = r->lay;
   const int C = p.N + p.M;
-  const int maxS = std::min(32, C > 0 ? (C + kMixChunk - 1) / kMixChunk : 1);
-  if (r->s_cfg) return std::max(1, std::min(r->s_cfg, maxS));
+  const int maxS = std::min(kMaxObjectSplits, C > 0 ? (C + 2 * kMixChunk - 1) / (2 * kMixChunk) : 1);
+  const int minS = (C + kMaxSplitChannels - 1) / kMaxSplitChannels;   // a split is sorted in shared memory
+  if (r->s_cfg) return std::max(std::max(1, minS), std::min(r->s_cfg, maxS));
   const int tiles = std::max(1, n * p.B / kMixTile);
-  return std::max(1, std::min((2 * 4 * 148 + tiles - 1) / tiles, maxS));
+  return std::max(std::max(1, minS), std::min((2 * 5 * 148 + tiles - 1) / tiles, maxS));
 }
 // Periods per upload chunk of a host-buffer call whose period takes bytes_per_period on the bus.
 // A chunk of any size needs ~0.15 ms to pass through the six kernels, so a chunk should take at least
@@ -669,7 +674,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
     if (p.N + p.M > 0) {
       mark(BEAR_CUDA_KERNEL_MIX_AUX); launch_mix_prep(p, n, st);
       mark(BEAR_CUDA_KERNEL_MIX); launch_mix(p, n, st);
-      launches += 2;
+      launches += 4;   // prep + order, mix + dense
       if (p.S > 1) { mark(BEAR_CUDA_KERNEL_MIX_AUX); launch_bus_sum(p, n, st); launches++; }
     }
     if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, n, st); launches++; }
