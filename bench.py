@@ -2,16 +2,21 @@
 """Benchmark of the BEAR render hot path (BASELINE.json metric: object-channels rendered in real
 time at 48 kHz, N x RTF).
 
-A step = one pass of the hot path over T periods of synthetic input of BASELINE.json configs[1]
-("64 moving Objects with per-block metadata changes, block size 512"; the listener yaw steps 2
-degrees per block so every block crossfades to a new BRIR view) per GPU.  With --gpus N each rank
-renders its own group of 64 objects of one 64*N-object scene and the per-step stereo partial mixes
-are summed with an NCCL all-reduce (weak scaling).
+Default workload = BASELINE.json configs[3], the configuration the north_star target is quoted on:
+ONE scene of 1024 simultaneous moving Objects (new metadata every period), period 256, the listener
+yaw stepping 2 degrees per period so that every period crossfades to a new BRIR view.  A step = one
+pass of the hot path over 10 s of that scene (1872 periods).  With --gpus N the scene is sharded by
+object group, 1024 / N objects per rank (strong scaling): every rank mixes its objects onto the 48 + 24
+bus rows, convolves 24 / N of the loudspeakers on the sum of all ranks' rows (read from the peers over
+NVLink) and the stereo partial mixes are summed with NCCL -- all of it inside the library
+(bear_cuda_comm_connect); torch.distributed only carries the 256-byte set-up blobs and the timing
+barrier.  `--workload cfg2_ht` is BASELINE configs[1] (64 moving Objects per GPU, period 512, weak
+scaling), the headline of round 1; at N = 1 it is also reported as the extra key `configs1_64_objects`.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload ...]
 
 ours:      value = device-resident throughput (audio and tables already in HBM), CUDA events on the
-           renderer's stream; e2e = the same metric through the host-buffer C-ABI call
+           renderer's stream, max over ranks; e2e = the same metric through the host-buffer C-ABI call
            (bear_cuda_process_batch: pinned host -> device -> kernels -> host).
 reference: the CPU implementation of the same path (the oracle port; the reference renderer itself
            needs VISR + Boost, which are not available) on all host cores, one instance per core.
@@ -22,7 +27,6 @@ import os
 import subprocess
 import sys
 import tempfile
-import threading
 import time
 from pathlib import Path
 
@@ -34,10 +38,15 @@ sys.path.insert(0, str(ROOT))
 FS = 48000
 METRIC = "object-channels rendered real-time at 48 kHz per B200 (N x RTF)"
 UNIT = "object-channels x RTF"
+GROUP = 64    # objects per generated group (seed = group index): the scene does not depend on the GPU count
 WORKLOADS = {
-    # name: (scenario, period, objects per GPU)
-    "cfg2_ht": ("cfg2_ht", 512, 64),
-    "cfg4_ht": ("cfg4_ht", 256, 1024),
+    # name: (period, objects, scaling, audio scale, text)
+    "cfg4_ht": (256, 1024, "strong", 0.02,
+                "BASELINE configs[3]: 1024 simultaneous moving Objects, per-period metadata, block 256, listener yaw "
+                "2 deg/block (view crossfade every block), sharded by object group"),
+    "cfg2_ht": (512, 64, "weak", 0.1,
+                "BASELINE configs[1]: 64 moving Objects per GPU, per-block metadata, block 512, listener yaw 2 deg/block "
+                "(view crossfade every block)"),
 }
 
 
@@ -47,29 +56,70 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="cfg2_ht", choices=sorted(WORKLOADS))
-    ap.add_argument("--seconds", type=float, default=10.0, help="audio seconds per step and GPU")
+    ap.add_argument("--workload", default="cfg4_ht", choices=sorted(WORKLOADS))
+    ap.add_argument("--seconds", type=float, default=10.0, help="audio seconds per step")
     ap.add_argument("--cpu-sample-blocks", type=int, default=0, help="blocks of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="only the headline workload")
     ap.add_argument("--chunk-blocks", type=int, default=0, help="periods per launch group (0 = library default)")
     ap.add_argument("--cmac-splits", type=int, default=0, help="partial spectra per period (0 = library default)")
+    ap.add_argument("--batch-files", type=int, default=256, help="files of the configs[4] extra (0 = skip)")
     return ap.parse_args()
 
 
 # ------------------------------------------------------------------------------------------- workload
-def make_workload(workload, T, group=0, num_views=180, seed=0):
-    """Synthetic default-shaped data file + tables + audio for T periods of one object group."""
+_DATA = {}
+
+
+def data_and_control(num_views=180, seed=0):
     from bear_b200 import control, data_file
-    scen, B, _ = WORKLOADS[workload]
-    data = data_file.from_tree(data_file.synthetic_tree(seed=seed, num_views=num_views))
-    ctl = control.HostControl(data)
-    N, M, H, tb = control.scenario(ctl, scen, T, B, seed=1000 + group)
+    key = (num_views, seed)
+    if key not in _DATA:
+        data = data_file.from_tree(data_file.synthetic_tree(seed=seed, num_views=num_views))
+        _DATA[key] = (data, control.HostControl(data))
+    return _DATA[key]
+
+
+def scene_tables(ctl, T, B, first_object, count, dense_every=0, num_views=180):
+    """Tables of objects [first_object, first_object + count) of the scene, generated group by group
+    (seed = group index).  Azimuths ~U(-180,180) change every period (benchmark.cpp:121-147
+    `update_every_time`), every 4th object is half diffuse, the listener yaw steps 2 degrees per
+    period.  dense_every = k: every k-th object gets all 24 gains non-zero, direct and diffuse (the
+    reference benchmark's `extent` objects, visr_bear/test/benchmark.cpp:132-139,274-277)."""
+    from bear_b200 import control
+    assert first_object % GROUP == 0 and count % GROUP == 0
+    yaw = (2.0 * np.arange(T)) % 360.0
+    parts = []
+    for g in range(first_object // GROUP, (first_object + count) // GROUP):
+        rng = np.random.default_rng(1000 + g)
+        az = rng.uniform(-180, 180, size=(T, GROUP))
+        dif = np.where(np.arange(GROUP) % 4 == 3, 0.5, 0.0)
+        tb = ctl.tables(T, obj_az=az, obj_diffuse=dif, yaw_deg=yaw)
+        if dense_every:
+            L = ctl.L
+            for i in range(0, GROUP, dense_every):
+                w = rng.uniform(0.05, 1.0, size=(T, L))
+                w /= np.sqrt((w ** 2).sum(-1, keepdims=True))
+                tb["direct_gains"][:, :, i] = (w * np.sqrt(0.5)).astype(np.float32)
+                tb["diffuse_gains"][:, :, i] = (w * np.sqrt(0.5)).astype(np.float32)
+        parts.append(tb)
+    tb = control.BlockTables(parts[0])
+    for key in ("direct_gains", "diffuse_gains"):
+        tb[key] = np.ascontiguousarray(np.concatenate([p[key] for p in parts], axis=2))
+    tb["direct_delays"] = np.ascontiguousarray(np.concatenate([p["direct_delays"] for p in parts], axis=1))
     if num_views != 180:  # reduced view table for CPU samples: cycle through the views that exist
         tb["brir_index"] = (np.arange(T) % num_views).astype(np.int32)
         tb["static_delays"] = ctl.static_delays(tb["brir_index"]).astype(np.float32)
-    scale = 0.1 if N <= 64 else 0.02
-    audio = control.synth_audio(N, T * B, seed_base=10000 * group, scale=scale)
-    return data, ctl, N, B, tb, audio
+    return tb
+
+
+def scene_audio(first_object, count, samples, scale):
+    from bear_b200 import control
+    return control.synth_audio(count, samples, seed_base=10000 + first_object, scale=scale)
+
+
+def periods_per_step(args, B):
+    return max(8, int(args.seconds * FS / B) // 8 * 8)
 
 
 # ------------------------------------------------------------------------------------------- clocks
@@ -124,7 +174,10 @@ _W = {}
 def _cpu_worker_init(workload, T, num_views):
     sys.path.insert(0, str(ROOT))
     from oracle import bear_ref
-    data, ctl, N, B, tb, audio = make_workload(workload, T, num_views=num_views)
+    B, N, _, scale, _ = WORKLOADS[workload]
+    data, ctl = data_and_control(num_views)
+    tb = scene_tables(ctl, T, B, 0, N, num_views=num_views)
+    audio = scene_audio(0, N, T * B, scale)
     _W.update(r=bear_ref.RefRenderer(data, N, 0, 0, B), blocks=tb.blocks(), audio=audio, N=N, B=B, T=T)
 
 
@@ -140,6 +193,14 @@ def cpu_sample_blocks(args):
     return 48 if args.workload == "cfg2_ht" else 24
 
 
+def oracle_build():
+    try:
+        flags = [l for l in (ROOT / "oracle" / "Makefile").read_text().splitlines() if l.startswith("CXXFLAGS")]
+        return "oracle/bear_ref.cpp f32, own FFT, " + (flags[0].split("=", 1)[1].strip() if flags else "")
+    except OSError:
+        return "oracle/bear_ref.cpp f32"
+
+
 def cpu_baseline_single(args):
     """Oracle port on one host core, bounded sample of the same workload (~10-20 s of CPU work)."""
     T = cpu_sample_blocks(args)
@@ -152,8 +213,35 @@ def cpu_baseline_single(args):
     N, B = _W["N"], _W["B"]
     audio_s = reps * T * B / FS
     return {"value": N * audio_s / total, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "%d x %d periods of %d (%.2f s of audio) of the same workload, oracle/bear_ref f32, 1 thread"
-                      % (reps, T, B, audio_s)}
+            "sample": "%d x %d periods of %d (%.2f s of audio) of the same workload (%d objects), %s, 1 thread"
+                      % (reps, T, B, audio_s, N, oracle_build())}
+
+
+def libear_convolver_anchor():
+    """The reference's own partitioned convolver (libear BlockConvolver compiled in place, oracle/_ref)
+    on the convolution load of one channel -- 2976 taps at block 512 -- next to the oracle's convolver
+    on the same load: a sanity anchor for how far the port is from reference-grade CPU code (VISR's
+    convolver itself is not in the reference tree)."""
+    try:
+        from oracle import bear_ref
+        B, taps, blocks, reps = 512, 2976, 40, 4
+        rng = np.random.default_rng(0)
+        x = rng.standard_normal(blocks * B).astype(np.float32)
+        h = rng.standard_normal(taps).astype(np.float32)
+        out = {}
+        for name, fn in (("libear_block_convolver", bear_ref.ear_block_convolve), ("oracle_upols", bear_ref.upols)):
+            fn(x[:4 * B], h, B)
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                fn(x, h, B)
+            dt = (time.perf_counter() - t0) / (reps * blocks)          # seconds per channel-period
+            out[name] = {"us_per_channel_period": dt * 1e6, "rtf_48_channels": (B / FS) / (48 * dt)}
+        out["note"] = ("one thread; one channel-convolution of 2976 taps per 512-sample period, filter set-up included "
+                       "(amortised over %d periods); rtf_48_channels = real-time factor if one thread ran all 48 bus "
+                       "channels" % blocks)
+        return out
+    except Exception as e:  # the _ref library is optional
+        return {"unavailable": str(e)[:200]}
 
 
 def run_reference(args, rank):
@@ -164,7 +252,7 @@ def run_reference(args, rank):
     import multiprocessing as mp
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
     T = cpu_sample_blocks(args)
-    scen, B, N = WORKLOADS[args.workload]
+    B, N, scaling, _, _ = WORKLOADS[args.workload]
     ctx = mp.get_context("fork")
     with ctx.Pool(cores, initializer=_cpu_worker_init, initargs=(args.workload, T, min(180, T))) as pool:
         for _ in range(max(1, args.warmup)):
@@ -178,65 +266,100 @@ def run_reference(args, rank):
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * wall / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": workload_config(args, T, cores),
+        "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, T, 1, cores),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
-                         "sample": "%d instances x %d periods of %d per step, oracle/bear_ref f32 (the reference "
-                                   "renderer needs VISR+Boost: unbuildable here)" % (cores, T, B)},
+                         "sample": "%d instances x %d periods of %d (%d objects each) per step, %s (the reference "
+                                   "renderer needs VISR+Boost: unbuildable here)" % (cores, T, B, N, oracle_build())},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "libear_convolver_anchor": libear_convolver_anchor(),
     }
     emit(line)
 
 
-def workload_config(args, T, instances=None):
-    scen, B, N = WORKLOADS[args.workload]
-    c = {"workload": "BASELINE configs[1]: 64 moving Objects, per-block metadata, block 512, listener yaw 2 deg/block "
-                     "(view crossfade every block)" if args.workload == "cfg2_ht" else
-                     "BASELINE configs[3] shape: 1024 moving Objects, block 256, view crossfade every block",
-         "objects_per_gpu": N, "period": B, "periods_per_step": T, "audio_seconds_per_step": T * B / FS,
+def workload_config(args, T, world, instances=None):
+    B, N, scaling, _, text = WORKLOADS[args.workload]
+    total = N if scaling == "strong" else N * world
+    c = {"workload": text, "objects_total": total, "objects_per_gpu": total // world, "period": B, "periods_per_step": T,
+         "audio_seconds_per_step": T * B / FS,
          "data_file": "synthetic default shape (180 views x 24 x 2 x 2976 taps, 128-tap decorrelators)",
-         "sharding": "object groups, NCCL all-reduce of stereo partial mixes" if args.gpus > 1 else "single GPU",
-         "l2": "inputs larger than L2 (audio + spectra streamed per step >> 126 MB)"}
+         "sharding": ("object groups; bus rows of 24/N loudspeakers gathered from the peers over NVLink, NCCL reduce "
+                      "of the stereo partial mixes (bear_cuda_comm_connect)") if world > 1 else "single GPU",
+         "l2": "inputs larger than L2 (audio + tables streamed per step >> 126 MB)"}
     if instances:
         c["cpu_instances"] = instances
     return c
 
 
 # ------------------------------------------------------------------------------------------- GPU leg
+class Leg:
+    """One renderer with its share of a scene resident on the device and in pinned host memory."""
+
+    def __init__(self, data, ctl, B, T, first_object, count, scale, local_rank, dense_every=0, **kw):
+        from bear_b200 import device_io
+        from bear_b200.renderer import Renderer, pinned_empty
+        self.T, self.B, self.N = T, B, count
+        self.tb = scene_tables(ctl, T, B, first_object, count, dense_every)
+        self.audio = scene_audio(first_object, count, T * B, scale)
+        self.r = Renderer(data, count, 0, 0, B, max_batch_blocks=T, device=local_rank, **kw)
+        self.local_rank = local_rank
+        self._pinned_empty = pinned_empty
+        self._device_io = device_io
+
+    def make_resident(self):
+        self.io = self._device_io.DeviceBuffers(self.r, device_index=self.local_rank)
+        self.io.load_audio(self.audio)
+        self.io.load_tables(self.tb)
+        self.r.synchronize()
+        self.stream = self.io.stream
+
+    def make_pinned(self, receives=True):
+        pe = self._pinned_empty
+        self.h_audio = pe(self.audio.shape); self.h_audio[:] = self.audio
+        self.h_tb = type(self.tb)({k: pe(v.shape, v.dtype) for k, v in self.tb.items()})
+        for k, v in self.tb.items():
+            self.h_tb[k][...] = v
+        self.h_out = pe((2, self.T * self.B)) if receives else False
+        self.h2d = self.audio.nbytes + sum(v.nbytes for v in self.tb.values())
+        self.d2h = self.h_out.nbytes if receives else 0
+
+    def step_resident(self):
+        self.r.process_device(self.T)
+
+    def step_e2e(self):
+        self.r.process_batch(self.h_audio, None, None, self.h_tb, output=self.h_out)
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
 
-    from bear_b200 import device_io
-    from bear_b200.renderer import Renderer, pinned_empty
+    from bear_b200 import parallel
 
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    scen, B, N = WORKLOADS[args.workload]
-    T = max(8, int(args.seconds * FS / B) // 8 * 8)
-    data, ctl, N, B, tb, audio = make_workload(args.workload, T, group=rank)
-    r = Renderer(data, N, 0, 0, B, max_batch_blocks=T, device=local_rank, chunk_blocks=args.chunk_blocks,
-                 cmac_splits=args.cmac_splits)
-    io = device_io.DeviceBuffers(r, device_index=local_rank)
-    io.load_audio(audio)
-    io.load_tables(tb)
-    r.synchronize()
-    stream = io.stream
-    out_dev = io.output(T)
+    B, N, scaling, scale, _ = WORKLOADS[args.workload]
+    total = N if scaling == "strong" else N * world
+    if total % (world * GROUP):
+        raise SystemExit("%d objects do not split into %d groups of a multiple of %d" % (total, world, GROUP))
+    mine = total // world
+    T = periods_per_step(args, B)
+    data, ctl = data_and_control()
+    leg = Leg(data, ctl, B, T, rank * mine, mine, scale, local_rank, chunk_blocks=args.chunk_blocks,
+              cmac_splits=args.cmac_splits)
+    r = leg.r
+    if world > 1:
+        parallel.connect_renderers(r, rank, world, root=0)
+    leg.make_resident()
+    stream = leg.stream
 
     def barrier():
         r.synchronize()
         torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
-
-    def step_resident():
-        r.process_device(T)
-        if world > 1:
-            with torch.cuda.stream(stream):
-                dist.all_reduce(out_dev)
 
     def timed(fn, steps):
         barrier()
@@ -257,54 +380,40 @@ def run_ours(args, rank, world, local_rank):
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
-    for _ in range(400):      # a fixed count: every rank must issue the same number of collectives
-        step_resident()
+    for _ in range(100):      # a fixed count: every rank must issue the same number of collectives
+        leg.step_resident()
     r.synchronize()
     for _ in range(max(3, args.warmup)):
-        step_resident()
+        leg.step_resident()
+    launches0 = r.get_info().launches_total
+    ms = timed(leg.step_resident, args.steps)
+    launches = r.get_info().launches_total - launches0
+    # per-kernel times: a second pass with an event pair around every kernel (the events themselves
+    # cost a little, so the headline above is taken without them)
     r.set_profiling(True)
     r.get_profile(reset=True)
-    launches0 = r.get_info().launches_total
-    ms = timed(step_resident, args.steps)
-    launches = r.get_info().launches_total - launches0
+    ms_prof = timed(leg.step_resident, args.steps)
     prof = r.get_profile(reset=True)
     r.set_profiling(False)
     info_resident = r.get_info()     # incl. the work items / splits the device chose for this launch
 
     # ---- end to end: pinned host buffers through the host-buffer entry point -------------------
-    h_audio = pinned_empty(audio.shape); h_audio[:] = audio
-    h_tb = type(tb)({k: pinned_empty(v.shape, v.dtype) for k, v in tb.items()})
-    for k, v in tb.items():
-        h_tb[k][...] = v
-    h_out = pinned_empty((2, T * B))
-    h2d = audio.nbytes + sum(v.nbytes for v in tb.values())
-    d2h = h_out.nbytes
-
-    def step_e2e():
-        # host-buffer entry point (chunked uploads overlap the kernels); with several GPUs the partial
-        # mix it leaves in the device output area is then summed over the ranks and fetched again
-        r.process_batch(h_audio, None, None, h_tb, output=h_out)
-        if world > 1:
-            with torch.cuda.stream(stream):
-                dist.all_reduce(out_dev)
-                torch.from_numpy(h_out).copy_(out_dev, non_blocking=True)
-            stream.synchronize()
-
+    leg.make_pinned(receives=(rank == 0))
     e2e_steps = max(3, min(args.steps, 10))
     for _ in range(2):
-        step_e2e()
-    ms_e2e = timed(step_e2e, e2e_steps)
+        leg.step_e2e()
+    ms_e2e = timed(leg.step_e2e, e2e_steps)
     clk = clocks.stop() if rank == 0 else None
     # per-launch kernel times at the chunk size of the host-buffer path (untimed extra call)
     r.set_profiling(True)
     r.get_profile(reset=True)
-    step_e2e()
+    leg.step_e2e()
     e2e_prof = {k: v[0] / max(v[1], 1) for k, v in r.get_profile(reset=True).items() if v[1]}
     r.set_profiling(False)
 
     # the PCIe floor of that call: the same bytes copied host->device from pinned memory, nothing else
-    h_flat = torch.from_numpy(h_audio.reshape(-1))
-    d_flat = torch.empty(h2d // 4, dtype=torch.float32, device="cuda")
+    h_flat = torch.from_numpy(leg.h_audio.reshape(-1))
+    d_flat = torch.empty(leg.h2d // 4, dtype=torch.float32, device="cuda")
 
     def step_copy():
         with torch.cuda.stream(stream):
@@ -313,95 +422,16 @@ def run_ours(args, rank, world, local_rank):
 
     step_copy()
     ms_copy = timed(step_copy, e2e_steps) / e2e_steps
-
-    # ---- the same call fed with the file's interleaved frames (float and 16-bit PCM): what a file
-    # renderer holds after reading a block of a BW64 file; de-interleaving / PCM decoding on the device
-    frames_res = {}
-    if world == 1:
-        tracks = np.arange(N, dtype=np.int32)
-        for fmt, dt, scale in (("f32", np.float32, 1.0), ("s16", np.int16, 32768.0)):
-            h_frames = pinned_empty((T * B, N), dt)
-            h_frames[...] = np.clip(np.round(audio.T * scale), -scale, scale - 1) if fmt != "f32" else audio.T
-
-            def step_frames():
-                r.process_batch_frames(h_frames, tracks, h_tb, output=h_out)
-
-            step_frames()
-            ms_f = timed(step_frames, e2e_steps) / e2e_steps
-            frames_res[fmt] = {"ms_per_step": ms_f, "h2d_bytes_per_step": int(h_frames.nbytes + h2d - audio.nbytes),
-                               "value": N * audio_s_of(T, B) / (ms_f * 1e-3)}
-
-    # ---- real-time use: one period per call through bear_cuda_process (host pointers), wall clock ----
-    stream_ms = None
-    stream_kernels = None
-    if rank == 0:
-        with Renderer(data, N, 0, 0, B, max_batch_blocks=1, device=local_rank) as rs:
-            blk = [tb.block(k) for k in range(8)]
-            xin = [np.ascontiguousarray(audio[:, k * B:(k + 1) * B]) for k in range(8)]
-            out1 = np.empty((2, B), np.float32)
-            for k in range(16):
-                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
-            t0 = time.perf_counter()
-            for k in range(200):
-                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
-            stream_ms = (time.perf_counter() - t0) / 200 * 1e3
-            rs.set_profiling(True)
-            for k in range(50):
-                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
-            stream_kernels = {kk: v[0] / max(v[1], 1) for kk, v in rs.get_profile().items() if v[1]}
-
-    # ---- the "1000 objects in real time" target: 1024 moving objects, period 256 (BASELINE configs[3]
-    # shape on ONE GPU), 2 s of audio per launch, device-resident, same timing method ----
-    many = None
-    if rank == 0 and world == 1 and args.workload == "cfg2_ht":
-        from bear_b200 import control as _control
-        B4, T4 = 256, 376
-        N4, _, _, tb4 = _control.scenario(ctl, "cfg4_ht", T4, B4, seed=77)
-        audio4 = _control.synth_audio(N4, T4 * B4, seed_base=500000, scale=0.02)
-        with Renderer(data, N4, 0, 0, B4, max_batch_blocks=T4, device=local_rank) as r4:
-            io4 = device_io.DeviceBuffers(r4, device_index=local_rank)
-            io4.load_audio(audio4)
-            io4.load_tables(tb4)
-            r4.synchronize()
-            for _ in range(5):
-                r4.process_device(T4)
-            r4.synchronize()
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record(io4.stream)
-            for _ in range(10):
-                r4.process_device(T4)
-            e1.record(io4.stream)
-            e1.synchronize()
-            ms4 = e0.elapsed_time(e1) / 10
-        rtf4 = (T4 * B4 / FS) / (ms4 * 1e-3)
-        many = {"objects": N4, "period": B4, "periods_per_launch": T4, "ms_per_launch": ms4, "rtf": rtf4,
-                "object_channels_x_rtf": N4 * rtf4,
-                "note": "1024 moving objects with per-period metadata and a view change every period on one GPU"}
-        del audio4, tb4
-
-    # ---- control tail on the device (delays + gain normalisation + split), kernel time only ----
-    control_ms = None
-    if rank == 0:
-        import copy
-        d2 = copy.copy(data)
-        S = 40   # default.tf: max loudspeaker delay 38 + 2 (finalise.py:214-215)
-        d2.gain_norm_factors = np.random.default_rng(0).random((S, data.num_views, 2 * ctl.L, 2 * ctl.L, 2),
-                                                               dtype=np.float32)
-        Tc = min(T, 128)
-        with Renderer(d2, N, 0, 0, B, max_batch_blocks=Tc, device=local_rank) as rc:
-            raw = np.concatenate([tb["direct_gains"][:Tc], tb["diffuse_gains"][:Tc]], axis=1)
-            rc.set_profiling(True)
-            for _ in range(4):
-                rc.control_tables(raw, None, tb["brir_index"][:Tc])
-            t_ctl, n_ctl = rc.get_profile()["control_kernel"]
-            control_ms = {"ms_per_launch": t_ctl / max(n_ctl, 1), "periods_per_launch": Tc, "objects": N,
-                          "ms_per_10s_audio": t_ctl / max(n_ctl, 1) * T / Tc,
-                          "note": "control_kernel (DirectDelayCalc + GainNorm + DirectDiffuseSplit + StaticDelayCalc on the "
-                                  "device), gain-norm table of default.tf shape with random values"}
+    del d_flat
 
     audio_s = T * B / FS
-    value = world * N * audio_s * args.steps / (ms * 1e-3)
-    e2e_value = world * N * audio_s * e2e_steps / (ms_e2e * 1e-3)
+    value = total * audio_s * args.steps / (ms * 1e-3)
+    e2e_value = total * audio_s * e2e_steps / (ms_e2e * 1e-3)
+    h2d_all, d2h_all = leg.h2d * world, 2 * T * B * 4
+
+    extras = {}
+    if not args.no_extras:
+        extras = run_extras(args, rank, world, local_rank, data, ctl, leg, barrier)
 
     if rank == 0:
         peaks = {}
@@ -412,25 +442,25 @@ def run_ours(args, rank, world, local_rank):
         peak, which = (peaks["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)") if "hbm_gbs" in peaks else \
             (6650.0, "fallback (B200_PROFILING.md)")
         info = info_resident
-        L, A, P = data.num_virtual_loudspeakers, data.n_hoa_channels, info.num_partitions
+        L, P = data.num_virtual_loudspeakers, info.num_partitions
+        nl = info.speakers_end - info.speakers_begin
         KS = info.cmac_splits_last or info.cmac_splits
-        views = np.asarray(tb["brir_index"]).astype(np.int64)
+        views = np.asarray(leg.tb["brir_index"]).astype(np.int64)
         n_views = int(np.unique(views).size)
-        S = info.object_splits
         fB = 4 * T * B                                   # bytes of one float row of the launch
-        # Algorithmic (minimum-traffic) bytes per launch of every kernel, DESIGN.md section 4:
+        # Algorithmic (minimum-traffic) bytes per launch of every kernel on THIS rank, DESIGN.md section 4:
         #   mix          audio in + gain/delay tables in, direct (2L rows) and diffuse (L rows) bus out
-        #   decorrelate  diffuse bus in, decorrelated bus out
-        #   bus_fdl      direct bus + decorrelated bus in, 2L packed spectra (B x 8 bytes a period) out
+        #   decorrelate  diffuse bus in, decorrelated bus out            (this rank's nl loudspeakers)
+        #   bus_fdl      direct bus + decorrelated bus in, packed spectra (B x 8 bytes a period) out
         #   cmac         filter partitions of every DISTINCT view of the launch once (the kernel groups
         #                the periods by view), every delay-line spectrum once, partial spectra out
         #   ifft_out     partial spectra in (old-view ones too in a view-change period), 2 rows out
         xf = int(np.count_nonzero(np.diff(np.concatenate([[views[0]], views])) != 0))
         alg_by_kernel = {
-            "mix_kernel": N * fB + 4 * T * (2 * 2 * L * N + 2 * 2 * N) + S * 3 * L * fB,
-            "decorrelate_kernel": S * L * fB + L * fB,
-            "bus_fdl_kernel": S * 2 * L * fB + L * fB + 2 * L * 2 * fB,
-            "cmac_kernel": 8 * B * (2 * L * P * n_views + 2 * L * T + 2 * 2 * KS * T),
+            "mix_kernel": mine * fB + 4 * T * (2 * 2 * L * mine + 2 * 2 * mine) + 3 * L * fB,
+            "decorrelate_kernel": 2 * nl * fB,
+            "bus_fdl_kernel": 2 * nl * fB + nl * fB + 2 * nl * 2 * fB,
+            "cmac_kernel": 8 * B * (2 * nl * P * n_views + 2 * nl * T + 2 * 2 * KS * T),
             "ifft_out_kernel": 8 * B * 2 * KS * (T + xf) + 2 * fB,
         }
         step_ms_kernels = sum(v[0] for v in prof.values()) / max(args.steps, 1)
@@ -444,67 +474,62 @@ def run_ours(args, rank, world, local_rank):
                                "frac": alg_by_kernel[name] / (ms_k * 1e-3) / 1e9 / peak,
                                "share_of_step": (t_k / max(args.steps, 1)) / step_ms_kernels}
         dominant = max(by_kernel, key=lambda k: by_kernel[k]["share_of_step"])
-        # cmac_kernel under the two older accountings, for comparison across rounds: one filter set per
-        # PERIOD (what a kernel without view grouping must read), and SURVEY 8(d)'s single-period
-        # streaming figure (delay-line partitions re-read by each of the P periods that use them,
-        # filters of old and new view both read in a view-change period)
-        alg_per_period = T * 8 * B * (2 * L * P + 2 * L + 2 * 2 * KS)
-        alg_survey = T * 2 * 8 * B * (L * P + L * P * 2.0 + KS * 2.0)
-        t_cmac, n_cmac = prof["cmac_kernel"]
-        cmac_ms = t_cmac / max(n_cmac, 1)
         traffic_all = {}
         tpath = ROOT / "profiles" / "kernel_traffic.json"
-        if tpath.exists():
+        if tpath.exists() and world == 1:
             try:
                 traffic_all = json.loads(tpath.read_text()).get(args.workload, {})
             except Exception:
                 traffic_all = {}
         traffic = traffic_all.get(dominant)
         dom = by_kernel[dominant]
+        conv = ("decorrelate_kernel", "bus_fdl_kernel", "cmac_kernel", "ifft_out_kernel")
+        conv_bytes = sum(alg_by_kernel[k] for k in conv if k in by_kernel)
+        conv_ms = sum(by_kernel[k]["avg_launch_ms"] for k in conv if k in by_kernel)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(3, args.warmup), "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args, T),
-            "rtf_per_gpu": audio_s * args.steps / (ms * 1e-3),
+            "scaling": scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args, T, world),
+            "rtf": audio_s * args.steps / (ms * 1e-3),
             "roofline": {"bound": "hbm", "kernel": dominant, "achieved": dom["achieved"], "peak": peak, "unit": "GB/s",
                          "frac": dom["frac"], "traffic": traffic, "peak_source": which,
                          "algorithmic_bytes_per_launch": dom["algorithmic_bytes_per_launch"],
                          "avg_launch_ms": dom["avg_launch_ms"], "share_of_step": dom["share_of_step"],
                          "traffic_source": "profiles/kernel_traffic.json (ncu --set full of the same command, "
                                            "dram read+write per launch)",
-                         "note": "dominant kernel by time; no tensor-core work on this path, so every kernel is "
-                                 "held against HBM.  A fraction well below 1 with traffic ~ algorithmic bytes "
-                                 "means the kernel is bound by FP32 issue / latency, not by re-reads "
+                         "note": "dominant kernel by time (rank 0's launches); no tensor-core work on this path, so "
+                                 "every kernel is held against HBM.  A fraction well below 1 with traffic ~ algorithmic "
+                                 "bytes means the kernel is bound by FP32 issue / latency, not by re-reads "
                                  "(DESIGN.md section 4)"},
             "roofline_by_kernel": {k: dict(v, traffic=traffic_all.get(k)) for k, v in by_kernel.items()},
-            "cmac_accounting": {
-                "distinct_views_in_launch": n_views, "work_items": int(info.cmac_items_last),
-                "splits": int(KS), "avg_launch_ms": cmac_ms,
-                "per_period_filter_bytes_per_launch": alg_per_period,
-                "achieved_per_period_accounting": alg_per_period / (cmac_ms * 1e-3) / 1e9 if cmac_ms > 0 else 0.0,
-                "survey_8d_streaming_bytes_per_launch": alg_survey,
-                "achieved_survey_8d": alg_survey / (cmac_ms * 1e-3) / 1e9 if cmac_ms > 0 else 0.0,
-                "note": "GB/s-equivalents above the HBM peak are possible because the kernel reads each view's "
-                        "filters once per launch (grouping) and the delay line mostly from L2"},
+            "convolution_kernels": {"algorithmic_bytes_per_launch": int(conv_bytes), "ms": conv_ms,
+                                    "achieved": conv_bytes / (conv_ms * 1e-3) / 1e9 if conv_ms else None,
+                                    "frac": conv_bytes / (conv_ms * 1e-3) / 1e9 / peak if conv_ms else None,
+                                    "note": "decorrelate + bus_fdl + cmac + ifft_out together (north_star: roofline "
+                                            "fraction in the convolution kernels)"},
+            "cmac": {"distinct_views_in_launch": n_views, "work_items": int(info.cmac_items_last), "splits": int(KS)},
             "kernel_ms_per_step": {k: v[0] / max(args.steps, 1) for k, v in prof.items() if v[1]},
-            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "ms_per_step_with_kernel_events": ms_prof / args.steps,
+            "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d_all, "d2h_bytes_per_step": d2h_all,
                     "ms_per_step": ms_e2e / e2e_steps, "steps": e2e_steps,
                     "kernel_ms_per_chunk_launch": e2e_prof,
-                    "h2d_copy_only_ms": ms_copy, "h2d_copy_only_gbs": h2d / ms_copy * 1e-6,
-                    "api": "bear_cuda_process_batch (pinned host buffers)" if world == 1 else
-                           "bear_cuda_process_batch (pinned host buffers) -> NCCL all-reduce of the partial mixes -> pinned host"},
-            "e2e_file_frames": dict(frames_res, note="bear_cuda_process_batch_frames: interleaved frames as read from "
-                                                     "the file (pinned), same tables; not the headline e2e (that is the "
-                                                     "reference-facing float call above)") if frames_res else None,
+                    "h2d_copy_only_ms": ms_copy, "h2d_copy_only_gbs_per_gpu": leg.h2d / ms_copy * 1e-6,
+                    "api": "bear_cuda_process_batch (pinned host buffers; every rank uploads its objects, rank 0 "
+                           "receives the mix)"},
             "gpu_launches": int(launches),
-            "many_objects": many,
-            "control_tail": control_ms,
-            "stream": {"ms_per_period_call": stream_ms, "period_ms": 1e3 * B / FS,
-                       "kernel_ms_per_period": stream_kernels if rank == 0 else None,
-                       "note": "bear_cuda_process, one period per call incl. host<->device copies and sync (real-time use)"},
             "clocks": clk,
         }
+        if world > 1:
+            # bytes each rank pulls over NVLink per step: its nl loudspeakers' 3 bus rows from W - 1 peers
+            line["exchange"] = {
+                "nvlink_bytes_read_per_rank_per_step": int(3 * nl * fB * (world - 1)),
+                "nccl_reduce_bytes_per_step": int(2 * fB),
+                "ms_per_step": sum(v[0] for k, v in prof.items() if k == "exchange") / max(args.steps, 1),
+                "note": "exchange = the one-word NCCL all-reduce that orders the ranks before the rows are read + the "
+                        "NCCL reduce of the stereo partial mixes (CUDA events on rank 0's stream: includes waiting for "
+                        "the slowest rank); bus_gather_kernel is counted under mix_aux_kernels"}
+        line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_single(args)
         emit(line)
@@ -512,6 +537,161 @@ def run_ours(args, rank, world, local_rank):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def run_extras(args, rank, world, local_rank, data, ctl, leg, barrier):
+    """Numbers next to the headline.  At every N: configs[4] (batch of files, sharded by file).  At
+    N = 1 also: configs[1] (64 objects, period 512), the dense-gain variant of the headline scene, the
+    interleaved-frames entry point, the one-period real-time call and the control tail on the device."""
+    import torch
+    import torch.distributed as dist
+    from bear_b200 import control, parallel
+    from bear_b200.renderer import Renderer, pinned_empty
+    extras = {}
+    B, N, scaling, scale, _ = WORKLOADS[args.workload]
+    T = leg.T
+
+    def event_ms(fn, steps, stream):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        e1.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    # ---- configs[4]: batch of mixed files sharded by file, no collective ------------------------
+    if args.batch_files:
+        Bf, Tf, distinct = 512, max(8, int(10.0 * FS / 512) // 8 * 8), 2
+        files = []
+        for f in range(distinct):
+            Nf, Mf, Hf, tbf = control.scenario(ctl, "cfg5_ht", Tf, Bf, seed=100 + f)
+            audio = [control.synth_audio(c, Tf * Bf, 1000 * f + s, 0.05) for c, s in ((Nf, 0), (Mf, 100), (Hf, 200))]
+            pinned = []
+            for a in audio:
+                p = pinned_empty(a.shape); p[:] = a
+                pinned.append(p)
+            ptb = type(tbf)({k: pinned_empty(v.shape, v.dtype) for k, v in tbf.items()})
+            for k, v in tbf.items():
+                ptb[k][...] = v
+            files.append((*pinned, ptb))
+        outf = pinned_empty((2, Tf * Bf))
+        my_files = parallel.file_shard(rank, world, args.batch_files)
+        with Renderer(data, Nf, Mf, Hf, Bf, max_batch_blocks=Tf, device=local_rank) as rf:
+            for i in range(2):
+                rf.reset()
+                rf.process_batch(*files[i % distinct][:3], files[i % distinct][3], output=outf)
+            barrier()
+            t0 = time.perf_counter()
+            for idx in my_files:
+                o, d, h, tbf = files[idx % distinct]
+                rf.reset()
+                rf.process_batch(o, d, h, tbf, output=outf)
+            torch.cuda.synchronize()
+            dt = torch.tensor([time.perf_counter() - t0], device="cuda")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        secs = float(dt.item())
+        extras["batch_files"] = {
+            "workload": "BASELINE configs[4]: %d files x (16 Objects + 12 DirectSpeakers + 16 HOA channels, %.1f s, "
+                        "period 512), sharded by file, no collective" % (args.batch_files, Tf * Bf / FS),
+            "files": args.batch_files, "files_per_s": args.batch_files / secs, "wall_s": secs,
+            "channels_x_rtf": (Nf + Mf + Hf) * args.batch_files * (Tf * Bf / FS) / secs, "scaling": "strong",
+            "api": "bear_cuda_reset + bear_cuda_process_batch (pinned host buffers), wall clock, max over ranks"}
+        del files, outf
+    if world > 1 or rank != 0:
+        return extras
+
+    # ---- the other BASELINE object config on one GPU (configs[1]: 64 moving objects, period 512) ----
+    other = "cfg2_ht" if args.workload == "cfg4_ht" else "cfg4_ht"
+    Bo, No, _, so, text = WORKLOADS[other]
+    To = periods_per_step(args, Bo)
+    lo = Leg(data, ctl, Bo, To, 0, No, so, local_rank)
+    lo.make_resident()
+    for _ in range(20):
+        lo.step_resident()
+    ms_o = event_ms(lo.step_resident, 10, lo.stream)
+    lo.r.set_profiling(True)
+    lo.r.get_profile(reset=True)
+    for _ in range(4):
+        lo.step_resident()
+    prof_o = {k: v[0] / max(v[1], 1) for k, v in lo.r.get_profile(reset=True).items() if v[1]}
+    lo.r.set_profiling(False)
+    lo.make_pinned()
+    for _ in range(2):
+        lo.step_e2e()
+    ms_oe = event_ms(lo.step_e2e, 5, lo.stream)
+    a_s = To * Bo / FS
+    extras["configs1_64_objects" if other == "cfg2_ht" else "configs3_1024_objects"] = {
+        "workload": text, "objects": No, "period": Bo, "periods_per_step": To,
+        "value": No * a_s / (ms_o * 1e-3), "ms_per_step": ms_o, "kernel_ms_per_launch": prof_o,
+        "e2e": {"value": No * a_s / (ms_oe * 1e-3), "ms_per_step": ms_oe, "h2d_bytes_per_step": lo.h2d}}
+    if No <= 64:
+        # interleaved file frames (float and 16-bit PCM) on that scene: what a file renderer holds after
+        # reading a block of a BW64 file; de-interleaving / PCM decoding on the device
+        frames = {}
+        tracks = np.arange(No, dtype=np.int32)
+        for fmt, dtp, sc in (("f32", np.float32, 1.0), ("s16", np.int16, 32768.0)):
+            h_frames = pinned_empty((To * Bo, No), dtp)
+            h_frames[...] = np.clip(np.round(lo.audio.T * sc), -sc, sc - 1) if fmt != "f32" else lo.audio.T
+            fn = lambda: lo.r.process_batch_frames(h_frames, tracks, lo.h_tb, output=lo.h_out)
+            fn()
+            ms_f = event_ms(fn, 5, lo.stream)
+            frames[fmt] = {"ms_per_step": ms_f, "value": No * a_s / (ms_f * 1e-3)}
+        extras["e2e_file_frames"] = dict(frames, note="bear_cuda_process_batch_frames on the 64-object scene: "
+                                                      "interleaved frames as read from the file (pinned), same tables")
+        # real-time use: one period per call through bear_cuda_process (host pointers), wall clock
+        with Renderer(data, No, 0, 0, Bo, max_batch_blocks=1, device=local_rank) as rs:
+            blk = [lo.tb.block(k) for k in range(8)]
+            xin = [np.ascontiguousarray(lo.audio[:, k * Bo:(k + 1) * Bo]) for k in range(8)]
+            out1 = np.empty((2, Bo), np.float32)
+            for k in range(16):
+                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
+            t0 = time.perf_counter()
+            for k in range(200):
+                rs.process(xin[k % 8], None, None, blk[k % 8], output=out1)
+            extras["stream"] = {"ms_per_period_call": (time.perf_counter() - t0) / 200 * 1e3, "period_ms": 1e3 * Bo / FS,
+                                "objects": No,
+                                "note": "bear_cuda_process, one period per call incl. host<->device copies and sync"}
+    lo.r.close()
+    del lo
+
+    # ---- the headline scene with extent-like objects: every 4th object has all 24 gains non-zero ----
+    ld = Leg(data, ctl, B, T, 0, N, scale, local_rank, dense_every=4)
+    ld.make_resident()
+    for _ in range(5):
+        ld.step_resident()
+    ms_d = event_ms(ld.step_resident, 5, ld.stream)
+    ld.r.set_profiling(True)
+    ld.r.get_profile(reset=True)
+    for _ in range(3):
+        ld.step_resident()
+    prof_d = {k: v[0] / max(v[1], 1) for k, v in ld.r.get_profile(reset=True).items() if v[1]}
+    extras["dense_gains"] = {
+        "workload": "the headline scene with every 4th object dense (24 non-zero direct and diffuse gains: the "
+                    "reference benchmark's extent objects, visr_bear/test/benchmark.cpp:132-139,274-277)",
+        "objects": N, "value": N * (T * B / FS) / (ms_d * 1e-3), "ms_per_step": ms_d, "kernel_ms_per_launch": prof_d}
+    ld.r.close()
+    del ld
+
+    # ---- control tail on the device (delays + gain normalisation + split), kernel time only ----
+    import copy
+    d2 = copy.copy(data)
+    S = 40   # default.tf: max loudspeaker delay 38 + 2 (finalise.py:214-215)
+    d2.gain_norm_factors = np.random.default_rng(0).random((S, data.num_views, 2 * ctl.L, 2 * ctl.L, 2), dtype=np.float32)
+    Tc, Nc = 128, 64
+    tbc = scene_tables(ctl, Tc, 512, 0, Nc)
+    with Renderer(d2, Nc, 0, 0, 512, max_batch_blocks=Tc, device=local_rank) as rc:
+        raw = np.concatenate([tbc["direct_gains"], tbc["diffuse_gains"]], axis=1)
+        rc.set_profiling(True)
+        for _ in range(4):
+            rc.control_tables(raw, None, tbc["brir_index"])
+        t_ctl, n_ctl = rc.get_profile()["control_kernel"]
+        extras["control_tail"] = {"ms_per_launch": t_ctl / max(n_ctl, 1), "periods_per_launch": Tc, "objects": Nc,
+                                  "note": "control_kernel (DirectDelayCalc + GainNorm + DirectDiffuseSplit + StaticDelayCalc "
+                                          "on the device), gain-norm table of default.tf shape with random values"}
+    return extras
 
 
 _REAL_STDOUT = None
@@ -526,10 +706,6 @@ def emit(line):
     else:
         sys.stdout.write(data.decode())
         sys.stdout.flush()
-
-
-def audio_s_of(T, B):
-    return T * B / FS
 
 
 def main():
