@@ -643,7 +643,10 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
   for (int i = 0; i < kMixSlots / 2; i++) accQ[i] = 0ull;
   unsigned nact = 0u, spk_lo = 0u, spk_hi = 0u;   // slots in use and their loudspeakers (same in all threads)
   bool qdirty = false;
-  // end of a run: the slot sums go to the bus rows of their loudspeakers
+  // end of a run: the slot sums are added to the bus rows of their loudspeakers with reductions
+  // (red.global.add: nothing comes back, so the thread does not wait for L2; every address belongs to
+  // one thread, whose stores and reductions to it are performed in program order -- the result does not
+  // depend on timing)
   auto flush = [&]() {
 #pragma unroll
     for (int i = 0; i < kMixSlots; i++) {
@@ -652,12 +655,12 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
         float vL, vR;
         unpack2(acc[i], vL, vR);
         float *pd = od + (size_t)(2 * l) * os;
-        pd[0] += vL;
-        pd[os] += vR;
+        atomicAdd(pd, vL);
+        atomicAdd(pd + os, vR);
         if (qdirty) {
           float qa, qb;
           unpack2(accQ[i >> 1], qa, qb);
-          oq[(size_t)l * os] += (i & 1) ? qb : qa;
+          atomicAdd(oq + (size_t)l * os, (i & 1) ? qb : qa);
         }
       }
       acc[i] = 0ull;
@@ -764,12 +767,15 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
 }
 
 // mix_dense_kernel: the channels whose gains are dense (more than kMixSlots non-zero loudspeakers:
-// objects with extent), straight from the gain tables with all 3L accumulators in registers, added to
-// the bus rows.  Every thread reads the same gain address (a broadcast from L1), the delayed reads
-// come from global memory.  Periods without dense channels return at once.
+// objects with extent), from the gain tables themselves with all 3L accumulators in registers, added
+// to the bus rows.  Per channel the 4 x L table values of the period are staged in shared memory as
+// (start, start, delta, delta) of loudspeaker pairs, so the inner loop is one broadcast load, one
+// packed ramp and two FFMA2 per pair; the delayed reads come from global memory.  Periods without
+// dense channels return at once.
 // grid: periods * B / kMixTile; block kMixTile.
 __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
 {
+  __shared__ __align__(16) float sgd[kMaxSpeakers * 2], sgq[kMaxSpeakers * 2];
   const int tid = threadIdx.x;
   const int t = p.k0 * p.B + blockIdx.x * kMixTile + tid;
   const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
@@ -781,10 +787,13 @@ __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
   if (total == 0) return;
   const float invB = 1.0f / (float)p.B;
   const float rg = (float)(n + p.goff) * invB, rd = (float)(n + p.doff) * invB;
+  const f32x2 rg2 = splat2(rg);
   f32x2 acc[kMaxSpeakers];
-  float accQ[kMaxSpeakers];
+  f32x2 accQ[kMaxSpeakers / 2];
 #pragma unroll
-  for (int l = 0; l < kMaxSpeakers; l++) { acc[l] = 0ull; accQ[l] = 0.f; }
+  for (int l = 0; l < kMaxSpeakers; l++) acc[l] = 0ull;
+#pragma unroll
+  for (int l = 0; l < kMaxSpeakers / 2; l++) accQ[l] = 0ull;
   for (int s = 0; s < p.S; s++) {
     const int c0 = min(C, s * per);
     const int nlisted = p.mix_counts[((size_t)k * kMaxObjectSplits + s) * 2];
@@ -792,27 +801,42 @@ __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
     for (int i = 0; i < ndense; i++) {
       const unsigned e = p.mix_order[(size_t)k * C + c0 + nlisted + i];
       const int c = (int)(e & 0xffffffu);
+      const bool obj = c < p.N, dif = (e >> 30 & 1u) != 0u;
+      __syncthreads();   // the previous channel's gains have been used
+      if (tid < kMaxSpeakers) {
+        const int l = tid, ld = obj ? p.N : p.M;
+        float g0 = 0.f, g1 = 0.f, q0 = 0.f, q1 = 0.f;
+        if (l < L) {
+          const float *g = (obj ? p.g_dir + (size_t)k * L * ld + c : p.g_ds + (size_t)k * L * ld + (c - p.N));
+          g0 = g[(size_t)l * ld]; g1 = g[(size_t)(L + l) * ld];
+          if (dif) {
+            const float *q = p.g_dif + (size_t)k * L * p.N + c;
+            q0 = q[(size_t)l * p.N]; q1 = q[(size_t)(L + l) * p.N];
+          }
+        }
+        const int o = 4 * (l >> 1) + (l & 1);           // pair layout: (g0[2i], g0[2i+1], dg[2i], dg[2i+1])
+        sgd[o] = g0; sgd[o + 2] = g1 - g0;
+        sgq[o] = q0; sgq[o + 2] = q1 - q0;
+      }
       const float4 dl = *reinterpret_cast<const float4 *>(p.mix_recs + ((size_t)k * C + c) * kMixRecWords);
       const float *xr = p.xin + (size_t)c * p.xs + p.hist + t;
       const f32x2 x2 = delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
-      const bool obj = c < p.N;
-      const int ld = obj ? p.N : p.M;
-      const float *g = (obj ? p.g_dir + (size_t)k * L * ld + c : p.g_ds + (size_t)k * L * ld + (c - p.N));
+      __syncthreads();
 #pragma unroll
-      for (int l = 0; l < kMaxSpeakers; l++)
-        if (l < L) {
-          const float g0 = __ldg(g + (size_t)l * ld), g1 = __ldg(g + (size_t)(L + l) * ld);
-          acc[l] = fma2(splat2(fmaf(rg, g1 - g0, g0)), x2, acc[l]);
+      for (int j = 0; j < kMaxSpeakers / 2; j++) {
+        const float4 g = reinterpret_cast<const float4 *>(sgd)[j];
+        float ga, gb;
+        unpack2(fma2(rg2, pack2(g.z, g.w), pack2(g.x, g.y)), ga, gb);
+        acc[2 * j] = fma2(splat2(ga), x2, acc[2 * j]);
+        acc[2 * j + 1] = fma2(splat2(gb), x2, acc[2 * j + 1]);
+      }
+      if (dif) {
+        const f32x2 x0 = splat2(xr[0]);
+#pragma unroll
+        for (int j = 0; j < kMaxSpeakers / 2; j++) {
+          const float4 q = reinterpret_cast<const float4 *>(sgq)[j];
+          accQ[j] = fma2(fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0, accQ[j]);
         }
-      if (e >> 30 & 1u) {
-        const float x0 = xr[0];
-        const float *q = p.g_dif + (size_t)k * L * p.N + c;
-#pragma unroll
-        for (int l = 0; l < kMaxSpeakers; l++)
-          if (l < L) {
-            const float q0 = __ldg(q + (size_t)l * p.N), q1 = __ldg(q + (size_t)(L + l) * p.N);
-            accQ[l] = fmaf(fmaf(rg, q1 - q0, q0), x0, accQ[l]);
-          }
       }
     }
   }
@@ -820,11 +844,12 @@ __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
 #pragma unroll
   for (int l = 0; l < kMaxSpeakers; l++)
     if (l < L) {
-      float vL, vR;
+      float vL, vR, qa, qb;
       unpack2(acc[l], vL, vR);
+      unpack2(accQ[l >> 1], qa, qb);
       od[(size_t)(2 * l) * p.cs] += vL;
       od[(size_t)(2 * l + 1) * p.cs] += vR;
-      oq[(size_t)l * p.cs] += accQ[l];
+      oq[(size_t)l * p.cs] += (l & 1) ? qb : qa;
     }
 }
 

@@ -100,7 +100,8 @@ def test_static_scratch_variant_long_calls_match_the_oracle_and_allocate_nothing
             assert np.abs(want).max() > 0.05
             assert np.abs(got - want).max() <= 1e-5
         info = r.get_info()
-        assert info.cmac_items_last > 0 and info.cmac_splits_last <= r.info.cmac_splits   # the grouped kernel ran
+        if chunk_blocks == 0:   # one launch of 12 periods: the grouped kernel ran
+            assert info.cmac_items_last > 0 and info.cmac_splits_last <= r.info.cmac_splits
     ref_r.close()
 
 
