@@ -345,9 +345,83 @@ static int render_scene(const char *data_path, const char *in_path, const char *
   return 0;
 }
 
+// `test_host hoa_schedule <quaternions> <out> <count> <periods>` (no GPU): what the facade's HOA gain
+// calculation (HOASchedule = GainCalcHOA, gain_calc_hoa.cpp:86-124, with sh::rotation_matrix standing in
+// for quaternion_to_sh_rotation_matrix, sh_rotation.cpp:140-157) emits per period for a first-order SN3D
+// stream of 4 channels when listener i (orientation quaternion {w,x,y,z}, doubles) is set before period
+// i -- the scenario of the reference's head-tracked HOA golden (test_changes.py:183-217,263-281).
+// Writes [periods][16][4] floats.
+static int dump_hoa_schedule(const char *quat_path, const char *out_path, int count, int periods)
+{
+  std::vector<double> q(4 * (size_t)count);
+  FILE *f = std::fopen(quat_path, "rb");
+  if (!f || std::fread(q.data(), sizeof(double), q.size(), f) != q.size()) return 2;
+  std::fclose(f);
+  const size_t B = 512, fs = 48000, A = 16, H = 4;
+  HOASchedule sched(A, H);
+  HOAInput hi; hi.channels = {0, 1, 2, 3}; hi.orders = {0, 1, 1, 1}; hi.degrees = {0, -1, 0, 1}; hi.normalization = "SN3D";
+  hi.rtime = Time(0); hi.duration = Time(1);
+  sched.update(0, hi);
+  std::vector<float> out;
+  for (int k = 0; k < periods; k++) {
+    if (k < count) {
+      Listener l;
+      l.set_orientation_quaternion({q[4 * k], q[4 * k + 1], q[4 * k + 2], q[4 * k + 3]});
+      sched.set_orientation(l.orientation());
+    }
+    const auto &m = sched.matrix_at(Time((int64_t)((k + 1) * B), (int64_t)fs));
+    out.insert(out.end(), m.begin(), m.end());
+  }
+  f = std::fopen(out_path, "wb");
+  std::fwrite(out.data(), sizeof(float), out.size(), f);
+  std::fclose(f);
+  return 0;
+}
+
+// `test_host render_hoa <data file> <audio> <quaternions> <out> <count> <periods>`: the same scenario
+// through the whole Renderer facade on cuda:0 (add_hoa_block, set_listener before each period, process).
+static int render_hoa_head_tracked(const char *data_path, const char *in_path, const char *quat_path, const char *out_path,
+                                   int count, int periods)
+{
+  const size_t B = 512, H = 4;
+  std::vector<double> q(4 * (size_t)count);
+  FILE *f = std::fopen(quat_path, "rb");
+  if (!f || std::fread(q.data(), sizeof(double), q.size(), f) != q.size()) return 2;
+  std::fclose(f);
+  std::vector<float> in(H * B * periods), out(2 * B * periods);
+  f = std::fopen(in_path, "rb");
+  if (!f || std::fread(in.data(), sizeof(float), in.size(), f) != in.size()) return 2;
+  std::fclose(f);
+  Config cfg;
+  cfg.set_num_hoa_channels(H); cfg.set_period_size(B); cfg.set_data_path(data_path);
+  Renderer r(cfg);
+  HOAInput hi; hi.channels = {0, 1, 2, 3}; hi.orders = {0, 1, 1, 1}; hi.degrees = {0, -1, 0, 1}; hi.normalization = "SN3D";
+  hi.rtime = Time(0); hi.duration = Time(1);
+  if (!r.add_hoa_block(0, hi)) return 3;
+  for (int k = 0; k < periods; k++) {
+    if (k < count) {
+      Listener l;
+      l.set_orientation_quaternion({q[4 * k], q[4 * k + 1], q[4 * k + 2], q[4 * k + 3]});
+      r.set_listener(l);
+    }
+    const float *ip[H];
+    for (size_t c = 0; c < H; c++) ip[c] = in.data() + (c * periods + k) * B;
+    float *op[2] = {out.data() + (size_t)k * B, out.data() + (size_t)(periods + k) * B};
+    r.process(nullptr, nullptr, ip, op);
+  }
+  f = std::fopen(out_path, "wb");
+  std::fwrite(out.data(), sizeof(float), out.size(), f);
+  std::fclose(f);
+  return 0;
+}
+
 int main(int argc, char **argv)
 {
   if (argc >= 6 && std::string(argv[1]) == "render") return render_scene(argv[2], argv[3], argv[4], std::atoi(argv[5]));
+  if (argc >= 6 && std::string(argv[1]) == "hoa_schedule")
+    return dump_hoa_schedule(argv[2], argv[3], std::atoi(argv[4]), std::atoi(argv[5]));
+  if (argc >= 8 && std::string(argv[1]) == "render_hoa")
+    return render_hoa_head_tracked(argv[2], argv[3], argv[4], argv[5], std::atoi(argv[6]), std::atoi(argv[7]));
   test_time();
   test_config();
   test_listener_axes();

@@ -9,12 +9,13 @@ eight periods -- where gains ramp up from zero and delays ramp from their defaul
 seen by that fit, so matching them pins the reference's ramp and delay-line conventions; the
 reference's own tolerance for these files is atol 1e-4, the bar here is 2e-5."""
 import json
+import subprocess
 
 import numpy as np
 import pytest
 
 from bear_b200 import control, data_file, tensorfile
-from conftest import GOLDEN
+from conftest import GOLDEN, ROOT
 
 B, NBLK = 512, 93
 N = B * NBLK
@@ -108,4 +109,148 @@ def test_cuda_path_reproduces_reference_golden(replay_data, name, mode):
                 s = slice(k * B, (k + 1) * B)
                 out[:, s] = r.process(obj[:, s] if Nn else None, ds[:, s] if M else None, hoa[:, s] if H else None,
                                       tb.block(k))
+    np.testing.assert_allclose(out, golden, atol=ATOL, rtol=0)
+
+
+# ---------------------------------------------------------------------------------------------------
+# head_track_hoa_out.npy: the one head-tracked golden that needs nothing of default.tf beyond what the
+# fixture carries (HOA decoder, hoa delay).  100 listeners are pushed, one before each period
+# (test_changes.py:183-217 get_listeners, :168-176 listener_pre_block_cb); the HOA path reacts to the
+# listener through the SH rotation of the decode-input matrix (gain_calc_hoa.cpp:86-124), which the DSP
+# ramps over the period (dsp.cpp:178-180).  The per-period matrices are NOT computed here: they come
+# from include/bear_b200/host.hpp (HOASchedule + sh::rotation_matrix + Listener), so this replay pins
+# the facade's quaternion / axis conventions, its rotation by projection, the listener timing and the
+# ramped hoa_matrix against the reference with no free parameter (left ear).  The right ear rests on the
+# left/right mirror symmetry of default.tf's decoder, as in the static replay above.
+# ---------------------------------------------------------------------------------------------------
+def _quat_mul(a, b):
+    w1, x1, y1, z1 = a.T
+    w2, x2, y2, z2 = b.T
+    return np.stack([w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                     w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2], 1)
+
+
+def _from_rotation_vector(v):
+    ang = np.linalg.norm(v, axis=1)
+    axis = v / np.where(ang > 0, ang, 1.0)[:, None]
+    return np.concatenate([np.cos(ang / 2)[:, None], np.sin(ang / 2)[:, None] * axis], 1)
+
+
+def reference_listener_quaternions():
+    """orientation_quaternion of get_listeners(), test_changes.py:183-217 ({w, x, y, z})."""
+    t = np.arange(100) * (512 / 48000)
+    z = np.zeros_like(t)
+    q_lr = _from_rotation_vector(np.stack([z, z, t * 7], 1))
+    q_ss = _from_rotation_vector(np.stack([z, np.radians(15 * np.sin(t * 3.5)), z], 1))
+    q_ud = _from_rotation_vector(np.stack([np.radians(15 * np.sin(t * 6.5)), z, z], 1))
+    return _quat_mul(_quat_mul(q_lr, q_ss), q_ud)
+
+
+@pytest.fixture(scope="module")
+def test_host_exe(tmp_path_factory):
+    exe = tmp_path_factory.mktemp("cxx") / "test_host"
+    lib_dir = ROOT / "bear_b200"
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-pthread", "-I", str(ROOT / "include"),
+                           str(ROOT / "tests" / "cxx" / "test_host.cpp"), "-o", str(exe), "-L", str(lib_dir),
+                           "-lbear_cuda", "-Wl,-rpath," + str(lib_dir)])
+    return str(exe)
+
+
+@pytest.fixture(scope="module")
+def head_tracked_hoa(test_host_exe, tmp_path_factory):
+    """(hoa_gains [NBLK, 16, 4] from host.hpp, audio [4, N], golden [2, N], quaternion file)"""
+    d = tmp_path_factory.mktemp("ht")
+    q = reference_listener_quaternions()
+    (d / "q.bin").write_bytes(np.ascontiguousarray(q, np.float64).tobytes())
+    subprocess.check_call([test_host_exe, "hoa_schedule", str(d / "q.bin"), str(d / "g.bin"), "100", str(NBLK)])
+    gains = np.frombuffer((d / "g.bin").read_bytes(), np.float32).reshape(NBLK, 16, 4)
+    x = np.roll(np.load(GOLDEN / "input.npy"), 3000, axis=1)[:, :N]
+    audio = np.concatenate([x, 0 * x, 0 * x, x]).astype(np.float32)
+    golden = np.load(GOLDEN / "head_track_hoa_out.npy")[:, :N]
+    return gains, audio, golden, str(d / "q.bin")
+
+
+def test_facade_hoa_matrix_is_the_first_order_rotation(head_tracked_hoa):
+    """host.hpp's matrices against the closed form for first order (sh_rotation.cpp:6-26: the ACN 1..3
+    block is the re-ordered transpose of the quaternion's rotation matrix), entries below 1e-5 zeroed
+    (sh_rotation.cpp:132-136)."""
+    gains = head_tracked_hoa[0]
+    q = reference_listener_quaternions()[:NBLK]
+    w, x, y, z = q.T
+    R = np.empty((NBLK, 3, 3))   # rotation matrix of the unit quaternion
+    R[:, 0] = np.stack([1 - 2 * (y * y + z * z), 2 * (x * y - z * w), 2 * (x * z + y * w)], 1)
+    R[:, 1] = np.stack([2 * (x * y + z * w), 1 - 2 * (x * x + z * z), 2 * (y * z - x * w)], 1)
+    R[:, 2] = np.stack([2 * (x * z - y * w), 2 * (y * z + x * w), 1 - 2 * (x * x + y * y)], 1)
+    a = R.transpose(0, 2, 1)     # adm_matrix = toRotationMatrix().transpose()
+    want = np.zeros((NBLK, 16, 4))
+    want[:, 0, 0] = 1
+    blk = np.empty((NBLK, 3, 3))
+    blk[:, 0] = np.stack([a[:, 0, 0], -a[:, 2, 0], -a[:, 1, 0]], 1)
+    blk[:, 1] = np.stack([-a[:, 0, 2], a[:, 2, 2], a[:, 1, 2]], 1)
+    blk[:, 2] = np.stack([-a[:, 0, 1], a[:, 2, 1], a[:, 1, 1]], 1)
+    want[:, 1:4, 1:4] = blk
+    want[np.abs(want) < 1e-5] = 0
+    np.testing.assert_allclose(gains, want, atol=2e-7)
+
+
+@pytest.mark.parametrize("ears", ["left", "both"])
+def test_oracle_reproduces_head_tracked_hoa_golden(oracle, replay_data, head_tracked_hoa, ears):
+    gains, audio, golden, _ = head_tracked_hoa
+    ctl = control.HostControl(replay_data)
+    tb = ctl.tables(NBLK, hoa_gains=gains, H=4)
+    none = np.zeros((0, N), np.float32)
+    out = oracle.RefRenderer(replay_data, 0, 0, 4, B).render(none, none, audio, tb.blocks())
+    assert np.abs(golden).max() > 0.1 and np.abs(golden[0] - golden[1]).max() > 0.01   # the head really turns
+    sel = slice(0, 1) if ears == "left" else slice(0, 2)
+    np.testing.assert_allclose(out[sel], golden[sel], atol=ATOL, rtol=0)
+
+
+def test_head_tracked_hoa_golden_has_teeth(oracle, replay_data, head_tracked_hoa):
+    """Without the rotation, with the conjugate orientation, or with the matrix applied one period late,
+    the replay misses the golden by far more than the bar."""
+    gains, audio, golden, _ = head_tracked_hoa
+    ctl = control.HostControl(replay_data)
+    none = np.zeros((0, N), np.float32)
+    static = np.broadcast_to(np.eye(16, 4, dtype=np.float32), gains.shape)
+    late = np.concatenate([gains[:1], gains[:-1]])
+    mirrored = gains * np.where(np.arange(16) == 1, -1.0, 1.0)[None, :, None]    # yaw the other way round
+    for wrong in (static, late, mirrored):
+        tb = ctl.tables(NBLK, hoa_gains=np.ascontiguousarray(wrong, dtype=np.float32), H=4)
+        out = oracle.RefRenderer(replay_data, 0, 0, 4, B).render(none, none, audio, tb.blocks())
+        assert np.abs(out[0] - golden[0]).max() > 50 * ATOL
+
+
+@pytest.mark.gpu
+def test_cuda_facade_reproduces_head_tracked_hoa_golden(replay_data, head_tracked_hoa, test_host_exe, tmp_path):
+    """The whole C++ Renderer facade on the GPU: add_hoa_block, set_listener before each period, process."""
+    gains, audio, golden, qfile = head_tracked_hoa
+    fx = tensorfile.read(GOLDEN / "unity_brirs_decorrelators.tf")
+    tree = {"views": np.array(fx["views"][:1]), "brirs": replay_data.brirs, "delays": np.array(fx["delays"][:1]),
+            "fs": 48000.0, "layout": fx["layout"], "decorrelation_filters": np.array(fx["decorrelation_filters"]),
+            "decorrelation_delay": fx["decorrelation_delay"], "front_loudspeaker": fx["front_loudspeaker"],
+            "hoa": {"irs": replay_data.hoa_irs, "delay": fx["hoa"]["delay"]}}
+    tensorfile.write(tmp_path / "replay.tf", tree)
+    (tmp_path / "in.bin").write_bytes(audio.tobytes())
+    r = subprocess.run([test_host_exe, "render_hoa", str(tmp_path / "replay.tf"), str(tmp_path / "in.bin"), qfile,
+                        str(tmp_path / "out.bin"), "100", str(NBLK)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    out = np.frombuffer((tmp_path / "out.bin").read_bytes(), np.float32).reshape(2, N)
+    np.testing.assert_allclose(out, golden, atol=ATOL, rtol=0)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["stream", "batch"])
+def test_cuda_path_reproduces_head_tracked_hoa_golden(replay_data, head_tracked_hoa, mode):
+    from bear_b200.renderer import Renderer
+    gains, audio, golden, _ = head_tracked_hoa
+    tb = control.HostControl(replay_data).tables(NBLK, hoa_gains=gains, H=4)
+    if mode == "batch":
+        with Renderer(replay_data, 0, 0, 4, B, max_batch_blocks=NBLK) as r:
+            out = r.process_batch(None, None, audio, tb)
+    else:
+        out = np.zeros((2, N), np.float32)
+        with Renderer(replay_data, 0, 0, 4, B) as r:
+            for k in range(NBLK):
+                s = slice(k * B, (k + 1) * B)
+                out[:, s] = r.process(None, None, audio[:, s], tb.block(k))
     np.testing.assert_allclose(out, golden, atol=ATOL, rtol=0)
