@@ -180,7 +180,9 @@ File::File(const std::string &path)
   if (std::memcmp(bytes_.data(), "TENF", 4) != 0) throw FormatError("magic number not found");
   if (read_le(bytes_.data() + 4, 4) != 0) throw FormatError("unknown version number");
   uint64_t dlen = read_le(bytes_.data() + 8, 8), jlen = read_le(bytes_.data() + 16, 8);
-  if (bytes_.size() < header + dlen + jlen) throw FormatError("file not long enough");
+  // (compared by subtraction: the sum of two untrusted 64-bit lengths can wrap)
+  const uint64_t room = bytes_.size() - header;
+  if (dlen > room || jlen > room - dlen) throw FormatError("file not long enough");
   if (jlen == 0) throw FormatError("no JSON metadata found");
   meta_ = parse_json(reinterpret_cast<const char *>(bytes_.data()) + header + dlen, jlen);
 }
@@ -201,16 +203,24 @@ static double load_as_double(const unsigned char *p, bool swap)
 FloatTensor File::unpack_f32(const Json &v) const
 {
   if (!v.is_tensor() || v.at("_tenf_type").str != "array") throw FormatError("unknown type");
+  // shape, strides and base come from the file: non-negative integers that fit the file, or a format
+  // error (a negative or huge double converted to size_t would be undefined behaviour)
+  auto index_field = [&](const Json &j, const char *what) {
+    const double d = j.num;
+    if (j.kind != Json::Number || !(d >= 0.0) || d != std::floor(d) || d > 9007199254740992.0)
+      throw FormatError(std::string(what) + " must be a non-negative integer");
+    return (size_t)d;
+  };
   std::vector<size_t> shape, strides;
-  for (auto &s : v.at("shape").arr) shape.push_back((size_t)s.num);
-  for (auto &s : v.at("strides").arr) strides.push_back((size_t)s.num);
+  for (auto &s : v.at("shape").arr) shape.push_back(index_field(s, "shape"));
+  for (auto &s : v.at("strides").arr) strides.push_back(index_field(s, "strides"));
   if (shape.size() != strides.size()) throw FormatError("mismatched strides and shape");
   const std::string dtype = v.at("dtype").str;
   if (dtype.size() < 3) throw FormatError("unknown byte order");
   const char order = dtype[0];
   if (order != '<' && order != '>' && order != '|') throw FormatError("unknown byte order");
   const std::string type = dtype.substr(1);
-  const size_t base = (size_t)v.at("base").num;
+  const size_t base = index_field(v.at("base"), "base");
 
   size_t item = 0;
   double (*load)(const unsigned char *, bool) = nullptr;
@@ -229,12 +239,20 @@ FloatTensor File::unpack_f32(const Json &v) const
     if (s % item) throw FormatError("stride is not a multiple of the type size");
 
   const bool swap = order == '>';  // hosts running CUDA are little endian
+  // element count and byte span with overflow checks: neither can exceed the file (every element of a
+  // non-degenerate array occupies bytes of it; zero strides are allowed, so the count is bounded separately)
+  const size_t fsize = bytes_.size();
   size_t total = 1, span = item;
   for (size_t i = 0; i < shape.size(); i++) {
+    if (shape[i] && total > (size_t)1 << 40) throw FormatError("array too large");
     total *= shape[i];
-    if (shape[i]) span += strides[i] * (shape[i] - 1);
+    if (shape[i] > 1) {
+      if (strides[i] && shape[i] - 1 > (fsize - std::min(fsize, span)) / strides[i]) throw FormatError("file not long enough");
+      span += strides[i] * (shape[i] - 1);
+    }
   }
-  if (total && base + span > bytes_.size()) throw FormatError("file not long enough");
+  if (total > (size_t)1 << 40) throw FormatError("array too large");
+  if (total && (base > fsize || span > fsize - base)) throw FormatError("file not long enough");
 
   FloatTensor out;
   out.shape = shape;

@@ -57,3 +57,40 @@ def test_format_errors(tmp_path, mutate, msg):
         tensorfile.read(p)
     with pytest.raises(renderer.BearCudaError, match="tensorfile format error: " + msg):
         renderer.tenf_read_f32(p, "multi_dim/float32")
+
+
+def _with_json(good, edit):
+    """The fixture with its trailing JSON metadata edited (header lengths updated)."""
+    import json
+    import struct
+    dlen, jlen = struct.unpack("<QQ", good[8:24])
+    meta = json.loads(good[24 + dlen:24 + dlen + jlen])
+    edit(meta["multi_dim"]["float32"])
+    mb = json.dumps(meta).encode()
+    return good[:16] + struct.pack("<Q", len(mb)) + good[24:24 + dlen] + mb
+
+
+@pytest.mark.parametrize("edit", [
+    lambda t: t.__setitem__("shape", [-1, 4, 8]),
+    lambda t: t.__setitem__("shape", [2.5, 4, 8]),
+    lambda t: t.__setitem__("shape", [2 ** 40, 2 ** 40, 8]),
+    lambda t: t.__setitem__("strides", [2 ** 62, 32, 4]),
+    lambda t: t.__setitem__("strides", [-128, 32, 4]),
+    lambda t: t.__setitem__("base", 2 ** 63),
+    lambda t: t.__setitem__("base", -8),
+], ids=["negative", "fractional", "huge-count", "huge-stride", "negative-stride", "huge-base", "negative-base"])
+def test_crafted_size_fields_are_format_errors_in_the_cxx_reader(tmp_path, edit):
+    """Untrusted shape / strides / base: a format error, never a wrapped size or an out-of-bounds read."""
+    p = tmp_path / "crafted.tenf"
+    p.write_bytes(_with_json((GOLDEN / "tensorfile_le_1.tenf").read_bytes(), edit))
+    with pytest.raises(renderer.BearCudaError, match="tensorfile format error"):
+        renderer.tenf_read_f32(p, "multi_dim/float32")
+
+
+def test_crafted_header_lengths_do_not_wrap(tmp_path):
+    import struct
+    good = (GOLDEN / "tensorfile_le_1.tenf").read_bytes()
+    p = tmp_path / "wrap.tenf"
+    p.write_bytes(good[:8] + struct.pack("<QQ", 2 ** 64 - 8, 16) + good[24:])   # data + JSON lengths sum to 8 mod 2^64
+    with pytest.raises(renderer.BearCudaError, match="file not long enough"):
+        renderer.tenf_read_f32(p, "multi_dim/float32")
