@@ -393,11 +393,14 @@ __device__ __forceinline__ f32x2 delayed_read2(const float *__restrict__ xa, flo
   const float fa = ua - 8388608.0f, fb = ub - 8388608.0f;
   const int ia = __float_as_int(ua) - 0x4B000000, ib = __float_as_int(ub) - 0x4B000000;
   const f32x2 s = add2(splat2(1.5f), sub2(d, pack2(fa, fb)));
+  // c0 = -(s-1)(s-2)(s-3)/6, c1 = s(s-2)(s-3)/2, c2 = -s(s-1)(s-3)/2, c3 = s(s-1)(s-2)/6 with the shared
+  // factors a = s(s-3) and b = (s-1)(s-2) taken out: 10 packed operations for the eight coefficients
   const f32x2 s1 = add2(s, splat2(-1.0f)), s2 = add2(s, splat2(-2.0f)), s3 = add2(s, splat2(-3.0f));
-  const f32x2 c0 = mul2(mul2(mul2(s1, s2), s3), splat2(-1.0f / 6.0f));
-  const f32x2 c1 = mul2(mul2(mul2(s, s2), s3), splat2(0.5f));
-  const f32x2 c2 = mul2(mul2(mul2(s, s1), s3), splat2(-0.5f));
-  const f32x2 c3 = mul2(mul2(mul2(s, s1), s2), splat2(1.0f / 6.0f));
+  const f32x2 a = mul2(s, s3), b = mul2(s1, s2);
+  const f32x2 c0 = mul2(b, mul2(s3, splat2(-1.0f / 6.0f)));
+  const f32x2 c1 = mul2(a, mul2(s2, splat2(0.5f)));
+  const f32x2 c2 = mul2(a, mul2(s1, splat2(-0.5f)));
+  const f32x2 c3 = mul2(b, mul2(s, splat2(1.0f / 6.0f)));
   const float *qa = xa - ia, *qb = xb - ib;
   f32x2 acc = mul2(c0, pack2(qa[0], qb[0]));
   acc = fma2(c1, pack2(qa[-1], qb[-1]), acc);
@@ -492,11 +495,22 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
   const float *gd = (obj ? p.g_dir : p.g_ds) + (size_t)k * L * ld + ci;   // [slot k: L rows][slot k+1: L rows]
   const float *gq = p.g_dif + (size_t)k * L * ld + ci;
   unsigned mask = 0u, any_q = 0u;
-  for (int l = 0; l < L; l++) {
-    const bool nzd = gd[(size_t)l * ld] != 0.f || gd[(size_t)(L + l) * ld] != 0.f;
-    const bool nzq = obj && (gq[(size_t)l * ld] != 0.f || gq[(size_t)(L + l) * ld] != 0.f);
-    if (nzd || nzq) mask |= 1u << l;
-    if (nzq) any_q = 1u;
+  for (int l0 = 0; l0 < L; l0 += 8) {   // eight loudspeakers' table entries are loaded before any is tested
+    float va[8], vb[8], qa[8], qb[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      const int l = min(l0 + i, L - 1);
+      va[i] = gd[(size_t)l * ld]; vb[i] = gd[(size_t)(L + l) * ld];
+      qa[i] = obj ? gq[(size_t)l * ld] : 0.f; qb[i] = obj ? gq[(size_t)(L + l) * ld] : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+      if (l0 + i < L) {
+        const bool nzq = qa[i] != 0.f || qb[i] != 0.f;
+        if (va[i] != 0.f || vb[i] != 0.f || nzq) mask |= 1u << (l0 + i);
+        if (nzq) any_q = 1u;
+      }
+    }
   }
   const int ns = __popc(mask);
   unsigned *keys = p.mix_keys + (size_t)k * C;
@@ -597,20 +611,26 @@ __device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
 //   cdir[2l+e][t] += g_c,l(t) * D[x_c, tau_c,e(t)](t)      (per_ear_delay.cpp:22-56)
 //   qdif[l][t]    += q_c,l(t) * x_c(t)                     (dsp.cpp:127-129)
 // grid: (periods * B / kMixTile, S); block: kMixTile; one output sample per thread.  The CTA zeroes
-// its tile of the 3L rows, then walks its channels in sorted order in chunks of kMixChunk: warp 0
-// reads the chunk's order entries and requests, per channel, the input row (history + tile) and the
-// record by bulk copies (TMA, 1-D) on an mbarrier, double buffered, so the copies of chunk i+1 run
-// under the arithmetic of chunk i.  Per channel: two Lagrange-3 reads at the ramped per-ear delays,
-// then per slot pair one packed gain ramp and two FFMA2 into the (left, right) slot accumulators.
+// its tile of the 3L rows, then walks its channels in sorted order in chunks of kMixChunk through a
+// ring of kMixStages shared-memory stages: warp 0 reads a chunk's order entries and requests, per
+// channel, the input row (history + tile) and the record by bulk copies (TMA, 1-D) that complete on
+// the stage's "full" mbarrier, two chunks ahead of the arithmetic; a warp that is done with a stage
+// arrives on its "empty" mbarrier, which is all warp 0 waits for before it refills the stage -- there
+// is no CTA-wide barrier in the loop, the warps drift apart by up to a chunk.  Per channel: two
+// Lagrange-3 reads at the ramped per-ear delays (the next channel's are computed before this channel's
+// sums, for instruction-level parallelism), then per slot pair one packed gain ramp and two FFMA2 into
+// the (left, right) slot accumulators.
 // ----------------------------------------------------------------------------------------------
+constexpr int kMixStages = 3;
+
 __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
 {
   extern __shared__ __align__(16) float smx[];
   const int XW = p.hist + kMixTile;
-  float *const xt0 = smx;                                    // [2][kMixChunk][XW] input rows
-  float *const rc0 = smx + 2 * kMixChunk * XW;               // [2][kMixChunk][kMixRecWords] records
-  __shared__ __align__(8) unsigned long long bars[2];
-  __shared__ unsigned sord[2][kMixChunk];                    // order entries of the staged chunks
+  float *const xt0 = smx;                                             // [stages][kMixChunk][XW] input rows
+  float *const rc0 = smx + kMixStages * kMixChunk * XW;               // [stages][kMixChunk][kMixRecWords] records
+  __shared__ __align__(8) unsigned long long bars[2 * kMixStages];    // full[stage], empty[stage]
+  __shared__ unsigned sord[kMixStages][kMixChunk];                    // order entries of the staged chunks
   const int tid = threadIdx.x;
   const int t = p.k0 * p.B + blockIdx.x * kMixTile + tid;
   const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
@@ -672,24 +692,32 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
 
   const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
   if (tid == 0) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0) : "memory");
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8) : "memory");
+#pragma unroll
+    for (int i = 0; i < kMixStages; i++) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * i) : "memory");                       // full
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar0 + 8 * (kMixStages + i)), "r"(kMixTile / 32) : "memory");  // empty
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
   const int nchunks = (nlisted + kMixChunk - 1) / kMixChunk;
   const unsigned *order = p.mix_order + (size_t)k * C + c0;
-  // warp 0 requests chunk ci: lane i reads the i-th order entry and requests that channel's input row
-  // and record (the diffuse half of a record only when the channel has diffuse gains)
+  unsigned e_pref = (tid < min(kMixChunk, nlisted)) ? order[tid] : 0u;   // warp 0: order entry of the chunk to request next
+  // warp 0 requests chunk ci into stage ci % kMixStages: lane i takes the i-th order entry and requests
+  // that channel's input row and record (the diffuse half of a record only when the channel has diffuse gains)
   auto request = [&](int ci) {
-    const int i0 = ci * kMixChunk, cnt = min(kMixChunk, nlisted - i0), st = ci & 1;
+    const int i0 = ci * kMixChunk, cnt = min(kMixChunk, nlisted - i0), st = ci % kMixStages;
     const unsigned bar = bar0 + 8 * st;
-    unsigned e = 0u, bytes = 0u;
+    if (ci >= kMixStages)   // every warp is done with the chunk that used this stage before
+      mbar_wait(bar0 + 8 * (kMixStages + st), (unsigned)(ci / kMixStages - 1) & 1u);
+    const unsigned e = e_pref;
+    unsigned bytes = 0u;
     if (tid < cnt) {
-      e = order[i0 + tid];
       sord[st][tid] = e;
       bytes = (unsigned)XW * 4u + ((e >> 30 & 1u) ? kMixRecWords * 4u : (kMixRecWords - kMixSlots * 2) * 4u);
     }
+    const int inext = i0 + kMixChunk + tid;
+    e_pref = (tid < kMixChunk && inext < nlisted) ? order[inext] : 0u;
     unsigned total = bytes;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
@@ -709,59 +737,55 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
                    ::"r"(rdst), "l"(rsrc), "r"(bytes - (unsigned)XW * 4u), "r"(bar) : "memory");
     }
   };
-  if (tid < 32 && nchunks > 0) request(0);
-  __syncthreads();
+  if (tid < 32) {
+    if (nchunks > 0) request(0);
+    if (nchunks > 1) request(1);
+  }
+  auto lagrange = [&](const float *rec, const float *xr) {
+    const float4 dl = *reinterpret_cast<const float4 *>(rec);
+    return delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
+  };
   for (int ci = 0; ci < nchunks; ci++) {
-    const int st = ci & 1;
-    if (tid < 32 && ci + 1 < nchunks) request(ci + 1);   // its buffer was released by the barrier below
-    mbar_wait(bar0 + 8 * st, (ci >> 1) & 1);
+    const int st = ci % kMixStages;
+    if (tid < 32 && ci + 2 < nchunks) request(ci + 2);
+    mbar_wait(bar0 + 8 * st, (unsigned)(ci / kMixStages) & 1u);
     const int cnt = min(kMixChunk, nlisted - ci * kMixChunk);
-    const float *xrow = xt0 + st * kMixChunk * XW + p.hist + tid;
-    const float *recs = rc0 + st * kMixChunk * kMixRecWords;
-    // channels two at a time: both channels' delayed reads are issued before either's accumulation
-    constexpr int UC = 2;
-    for (int j0 = 0; j0 < cnt; j0 += UC) {
-      f32x2 x2[UC];
-#pragma unroll
-      for (int u = 0; u < UC; u++) {
-        const int j = min(j0 + u, cnt - 1);
-        const float4 dl = *reinterpret_cast<const float4 *>(recs + j * kMixRecWords);
-        const float *xr = xrow + j * XW;
-        x2[u] = delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
+    const float *xr = xt0 + st * kMixChunk * XW + p.hist + tid;
+    const float *rec = rc0 + st * kMixChunk * kMixRecWords;
+    f32x2 x2n = lagrange(rec, xr);
+    for (int j = 0; j < cnt; j++, rec += kMixRecWords, xr += XW) {
+      const f32x2 x2 = x2n;
+      if (j + 1 < cnt) x2n = lagrange(rec + kMixRecWords, xr + XW);   // the next channel's reads, ahead of this one's sums
+      const float4 *r4 = reinterpret_cast<const float4 *>(rec);
+      const unsigned e = sord[st][j];
+      if (e >> 31) {   // a new loudspeaker set: close the run, take the slot map of this one
+        flush();
+        const uint4 meta = *reinterpret_cast<const uint4 *>(r4 + 1);
+        nact = meta.x & 0xffu; spk_lo = meta.y; spk_hi = meta.z;
       }
 #pragma unroll
-      for (int u = 0; u < UC; u++) {
-        const int j = j0 + u;
-        if (j >= cnt) break;
-        const float4 *rec = reinterpret_cast<const float4 *>(recs + j * kMixRecWords);
-        const unsigned e = sord[st][j];
-        if (e >> 31) {   // a new loudspeaker set: close the run, take the slot map of this one
-          flush();
-          const uint4 meta = *reinterpret_cast<const uint4 *>(rec + 1);
-          nact = meta.x & 0xffu; spk_lo = meta.y; spk_hi = meta.z;
-        }
+      for (int i = 0; i < kMixSlots / 2; i++) {
+        if (i == kMixSlots / 4 && nact <= (unsigned)kMixSlots / 2) break;   // upper half of the slots unused
+        const float4 g = r4[2 + i];
+        float ga, gb;
+        unpack2(fma2(rg2, pack2(g.z, g.w), pack2(g.x, g.y)), ga, gb);
+        acc[2 * i] = fma2(splat2(ga), x2, acc[2 * i]);
+        acc[2 * i + 1] = fma2(splat2(gb), x2, acc[2 * i + 1]);
+      }
+      if (e >> 30 & 1u) {
+        const f32x2 x0 = splat2(xr[0]);
+        qdirty = true;
 #pragma unroll
         for (int i = 0; i < kMixSlots / 2; i++) {
-          if (i == kMixSlots / 4 && nact <= (unsigned)kMixSlots / 2) break;   // upper half of the slots unused
-          const float4 g = rec[2 + i];
-          float ga, gb;
-          unpack2(fma2(rg2, pack2(g.z, g.w), pack2(g.x, g.y)), ga, gb);
-          acc[2 * i] = fma2(splat2(ga), x2[u], acc[2 * i]);
-          acc[2 * i + 1] = fma2(splat2(gb), x2[u], acc[2 * i + 1]);
-        }
-        if (e >> 30 & 1u) {
-          const f32x2 x0 = splat2(xrow[j * XW]);
-          qdirty = true;
-#pragma unroll
-          for (int i = 0; i < kMixSlots / 2; i++) {
-            if (i == kMixSlots / 4 && nact <= (unsigned)kMixSlots / 2) break;
-            const float4 q = rec[2 + kMixSlots / 2 + i];
-            accQ[i] = fma2(fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0, accQ[i]);
-          }
+          if (i == kMixSlots / 4 && nact <= (unsigned)kMixSlots / 2) break;
+          const float4 q = r4[2 + kMixSlots / 2 + i];
+          accQ[i] = fma2(fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0, accQ[i]);
         }
       }
     }
-    __syncthreads();   // every thread is done with buffer st before warp 0 requests chunk ci + 2 into it
+    __syncwarp();
+    if ((tid & 31) == 0)   // this warp is done with stage st
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar0 + 8 * (kMixStages + st)) : "memory");
   }
   flush();
 }
@@ -1968,7 +1992,7 @@ cudaError_t static_scratch_pointer(float2 **out)
   return cudaSuccess;
 }
 
-size_t mix_smem_bytes(int hist) { return (size_t)2 * kMixChunk * (hist + kMixTile + kMixRecWords) * sizeof(float); }
+size_t mix_smem_bytes(int hist) { return (size_t)kMixStages * kMixChunk * (hist + kMixTile + kMixRecWords) * sizeof(float); }
 
 static int ilog2(int v)
 {
