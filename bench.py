@@ -174,6 +174,7 @@ _W = {}
 def _cpu_worker_init(workload, T, num_views):
     sys.path.insert(0, str(ROOT))
     from oracle import bear_ref
+    bear_ref.use_native_build()
     B, N, _, scale, _ = WORKLOADS[workload]
     data, ctl = data_and_control(num_views)
     tb = scene_tables(ctl, T, B, 0, N, num_views=num_views)
@@ -194,11 +195,9 @@ def cpu_sample_blocks(args):
 
 
 def oracle_build():
-    try:
-        flags = [l for l in (ROOT / "oracle" / "Makefile").read_text().splitlines() if l.startswith("CXXFLAGS")]
-        return "oracle/bear_ref.cpp f32, own FFT, " + (flags[0].split("=", 1)[1].strip() if flags else "")
-    except OSError:
-        return "oracle/bear_ref.cpp f32"
+    """The timed CPU legs use a build of the oracle for this machine (-O3 -march=native)."""
+    from oracle import bear_ref
+    return "oracle/bear_ref.cpp f32 (own radix-2 FFT; g++ %s)" % bear_ref.use_native_build()
 
 
 def cpu_baseline_single(args):
@@ -253,6 +252,7 @@ def run_reference(args, rank):
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else os.cpu_count()
     T = cpu_sample_blocks(args)
     B, N, scaling, _, _ = WORKLOADS[args.workload]
+    build = oracle_build()   # compiled once here; the forked workers inherit the choice
     ctx = mp.get_context("fork")
     with ctx.Pool(cores, initializer=_cpu_worker_init, initargs=(args.workload, T, min(180, T))) as pool:
         for _ in range(max(1, args.warmup)):
@@ -270,7 +270,7 @@ def run_reference(args, rank):
         "config": workload_config(args, T, 1, cores),
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
                          "sample": "%d instances x %d periods of %d (%d objects each) per step, %s (the reference "
-                                   "renderer needs VISR+Boost: unbuildable here)" % (cores, T, B, N, oracle_build())},
+                                   "renderer needs VISR+Boost: unbuildable here)" % (cores, T, B, N, build)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
         "libear_convolver_anchor": libear_convolver_anchor(),

@@ -31,11 +31,35 @@ def build():
 
 
 _libs = {}
+_native = {"flags": None}
+
+
+def use_native_build():
+    """For the timed CPU baseline (bench.py) only: rebuild the f32 oracle for THIS machine
+    (-O3 -march=native, what BASELINE.md section 3 asks for) into oracle/_native/ and make lib("f32")
+    use it.  Returns the compiler flags in use; falls back to the shipped -march=x86-64-v3 build when no
+    compiler is around.  Parity tests never call this: they run the shipped build."""
+    if _native["flags"] is None:
+        flags = "-O3 -march=native -std=c++17 -fPIC -shared"
+        out = HERE / "_native" / "libbear_ref_f32.so"
+        try:
+            out.parent.mkdir(exist_ok=True)
+            subprocess.check_call(["g++"] + flags.split() + ["-DREAL=float", "-o", str(out), str(HERE / "bear_ref.cpp")],
+                                  stderr=subprocess.DEVNULL)
+            _native["path"] = out
+            _native["flags"] = flags
+            _libs.pop("f32", None)
+        except (OSError, subprocess.CalledProcessError):
+            _native["flags"] = "shipped build (-O3 -march=x86-64-v3)"
+    return _native["flags"]
+
 
 
 def lib(precision="f32"):
     if precision not in _libs:
         path = HERE / ("libbear_ref_%s.so" % precision)
+        if precision == "f32" and _native.get("path"):
+            path = _native["path"]
         if not path.exists():
             build()
         l = C.CDLL(str(path))
