@@ -332,6 +332,11 @@ __device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c)
   asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
   return d;
 }
+// acc += a * b with the accumulator tied to one register (no copy for the compiler to place)
+__device__ __forceinline__ void fma2_acc(f32x2 &acc, f32x2 a, f32x2 b)
+{
+  asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(acc) : "l"(a), "l"(b));
+}
 __device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b)
 {
   f32x2 d;
@@ -391,7 +396,7 @@ __device__ __forceinline__ f32x2 delayed_read2(const float *__restrict__ xa, flo
   // is exactly 2^23 + floor(h); its low mantissa bits are the integer, subtracting 2^23 back the float
   const float ua = __fadd_rd(ha, 8388608.0f), ub = __fadd_rd(hb, 8388608.0f);
   const float fa = ua - 8388608.0f, fb = ub - 8388608.0f;
-  const int ia = __float_as_int(ua) - 0x4B000000, ib = __float_as_int(ub) - 0x4B000000;
+  const int ia = __float_as_int(ua) & 0x7fffff, ib = __float_as_int(ub) & 0x7fffff;
   const f32x2 s = add2(splat2(1.5f), sub2(d, pack2(fa, fb)));
   // c0 = -(s-1)(s-2)(s-3)/6, c1 = s(s-2)(s-3)/2, c2 = -s(s-1)(s-3)/2, c3 = s(s-1)(s-2)/6 with the shared
   // factors a = s(s-3) and b = (s-1)(s-2) taken out: 10 packed operations for the eight coefficients
@@ -464,11 +469,11 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 // ----------------------------------------------------------------------------------------------
 
 // mix_prep_kernel: the record and the sort key of every (period, channel).
-// Record (kMixRecWords = 40 words):
+// Record (kMixRecWords = 8 + 4 kMixSlots words):
 //   [0..3]   per-ear delay ramp in samples: d0L, ddL, d0R, ddR (validated, then clamped to the history)
-//   [4]      number of slots | has_diffuse << 8        [5], [6] loudspeaker of slots 0..3, 4..7 (bytes)
-//   [8..23]  direct gains, slot pairs:  (g0[2i], g0[2i+1], dg[2i], dg[2i+1]),  i = 0..3
-//   [24..39] diffuse gains, same layout (objects only)
+//   [4]      number of slots | has_diffuse << 8        [5], [6] loudspeaker of slots 0..3, 4.. (bytes)
+//   [8..]    direct gains, slot pairs:  (g0[2i], g0[2i+1], dg[2i], dg[2i+1]),  i = 0 .. kMixSlots/2 - 1
+//   then     diffuse gains, same layout (objects only)
 // Key: bit 31 dense | loudspeaker mask << 1 | has_diffuse.
 // grid: (ceil((N+M)/128), periods); block 128; one thread per channel (coalesced table reads).
 __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
@@ -550,8 +555,9 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
 }
 
 // mix_order_kernel: the channels of one (period, object split) sorted by key (bitonic sort in shared
-// memory), written as order[k][c0 + i] = channel | has_diffuse << 30 | run_start << 31, where run_start
-// marks the first channel of a run with a new loudspeaker set; dense channels sort to the end.
+// memory), written as order[k][c0 + i] = channel | (run length - 1) << 17 | has_diffuse << 30 |
+// run_start << 31, where run_start marks the first channel of a run with a new loudspeaker set (only
+// that entry carries the length); dense channels sort to the end.
 // counts[k][split] = (listed channels, dense channels).
 // grid: (periods, S); block 256; dynamic shared memory: 8 bytes x the next power of two >= channels per split.
 __global__ void __launch_bounds__(256) mix_order_kernel(Layout p, int T)
@@ -583,7 +589,13 @@ __global__ void __launch_bounds__(256) mix_order_kernel(Layout p, int T)
     const unsigned key = (unsigned)(skey[i] >> 32), c = (unsigned)skey[i];
     const unsigned prev = i ? (unsigned)(skey[i - 1] >> 32) : ~0u;
     const unsigned start = (i == 0 || (key >> 1) != (prev >> 1)) ? 1u : 0u;
-    order[i] = c | (key & 1u) << 30 | start << 31;
+    unsigned run = 0u;
+    if (start) {   // the first channel of a run carries its length (runs are short: a handful of channels)
+      int j = i + 1;
+      while (j < len && (unsigned)(skey[j] >> 33) == key >> 1) j++;
+      run = (unsigned)(j - i - 1);
+    }
+    order[i] = c | run << 17 | (key & 1u) << 30 | start << 31;
     ndense += key >> 31;
   }
   __shared__ int sdense;
@@ -662,6 +674,7 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
 #pragma unroll
   for (int i = 0; i < kMixSlots / 2; i++) accQ[i] = 0ull;
   unsigned nact = 0u, spk_lo = 0u, spk_hi = 0u;   // slots in use and their loudspeakers (same in all threads)
+  int run_left = 0;                               // channels of the current run still to come
   bool qdirty = false;
   // end of a run: the slot sums are added to the bus rows of their loudspeakers with reductions
   // (red.global.add: nothing comes back, so the thread does not wait for L2; every address belongs to
@@ -753,33 +766,36 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
     const float *xr = xt0 + st * kMixChunk * XW + p.hist + tid;
     const float *rec = rc0 + st * kMixChunk * kMixRecWords;
     f32x2 x2n = lagrange(rec, xr);
-    for (int j = 0; j < cnt; j++, rec += kMixRecWords, xr += XW) {
-      const f32x2 x2 = x2n;
-      if (j + 1 < cnt) x2n = lagrange(rec + kMixRecWords, xr + XW);   // the next channel's reads, ahead of this one's sums
-      const float4 *r4 = reinterpret_cast<const float4 *>(rec);
-      const unsigned e = sord[st][j];
-      if (e >> 31) {   // a new loudspeaker set: close the run, take the slot map of this one
+    for (int j = 0; j < cnt;) {
+      if (run_left == 0) {   // a new loudspeaker set: close the run, take the slot map and length of this one
         flush();
-        const uint4 meta = *reinterpret_cast<const uint4 *>(r4 + 1);
+        const uint4 meta = *reinterpret_cast<const uint4 *>(rec + 4);
         nact = meta.x & 0xffu; spk_lo = meta.y; spk_hi = meta.z;
+        run_left = (int)(sord[st][j] >> 17 & 0xfffu) + 1;
       }
+      const int jend = min(cnt, j + run_left);
+      run_left -= jend - j;
+      // the channels of the run that are in this chunk: nothing in here depends on the gains
+      for (; j < jend; j++, rec += kMixRecWords, xr += XW) {
+        const f32x2 x2 = x2n;
+        if (j + 1 < cnt) x2n = lagrange(rec + kMixRecWords, xr + XW);   // the next channel's reads, ahead of this one's sums
+        const float4 *r4 = reinterpret_cast<const float4 *>(rec);
 #pragma unroll
-      for (int i = 0; i < kMixSlots / 2; i++) {
-        if (i == kMixSlots / 4 && nact <= (unsigned)kMixSlots / 2) break;   // upper half of the slots unused
-        const float4 g = r4[2 + i];
-        float ga, gb;
-        unpack2(fma2(rg2, pack2(g.z, g.w), pack2(g.x, g.y)), ga, gb);
-        acc[2 * i] = fma2(splat2(ga), x2, acc[2 * i]);
-        acc[2 * i + 1] = fma2(splat2(gb), x2, acc[2 * i + 1]);
-      }
-      if (e >> 30 & 1u) {
-        const f32x2 x0 = splat2(xr[0]);
-        qdirty = true;
+        for (int i = 0; i < kMixSlots / 2; i++) {   // all slots, used or not (unused ones hold zero gains): no branch
+          const float4 g = r4[2 + i];
+          float ga, gb;
+          unpack2(fma2(rg2, pack2(g.z, g.w), pack2(g.x, g.y)), ga, gb);
+          fma2_acc(acc[2 * i], splat2(ga), x2);
+          fma2_acc(acc[2 * i + 1], splat2(gb), x2);
+        }
+        if (sord[st][j] >> 30 & 1u) {
+          const f32x2 x0 = splat2(xr[0]);
+          qdirty = true;
 #pragma unroll
-        for (int i = 0; i < kMixSlots / 2; i++) {
-          if (i == kMixSlots / 4 && nact <= (unsigned)kMixSlots / 2) break;
-          const float4 q = r4[2 + kMixSlots / 2 + i];
-          accQ[i] = fma2(fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0, accQ[i]);
+          for (int i = 0; i < kMixSlots / 2; i++) {
+            const float4 q = r4[2 + kMixSlots / 2 + i];
+            fma2_acc(accQ[i], fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0);
+          }
         }
       }
     }

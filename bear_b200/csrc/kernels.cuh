@@ -8,7 +8,8 @@ namespace bearcuda {
 constexpr int kMaxSpeakers = 24;  // accumulator tile of the mix kernel (L <= 24)
 constexpr int kMixTile = 128;     // samples per CTA in the mix kernels
 constexpr int kMixChunk = 8;      // channels staged in shared memory per pass (two passes in flight)
-constexpr int kMixSlots = 8;      // non-zero loudspeakers a record lists; channels with more take the dense path
+constexpr int kMixSlots = 6;      // non-zero loudspeakers a record lists (two panning triplets); channels with
+                                  // more take the dense path
 constexpr int kMixRecWords = 8 + 4 * kMixSlots;   // words of one (period, channel) record of mix_prep_kernel
 constexpr int kMaxObjectSplits = 32;              // object splits of a launch (mix_counts row length)
 constexpr int kMaxSplitChannels = 4096;           // channels one object split can sort in shared memory
