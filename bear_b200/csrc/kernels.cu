@@ -739,7 +739,7 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
       asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(total) : "memory");
     __syncwarp();
     if (tid < cnt) {
-      const unsigned c = e & 0xffffffu;
+      const unsigned c = e & 0x1ffffu;
       const float *src = p.xin + (size_t)c * p.xs + (t - tid);   // column (hist + t0) - hist
       const unsigned dst = (unsigned)__cvta_generic_to_shared(xt0 + (st * kMixChunk + tid) * XW);
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
@@ -840,7 +840,7 @@ __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
     const int ndense = p.mix_counts[((size_t)k * kMaxObjectSplits + s) * 2 + 1];
     for (int i = 0; i < ndense; i++) {
       const unsigned e = p.mix_order[(size_t)k * C + c0 + nlisted + i];
-      const int c = (int)(e & 0xffffffu);
+      const int c = (int)(e & 0x1ffffu);
       const bool obj = c < p.N, dif = (e >> 30 & 1u) != 0u;
       __syncthreads();   // the previous channel's gains have been used
       if (tid < kMaxSpeakers) {
