@@ -624,12 +624,11 @@ __device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
 //   qdif[l][t]    += q_c,l(t) * x_c(t)                     (dsp.cpp:127-129)
 // grid: (periods * B / kMixTile, S); block: kMixTile; one output sample per thread.  The CTA zeroes
 // its tile of the 3L rows, then walks its channels in sorted order in chunks of kMixChunk through a
-// ring of kMixStages shared-memory stages.  A chunk is requested by one warp: its lanes read the chunk's
-// order entries and request, per channel, the input row (history + tile) and the record by bulk copies
-// (TMA, 1-D) that complete on the stage's "full" mbarrier.  A warp that is done with a stage arrives on
-// the stage's "empty" mbarrier; the warp whose arrival completes it (the last one to leave the stage)
-// requests the chunk that uses the stage next, so nobody ever waits for a stage to drain and there is
-// no CTA-wide barrier in the loop -- the warps drift apart by up to kMixStages - 1 chunks.  Per channel: two
+// ring of kMixStages shared-memory stages: warp 0 reads a chunk's order entries and requests, per
+// channel, the input row (history + tile) and the record by bulk copies (TMA, 1-D) that complete on
+// the stage's "full" mbarrier, two chunks ahead of the arithmetic; a warp that is done with a stage
+// arrives on its "empty" mbarrier, which is all warp 0 waits for before it refills the stage -- there
+// is no CTA-wide barrier in the loop, the warps drift apart by up to a chunk.  Per channel: two
 // Lagrange-3 reads at the ramped per-ear delays (the next channel's are computed before this channel's
 // sums, for instruction-level parallelism), then per slot pair one packed gain ramp and two FFMA2 into
 // the (left, right) slot accumulators.
@@ -644,7 +643,6 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
   float *const rc0 = smx + kMixStages * kMixChunk * XW;               // [stages][kMixChunk][kMixRecWords] records
   __shared__ __align__(8) unsigned long long bars[2 * kMixStages];    // full[stage], empty[stage]
   __shared__ unsigned sord[kMixStages][kMixChunk];                    // order entries of the staged chunks
-  __shared__ int sclaim[kMixStages];                                  // next chunk to be requested into each stage
   const int tid = threadIdx.x;
   const int t = p.k0 * p.B + blockIdx.x * kMixTile + tid;
   const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
@@ -712,53 +710,57 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
       asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar0 + 8 * i) : "memory");                       // full
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar0 + 8 * (kMixStages + i)), "r"(kMixTile / 32) : "memory");  // empty
     }
-#pragma unroll
-    for (int i = 0; i < kMixStages; i++) sclaim[i] = kMixStages + i;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   __syncthreads();
   const int nchunks = (nlisted + kMixChunk - 1) / kMixChunk;
   const unsigned *order = p.mix_order + (size_t)k * C + c0;
-  const int lane = tid & 31;
-  // the calling warp requests chunk ci into stage ci % kMixStages (which every warp has left): lane i
-  // takes the i-th order entry and requests that channel's input row and record (the diffuse half of a
-  // record only when the channel has diffuse gains)
+  unsigned e_pref = (tid < min(kMixChunk, nlisted)) ? order[tid] : 0u;   // warp 0: order entry of the chunk to request next
+  // warp 0 requests chunk ci into stage ci % kMixStages: lane i takes the i-th order entry and requests
+  // that channel's input row and record (the diffuse half of a record only when the channel has diffuse gains)
   auto request = [&](int ci) {
     const int i0 = ci * kMixChunk, cnt = min(kMixChunk, nlisted - i0), st = ci % kMixStages;
     const unsigned bar = bar0 + 8 * st;
-    unsigned e = 0u, bytes = 0u;
-    if (lane < cnt) {
-      e = order[i0 + lane];
-      sord[st][lane] = e;
+    if (ci >= kMixStages)   // every warp is done with the chunk that used this stage before
+      mbar_wait(bar0 + 8 * (kMixStages + st), (unsigned)(ci / kMixStages - 1) & 1u);
+    const unsigned e = e_pref;
+    unsigned bytes = 0u;
+    if (tid < cnt) {
+      sord[st][tid] = e;
       bytes = (unsigned)XW * 4u + ((e >> 30 & 1u) ? kMixRecWords * 4u : (kMixRecWords - kMixSlots * 2) * 4u);
     }
+    const int inext = i0 + kMixChunk + tid;
+    e_pref = (tid < kMixChunk && inext < nlisted) ? order[inext] : 0u;
     unsigned total = bytes;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) total += __shfl_xor_sync(0xffffffffu, total, o);
     __syncwarp();   // the lanes' sord entries are ordered before lane 0's (releasing) arrive
-    if (lane == 0)
+    if (tid == 0)
       asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(total) : "memory");
     __syncwarp();
-    if (lane < cnt) {
+    if (tid < cnt) {
       const unsigned c = e & 0x1ffffu;
       const float *src = p.xin + (size_t)c * p.xs + (t - tid);   // column (hist + t0) - hist
-      const unsigned dst = (unsigned)__cvta_generic_to_shared(xt0 + (st * kMixChunk + lane) * XW);
+      const unsigned dst = (unsigned)__cvta_generic_to_shared(xt0 + (st * kMixChunk + tid) * XW);
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                    ::"r"(dst), "l"(src), "r"(XW * 4), "r"(bar) : "memory");
       const float *rsrc = p.mix_recs + ((size_t)k * C + c) * kMixRecWords;
-      const unsigned rdst = (unsigned)__cvta_generic_to_shared(rc0 + (st * kMixChunk + lane) * kMixRecWords);
+      const unsigned rdst = (unsigned)__cvta_generic_to_shared(rc0 + (st * kMixChunk + tid) * kMixRecWords);
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                    ::"r"(rdst), "l"(rsrc), "r"(bytes - (unsigned)XW * 4u), "r"(bar) : "memory");
     }
   };
-  if (tid < 32)
-    for (int ci = 0; ci < min(nchunks, kMixStages); ci++) request(ci);
+  if (tid < 32) {
+    if (nchunks > 0) request(0);
+    if (nchunks > 1) request(1);
+  }
   auto lagrange = [&](const float *rec, const float *xr) {
     const float4 dl = *reinterpret_cast<const float4 *>(rec);
     return delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
   };
   for (int ci = 0; ci < nchunks; ci++) {
     const int st = ci % kMixStages;
+    if (tid < 32 && ci + 2 < nchunks) request(ci + 2);
     mbar_wait(bar0 + 8 * st, (unsigned)(ci / kMixStages) & 1u);
     const int cnt = min(kMixChunk, nlisted - ci * kMixChunk);
     const float *xr = xt0 + st * kMixChunk * XW + p.hist + tid;
@@ -797,19 +799,9 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
         }
       }
     }
-    // this warp is done with stage st; if it was the last one, it requests the stage's next chunk
     __syncwarp();
-    int mine = 0;
-    if (lane == 0) {
-      const unsigned ebar = bar0 + 8 * (kMixStages + st);
-      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ebar) : "memory");
-      unsigned done;
-      asm volatile("{\n.reg .pred p;\nmbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
-                   : "=r"(done) : "r"(ebar), "r"((unsigned)(ci / kMixStages) & 1u) : "memory");
-      // (a warp that arrived earlier may look only now and see the phase complete as well: the claim decides)
-      if (done && ci + kMixStages < nchunks) mine = atomicCAS(&sclaim[st], ci + kMixStages, ci + 2 * kMixStages) == ci + kMixStages;
-    }
-    if (__shfl_sync(0xffffffffu, mine, 0)) request(ci + kMixStages);
+    if ((tid & 31) == 0)   // this warp is done with stage st
+      asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar0 + 8 * (kMixStages + st)) : "memory");
   }
   flush();
 }
