@@ -626,14 +626,17 @@ __device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
 // its tile of the 3L rows, then walks its channels in sorted order in chunks of kMixChunk through a
 // ring of kMixStages shared-memory stages: warp 0 reads a chunk's order entries and requests, per
 // channel, the input row (history + tile) and the record by bulk copies (TMA, 1-D) that complete on
-// the stage's "full" mbarrier, two chunks ahead of the arithmetic; a warp that is done with a stage
+// the stage's "full" mbarrier, kMixStages - 1 chunks ahead of the arithmetic; a warp that is done with a stage
 // arrives on its "empty" mbarrier, which is all warp 0 waits for before it refills the stage -- there
 // is no CTA-wide barrier in the loop, the warps drift apart by up to a chunk.  Per channel: two
 // Lagrange-3 reads at the ramped per-ear delays (the next channel's are computed before this channel's
 // sums, for instruction-level parallelism), then per slot pair one packed gain ramp and two FFMA2 into
 // the (left, right) slot accumulators.
 // ----------------------------------------------------------------------------------------------
-constexpr int kMixStages = 3;
+#ifndef BEAR_MIX_STAGES
+#define BEAR_MIX_STAGES 3
+#endif
+constexpr int kMixStages = BEAR_MIX_STAGES;      // chunks in flight: the one being summed + kMixStages - 1 requested ahead
 
 __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
 {
@@ -750,17 +753,15 @@ __global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
                    ::"r"(rdst), "l"(rsrc), "r"(bytes - (unsigned)XW * 4u), "r"(bar) : "memory");
     }
   };
-  if (tid < 32) {
-    if (nchunks > 0) request(0);
-    if (nchunks > 1) request(1);
-  }
+  if (tid < 32)
+    for (int ci = 0; ci < min(nchunks, kMixStages - 1); ci++) request(ci);
   auto lagrange = [&](const float *rec, const float *xr) {
     const float4 dl = *reinterpret_cast<const float4 *>(rec);
     return delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
   };
   for (int ci = 0; ci < nchunks; ci++) {
     const int st = ci % kMixStages;
-    if (tid < 32 && ci + 2 < nchunks) request(ci + 2);
+    if (tid < 32 && ci + kMixStages - 1 < nchunks) request(ci + kMixStages - 1);
     mbar_wait(bar0 + 8 * st, (unsigned)(ci / kMixStages) & 1u);
     const int cnt = min(kMixChunk, nlisted - ci * kMixChunk);
     const float *xr = xt0 + st * kMixChunk * XW + p.hist + tid;

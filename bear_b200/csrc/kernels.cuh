@@ -7,7 +7,10 @@ namespace bearcuda {
 
 constexpr int kMaxSpeakers = 24;  // accumulator tile of the mix kernel (L <= 24)
 constexpr int kMixTile = 128;     // samples per CTA in the mix kernels
-constexpr int kMixChunk = 8;      // channels staged in shared memory per pass (two passes in flight)
+#ifndef BEAR_MIX_CHUNK
+#define BEAR_MIX_CHUNK 8
+#endif
+constexpr int kMixChunk = BEAR_MIX_CHUNK;   // channels staged in shared memory per pass
 constexpr int kMixSlots = 6;      // non-zero loudspeakers a record lists (two panning triplets); channels with
                                   // more take the dense path
 constexpr int kMixRecWords = 8 + 4 * kMixSlots;   // words of one (period, channel) record of mix_prep_kernel
@@ -135,6 +138,7 @@ void launch_frames(const Layout &p, const void *frames, int format, int frame_ch
                    int first_frame, int nframes, cudaStream_t st);
 cudaError_t configure_kernels(int B);
 cudaError_t configure_mix(int hist, int B);
+size_t mix_smem_bytes(int hist);
 
 // Fixed-size device scratch that lives in the library image (no allocation), and its device
 // address for the current device (resolved on first use per device).

@@ -37,7 +37,7 @@ struct Unsupported { std::string msg; };
 size_t round_up(size_t v, size_t m) { return (v + m - 1) / m * m; }
 bool mix_hist_too_large(int hist)
 {
-  return (size_t)3 * kMixChunk * (hist + kMixTile + kMixRecWords) * sizeof(float) > 200 * 1024;
+  return mix_smem_bytes(hist) > 200 * 1024;
 }
 
 // ---- NCCL, bound at run time -------------------------------------------------------------------

@@ -118,10 +118,11 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        if not LIB_PATH.exists():
+        path = Path(os.environ.get("BEAR_CUDA_LIB", LIB_PATH))    # (a differently tuned build, for experiments)
+        if not path.exists():
             raise RuntimeError("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
-                               "(there is no CPU fallback)" % LIB_PATH)
-        l = C.CDLL(str(LIB_PATH))
+                               "(there is no CPU fallback)" % path)
+        l = C.CDLL(str(path))
         vp, u32, sz = C.c_void_p, C.c_uint32, C.c_size_t
         l.bear_cuda_create.argtypes = [C.POINTER(Config), C.POINTER(Data), C.POINTER(vp)]
         l.bear_cuda_create_from_file.argtypes = [C.POINTER(Config), C.c_char_p, C.POINTER(vp)]
