@@ -1579,11 +1579,13 @@ __global__ void __launch_bounds__(128, 4) cmac_kernel(Layout p, int T)
     case 2: cmac_item_pipe_flags<2>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
     case 3: cmac_item_pipe_flags<3>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
     case 4: cmac_item_pipe_flags<4>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+#if BEAR_CMAC_GROUP == 6
     case 5: cmac_item_pipe_flags<5>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
-    default: cmac_item_pipe_flags<6>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
+#endif
+    default: cmac_item_pipe_flags<kCmacGroup>(p, j, e, ks, KS, pair, v, maskA, maskB, cmac_ring); break;
   }
 }
-static_assert(kCmacGroup == 6, "cmac_kernel dispatches on the item size");
+static_assert(kCmacGroup == 5 || kCmacGroup == 6, "cmac_kernel dispatches on the item size");
 
 // view_group_kernel: the periods k0-1 .. k0+n-1 of a launch sorted by view and cut into items of up
 // to kCmacGroup periods (counting sort in one CTA).  grp_sorted holds period indices relative to

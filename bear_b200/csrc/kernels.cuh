@@ -20,7 +20,10 @@ constexpr int kMaxRanks = 8;      // GPUs that can share one scene (bear_cuda_co
 // bits of Layout::err_flag (checked by the host after a call has finished)
 constexpr int kErrDelayRange = 1; // a table delay is negative or beyond history_samples - 4
 constexpr int kErrViewRange = 2;  // a brir_index on the device-resident path is outside [0, V)
-constexpr int kCmacGroup = 6;     // periods of one view that share a filter load in the cMAC kernel
+#ifndef BEAR_CMAC_GROUP
+#define BEAR_CMAC_GROUP 5
+#endif
+constexpr int kCmacGroup = BEAR_CMAC_GROUP;     // periods of one view that share a filter load in the cMAC kernel
 
 // Everything a kernel needs to find its data.  Passed by value (fits the 4 KB param space).
 struct Layout {
