@@ -634,7 +634,7 @@ __device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
 // the (left, right) slot accumulators.
 // ----------------------------------------------------------------------------------------------
 #ifndef BEAR_MIX_STAGES
-#define BEAR_MIX_STAGES 3
+#define BEAR_MIX_STAGES 2
 #endif
 constexpr int kMixStages = BEAR_MIX_STAGES;      // chunks in flight: the one being summed + kMixStages - 1 requested ahead
 
