@@ -162,6 +162,10 @@ struct bear_cuda_renderer {
   float *bus_sum = nullptr;                // [3L][cs] rows of this rank's loudspeakers summed over the ranks
   int *d_barrier = nullptr;                // payload of the cross-rank barrier
   size_t comm_bytes_per_period = 0;        // largest upload per period among the ranks (same chunking everywhere)
+  cudaStream_t conv_stream = nullptr;      // shared scene: exchange + convolution of chunk c run here, under the mix of chunk c+1
+  cudaStream_t result_stream = nullptr;    // the stream a chunk's output is complete on (render stream, or conv_stream)
+  std::vector<cudaEvent_t> mix_events;     // one per chunk: its bus rows are written
+  cudaEvent_t ev_call = nullptr;
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -227,6 +231,9 @@ struct bear_cuda_renderer {
       for (cudaEvent_t e : c) cudaEventDestroy(e);
     for (cudaEvent_t e : ev_free) cudaEventDestroy(e);
     if (comm) nccl().CommDestroy(comm);
+    for (cudaEvent_t e : mix_events) cudaEventDestroy(e);
+    if (ev_call) cudaEventDestroy(ev_call);
+    if (conv_stream) cudaStreamDestroy(conv_stream);
     for (int w = 0; w < kMaxRanks; w++)
       if (peer_bus[w][0] && w != lay.rank) cudaIpcCloseMemHandle(peer_bus[w][0]);
     if (h_err) cudaFreeHost(h_err);
@@ -416,6 +423,7 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   CK(cudaStreamCreateWithFlags(&r->stream, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&r->copy_stream, cudaStreamNonBlocking));
   CK(cudaStreamCreateWithFlags(&r->d2h_stream, cudaStreamNonBlocking));
+  r->result_stream = r->stream;
 
   Layout &p = r->lay;
   p.N = cfg.num_objects_channels; p.M = cfg.num_direct_speakers_channels; p.H = cfg.num_hoa_channels;
@@ -649,6 +657,16 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   };
   if (chunk <= 0 || chunk > T) chunk = T;
   const bool shared_scene = p.W > 1;
+  // A shared scene is issued in at least four chunks: the exchange (ordering collective, gather of the
+  // peers' rows over NVLink) and the convolution of chunk c then run on a second stream under the mix of
+  // chunk c+1 -- the mix keeps the SMs busy, the gather the NVLink ports.  (Per-kernel profiling keeps
+  // everything on one stream so that its event pairs mean something.)
+  if (shared_scene && chunk == T && T >= 64) chunk = (int)round_up((size_t)(T + 3) / 4, 8);
+  const int nchunks_total = (T + chunk - 1) / chunk;
+  const bool overlap = shared_scene && !r->profiling && r->conv_stream && nchunks_total > 1 &&
+                       nchunks_total <= (int)r->mix_events.size();
+  cudaStream_t sb = overlap ? r->conv_stream : st;   // exchange + convolution side
+  r->result_stream = sb;
   // bus rows of this call; a renderer that shares a scene alternates between its two sets, so that a
   // peer still reading the previous call's rows is never overwritten (one barrier per chunk suffices)
   float *const bus = r->bus[r->parity];
@@ -666,6 +684,10 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   p.bps = (size_t)chunk * p.B;
   uint64_t launches = 0;
   if (device_tables) { launch_validate_views(p, T, st); launches++; }
+  if (overlap) {   // the convolution side starts after everything queued so far (the previous call's carry)
+    CK(cudaEventRecord(r->ev_call, st));
+    CK(cudaStreamWaitEvent(sb, r->ev_call, 0));
+  }
   int nchunks = 0;
   for (int k0 = 0; k0 < T; nchunks++) {
     const int n = std::min(chunk, T - k0);
@@ -678,19 +700,23 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       if (p.S > 1) { mark(BEAR_CUDA_KERNEL_MIX_AUX); launch_bus_sum(p, n, st); launches++; }
     }
     if (p.H > 0) { mark(BEAR_CUDA_KERNEL_HOA_MIX); launch_hoa_mix(p, n, st); launches++; }
+    if (overlap) {
+      CK(cudaEventRecord(r->mix_events[nchunks], st));
+      CK(cudaStreamWaitEvent(sb, r->mix_events[nchunks], 0));
+    }
     if (shared_scene) {
       // every rank's bus rows of this chunk are complete before anyone reads them
       mark(BEAR_CUDA_KERNEL_EXCHANGE);
-      NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, st));
-      launch_bus_gather(p, n, st);
+      NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, sb));
+      launch_bus_gather(p, n, sb);
       if (p.l1 > p.l0) launches++;
     }
-    if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, st); launches++; }
-    if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, st); launches++; }
+    if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, sb); launches++; }
+    if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, sb); launches++; }
     p.KS = cmac_splits_for(r, n);
     p.ks_dev = cmac_groups_by_view(p, n);
-    mark(BEAR_CUDA_KERNEL_CMAC); launches += launch_cmac(p, n, st);
-    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, st); launches++;
+    mark(BEAR_CUDA_KERNEL_CMAC); launches += launch_cmac(p, n, sb);
+    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, sb); launches++;
     p.KS = r->ks_cfg;
     p.ks_dev = 0;
     if (shared_scene) {
@@ -701,9 +727,9 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       for (int e = 0; e < 2; e++) {
         float *row = p.out + (size_t)e * p.os + (size_t)k0 * p.B;
         if (r->comm_root >= 0)
-          NCK(nccl().Reduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm_root, r->comm, st));
+          NCK(nccl().Reduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm_root, r->comm, sb));
         else
-          NCK(nccl().AllReduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm, st));
+          NCK(nccl().AllReduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm, sb));
       }
       NCK(nccl().GroupEnd());
     }
@@ -711,6 +737,10 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
     k0 += n;
   }
   p.k0 = 0;
+  if (overlap) {   // the carry moves state both sides use: it follows both
+    CK(cudaEventRecord(r->ev_call, sb));
+    CK(cudaStreamWaitEvent(st, r->ev_call, 0));
+  }
   mark(BEAR_CUDA_KERNEL_CARRY);
 
   CarryPlan plan{};
@@ -1060,7 +1090,7 @@ int bear_cuda_process_batch(bear_cuda_renderer *r, uint32_t T, const float *obje
         r, (int)T, chunk, [&](int c, int, int) { CK(cudaStreamWaitEvent(r->stream, r->h2d_events[c], 0)); },
         [&](int c, int k0, int n) {
           if (!output) return;
-          CK(cudaEventRecord(r->done_events[c], r->stream));
+          CK(cudaEventRecord(r->done_events[c], r->result_stream));
           CK(cudaStreamWaitEvent(r->d2h_stream, r->done_events[c], 0));
           CK(cudaMemcpy2DAsync(output + (size_t)k0 * p.B, out_stride * sizeof(float), p.out + (size_t)k0 * p.B,
                                p.os * sizeof(float), (size_t)n * p.B * sizeof(float), 2, cudaMemcpyDeviceToHost,
@@ -1123,7 +1153,7 @@ int bear_cuda_process_batch_frames(bear_cuda_renderer *r, uint32_t T, const void
         },
         [&](int c, int k0, int n) {
           if (!output) return;
-          CK(cudaEventRecord(r->done_events[c], r->stream));
+          CK(cudaEventRecord(r->done_events[c], r->result_stream));
           CK(cudaStreamWaitEvent(r->d2h_stream, r->done_events[c], 0));
           CK(cudaMemcpy2DAsync(output + (size_t)k0 * p.B, out_stride * sizeof(float), p.out + (size_t)k0 * p.B,
                                p.os * sizeof(float), (size_t)n * p.B * sizeof(float), 2, cudaMemcpyDeviceToHost,
@@ -1550,6 +1580,10 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
     }
     NCK(nccl().CommInitRank(&r->comm, (int)world, bl[0].id, (int)rank));
     r->d_barrier = r->dalloc<int>(4);
+    CK(cudaStreamCreateWithFlags(&r->conv_stream, cudaStreamNonBlocking));
+    CK(cudaEventCreateWithFlags(&r->ev_call, cudaEventDisableTiming));
+    r->mix_events.resize(std::max<size_t>(r->done_events.size(), 4));
+    for (cudaEvent_t &e : r->mix_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     r->bus_sum = r->dalloc<float>((size_t)3 * p.L * p.cs);
     r->comm_root = root;
     uint32_t l0 = 0, l1 = 0;
