@@ -638,7 +638,10 @@ __device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
 #endif
 constexpr int kMixStages = BEAR_MIX_STAGES;      // chunks in flight: the one being summed + kMixStages - 1 requested ahead
 
-__global__ void __launch_bounds__(kMixTile, 5) mix_kernel(Layout p, int T)
+#ifndef BEAR_MIX_MINBLOCKS
+#define BEAR_MIX_MINBLOCKS 5
+#endif
+__global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layout p, int T)
 {
   extern __shared__ __align__(16) float smx[];
   const int XW = p.hist + kMixTile;

@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -166,6 +167,7 @@ struct bear_cuda_renderer {
   cudaStream_t result_stream = nullptr;    // the stream a chunk's output is complete on (render stream, or conv_stream)
   std::vector<cudaEvent_t> mix_events;     // one per chunk: its bus rows are written
   cudaEvent_t ev_call = nullptr;
+  int shared_chunks = 4;                   // chunks a shared-scene call is cut into (BEAR_CUDA_SHARED_CHUNKS overrides)
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -603,7 +605,7 @@ int cmac_splits_for(const bear_cuda_renderer *r, int n)
 
 // Object splits of a launch of n periods: mix_kernel runs one CTA per (tile of kMixTile samples, split),
 // each walking its share of the channels; a launch with few tiles splits the channels so that there
-// are about two waves of CTAs (4 per SM) -- a 16-period upload chunk of a 1024-object scene is
+// is about one wave of CTAs (5 per SM) -- a 16-period upload chunk of a 1024-object scene is
 // otherwise 32 CTAs that each walk 1024 channels.  The partial sums cost one small extra kernel.
 int object_splits_for(const bear_cuda_renderer *r, int n)
 {
@@ -613,7 +615,7 @@ int object_splits_for(const bear_cuda_renderer *r, int n)
   const int minS = (C + kMaxSplitChannels - 1) / kMaxSplitChannels;   // a split is sorted in shared memory
   if (r->s_cfg) return std::max(std::max(1, minS), std::min(r->s_cfg, maxS));
   const int tiles = std::max(1, n * p.B / kMixTile);
-  return std::max(std::max(1, minS), std::min((2 * 5 * 148 + tiles - 1) / tiles, maxS));
+  return std::max(std::max(1, minS), std::min((5 * 148 + tiles / 2) / tiles, maxS));   // about one wave of CTAs
 }
 // Periods per upload chunk of a host-buffer call whose period takes bytes_per_period on the bus.
 // A chunk of any size needs ~0.15 ms to pass through the six kernels, so a chunk should take at least
@@ -661,7 +663,8 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   // peers' rows over NVLink) and the convolution of chunk c then run on a second stream under the mix of
   // chunk c+1 -- the mix keeps the SMs busy, the gather the NVLink ports.  (Per-kernel profiling keeps
   // everything on one stream so that its event pairs mean something.)
-  if (shared_scene && chunk == T && T >= 64) chunk = (int)round_up((size_t)(T + 3) / 4, 8);
+  if (shared_scene && chunk == T && T >= 64 && r->shared_chunks > 1)
+    chunk = (int)round_up((size_t)(T + r->shared_chunks - 1) / r->shared_chunks, 8);
   const int nchunks_total = (T + chunk - 1) / chunk;
   const bool overlap = shared_scene && !r->profiling && r->conv_stream && nchunks_total > 1 &&
                        nchunks_total <= (int)r->mix_events.size();
@@ -1580,6 +1583,7 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
     }
     NCK(nccl().CommInitRank(&r->comm, (int)world, bl[0].id, (int)rank));
     r->d_barrier = r->dalloc<int>(4);
+    if (const char *env = std::getenv("BEAR_CUDA_SHARED_CHUNKS")) r->shared_chunks = std::max(1, std::atoi(env));
     CK(cudaStreamCreateWithFlags(&r->conv_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&r->ev_call, cudaEventDisableTiming));
     r->mix_events.resize(std::max<size_t>(r->done_events.size(), 4));
