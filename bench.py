@@ -63,6 +63,7 @@ def parse_args():
     ap.add_argument("--no-extras", action="store_true", help="only the headline workload")
     ap.add_argument("--chunk-blocks", type=int, default=0, help="periods per launch group (0 = library default)")
     ap.add_argument("--cmac-splits", type=int, default=0, help="partial spectra per period (0 = library default)")
+    ap.add_argument("--object-splits", type=int, default=0, help="mix CTAs per tile (0 = library default)")
     ap.add_argument("--batch-files", type=int, default=256, help="files of the configs[4] extra (0 = skip)")
     return ap.parse_args()
 
@@ -348,7 +349,7 @@ def run_ours(args, rank, world, local_rank):
     T = periods_per_step(args, B)
     data, ctl = data_and_control()
     leg = Leg(data, ctl, B, T, rank * mine, mine, scale, local_rank, chunk_blocks=args.chunk_blocks,
-              cmac_splits=args.cmac_splits)
+              cmac_splits=args.cmac_splits, object_splits=args.object_splits)
     r = leg.r
     if world > 1:
         parallel.connect_renderers(r, rank, world, root=0)
