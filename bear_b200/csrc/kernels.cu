@@ -639,7 +639,7 @@ __device__ __forceinline__ void mbar_wait(unsigned bar_addr, unsigned parity)
 constexpr int kMixStages = BEAR_MIX_STAGES;      // chunks in flight: the one being summed + kMixStages - 1 requested ahead
 
 #ifndef BEAR_MIX_MINBLOCKS
-#define BEAR_MIX_MINBLOCKS 5
+#define BEAR_MIX_MINBLOCKS 7
 #endif
 __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layout p, int T)
 {

@@ -8,7 +8,7 @@ namespace bearcuda {
 constexpr int kMaxSpeakers = 24;  // accumulator tile of the mix kernel (L <= 24)
 constexpr int kMixTile = 128;     // samples per CTA in the mix kernels
 #ifndef BEAR_MIX_CHUNK
-#define BEAR_MIX_CHUNK 16
+#define BEAR_MIX_CHUNK 12
 #endif
 constexpr int kMixChunk = BEAR_MIX_CHUNK;   // channels staged in shared memory per pass
 constexpr int kMixSlots = 6;      // non-zero loudspeakers a record lists (two panning triplets); channels with

@@ -615,19 +615,9 @@ int object_splits_for(const bear_cuda_renderer *r, int n)
   const int minS = (C + kMaxSplitChannels - 1) / kMaxSplitChannels;   // a split is sorted in shared memory
   if (r->s_cfg) return std::max(std::max(1, minS), std::min(r->s_cfg, maxS));
   const int tiles = std::max(1, n * p.B / kMixTile);
-  const int lo = std::max(1, minS), slots = 5 * 148;                 // CTAs resident at once
-  if (tiles < slots) return std::max(lo, std::min((slots + tiles / 2) / tiles, maxS));   // about one wave of CTAs
-  // Long launches: a CTA walks all its channels, so the last, partly filled wave of CTAs costs up to a
-  // whole CTA's time; a few splits make the CTAs shorter and the last wave fuller.  Pick the split count
-  // (<= 4) with the best wave efficiency, charging ~3 % per extra split for its partial sums.
-  int best = lo;
-  double best_score = 0.0;
-  for (int S = lo; S <= std::max(lo, std::min(4, maxS)); S++) {
-    const double ctas = (double)tiles * S, waves = std::ceil(ctas / slots);
-    const double score = ctas / (waves * slots) / (1.0 + 0.03 * (S - 1));
-    if (score > best_score + 1e-9) { best_score = score; best = S; }
-  }
-  return best;
+  // (long launches keep one split: measured at 1024 objects x 1872 periods, two splits cost more in partial
+  // sums and per-CTA set-up than their fuller last wave of CTAs gains -- 2.09 against 2.03 ms)
+  return std::max(std::max(1, minS), std::min((5 * 148 + tiles / 2) / tiles, maxS));   // about one wave of CTAs
 }
 // Periods per upload chunk of a host-buffer call whose period takes bytes_per_period on the bus.
 // A chunk of any size needs ~0.15 ms to pass through the six kernels, so a chunk should take at least
