@@ -1,7 +1,7 @@
 #!/bin/bash
 # bench.py at N GPUs with the shared-scene call cut into 1, 2, 3, 4, 6 chunks (device-resident value only)
 N=${1:-2}
-for c in 1 2 3 4 6; do
+for c in ${CHUNKS:-1 2 3 4 6}; do
   BEAR_CUDA_SHARED_CHUNKS=$c timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port $((29520 + c)) \
     bench.py --gpus $N --steps 10 --warmup 3 --no-extras --batch-files 0 2>/dev/null | python -c "
 import sys, json
