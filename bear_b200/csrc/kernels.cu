@@ -499,8 +499,10 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
   }
   const float *gd = (obj ? p.g_dir : p.g_ds) + (size_t)k * L * ld + ci;   // [slot k: L rows][slot k+1: L rows]
   const float *gq = p.g_dif + (size_t)k * L * ld + ci;
-  unsigned mask = 0u, any_q = 0u;
-  for (int l0 = 0; l0 < L; l0 += 8) {   // eight loudspeakers' table entries are loaded before any is tested
+  // one pass over the loudspeakers, eight at a time (their table entries are loaded before any is
+  // tested); a non-zero one takes the next slot and its (start, delta) pairs go straight to the record
+  unsigned mask = 0u, any_q = 0u, cnt = 0u, spk[2] = {0u, 0u};
+  for (int l0 = 0; l0 < L; l0 += 8) {
     float va[8], vb[8], qa[8], qb[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) {
@@ -512,45 +514,32 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
     for (int i = 0; i < 8; i++) {
       if (l0 + i < L) {
         const bool nzq = qa[i] != 0.f || qb[i] != 0.f;
-        if (va[i] != 0.f || vb[i] != 0.f || nzq) mask |= 1u << (l0 + i);
+        if (va[i] != 0.f || vb[i] != 0.f || nzq) {
+          mask |= 1u << (l0 + i);
+          if (cnt < (unsigned)kMixSlots) {
+            float *e = rec + 8 + 4 * (cnt >> 1) + (cnt & 1u);     // pair layout: (g0[2i], g0[2i+1], dg[2i], dg[2i+1])
+            e[0] = va[i]; e[2] = vb[i] - va[i];
+            e[2 * kMixSlots] = qa[i]; e[2 * kMixSlots + 2] = qb[i] - qa[i];
+            spk[cnt >> 2] |= (unsigned)(l0 + i) << (8 * (cnt & 3u));
+          }
+          cnt++;
+        }
         if (nzq) any_q = 1u;
       }
     }
   }
-  const int ns = __popc(mask);
   unsigned *keys = p.mix_keys + (size_t)k * C;
-  if (ns > kMixSlots) {
+  reinterpret_cast<float4 *>(rec)[0] = dl;
+  if (cnt > (unsigned)kMixSlots) {
     keys[c] = 0x80000000u | any_q;
-    reinterpret_cast<float4 *>(rec)[0] = dl;
     reinterpret_cast<uint4 *>(rec)[1] = make_uint4(255u | any_q << 8, 0u, 0u, 0u);
     return;
   }
   keys[c] = mask << 1 | any_q;
-  float g0[kMixSlots], dg[kMixSlots], q0[kMixSlots], dq[kMixSlots];
-  unsigned spk[2] = {0u, 0u};
-  unsigned m = mask;
-#pragma unroll
-  for (int s = 0; s < kMixSlots; s++) {
-    g0[s] = dg[s] = q0[s] = dq[s] = 0.f;
-    if (m) {
-      const int l = __ffs(m) - 1;
-      m &= m - 1;
-      spk[s >> 2] |= (unsigned)l << (8 * (s & 3));
-      const float a = gd[(size_t)l * ld], b = gd[(size_t)(L + l) * ld];
-      g0[s] = a; dg[s] = b - a;
-      if (obj) {
-        const float qa = gq[(size_t)l * ld], qb = gq[(size_t)(L + l) * ld];
-        q0[s] = qa; dq[s] = qb - qa;
-      }
-    }
-  }
-  float4 *r4 = reinterpret_cast<float4 *>(rec);
-  r4[0] = dl;
-  reinterpret_cast<uint4 *>(rec)[1] = make_uint4((unsigned)ns | any_q << 8, spk[0], spk[1], 0u);
-#pragma unroll
-  for (int i = 0; i < kMixSlots / 2; i++) {
-    r4[2 + i] = make_float4(g0[2 * i], g0[2 * i + 1], dg[2 * i], dg[2 * i + 1]);
-    r4[2 + kMixSlots / 2 + i] = make_float4(q0[2 * i], q0[2 * i + 1], dq[2 * i], dq[2 * i + 1]);
+  reinterpret_cast<uint4 *>(rec)[1] = make_uint4(cnt | any_q << 8, spk[0], spk[1], 0u);
+  for (unsigned s = cnt; s < (unsigned)kMixSlots; s++) {   // unused slots hold zero gains
+    float *e = rec + 8 + 4 * (s >> 1) + (s & 1u);
+    e[0] = 0.f; e[2] = 0.f; e[2 * kMixSlots] = 0.f; e[2 * kMixSlots + 2] = 0.f;
   }
 }
 
@@ -812,14 +801,21 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
 
 // mix_dense_kernel: the channels whose gains are dense (more than kMixSlots non-zero loudspeakers:
 // objects with extent), from the gain tables themselves with all 3L accumulators in registers, added
-// to the bus rows.  Per channel the 4 x L table values of the period are staged in shared memory as
-// (start, start, delta, delta) of loudspeaker pairs, so the inner loop is one broadcast load, one
-// packed ramp and two FFMA2 per pair; the delayed reads come from global memory.  Periods without
-// dense channels return at once.
-// grid: periods * B / kMixTile; block kMixTile.
+// to the bus rows.  Channels are taken in chunks of kMixChunk: their input rows (history + tile) arrive
+// by bulk copies (TMA, 1-D) on an mbarrier while all threads stage the chunk's 4 x L table values per
+// channel in shared memory as pair-packed (start, start, delta, delta); per channel the inner loop is
+// then one broadcast load, one packed ramp and two FFMA2 per loudspeaker pair.  Periods without dense
+// channels return at once.
+// grid: periods * B / kMixTile; block kMixTile; dynamic shared memory: kMixChunk rows + kMixChunk x 4 L + 4 floats.
 __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
 {
-  __shared__ __align__(16) float sgd[kMaxSpeakers * 2], sgq[kMaxSpeakers * 2];
+  extern __shared__ __align__(16) float smd[];
+  const int XW = p.hist + kMixTile;
+  float *const xt = smd;                                       // [kMixChunk][XW] input rows
+  float *const sg = smd + kMixChunk * XW;                      // [kMixChunk][2][kMaxSpeakers * 2] direct / diffuse pairs
+  float *const sdl = sg + kMixChunk * 4 * kMaxSpeakers;        // [kMixChunk][4] delay ramps
+  __shared__ __align__(8) unsigned long long bar;
+  __shared__ unsigned sent[kMixChunk];
   const int tid = threadIdx.x;
   const int t = p.k0 * p.B + blockIdx.x * kMixTile + tid;
   const int k = p.k0 + (blockIdx.x * kMixTile) / p.B;
@@ -838,48 +834,79 @@ __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
   for (int l = 0; l < kMaxSpeakers; l++) acc[l] = 0ull;
 #pragma unroll
   for (int l = 0; l < kMaxSpeakers / 2; l++) accQ[l] = 0ull;
+  const unsigned bar_addr = (unsigned)__cvta_generic_to_shared(&bar);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar_addr) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  unsigned phase = 0;
   for (int s = 0; s < p.S; s++) {
     const int c0 = min(C, s * per);
     const int nlisted = p.mix_counts[((size_t)k * kMaxObjectSplits + s) * 2];
     const int ndense = p.mix_counts[((size_t)k * kMaxObjectSplits + s) * 2 + 1];
-    for (int i = 0; i < ndense; i++) {
-      const unsigned e = p.mix_order[(size_t)k * C + c0 + nlisted + i];
-      const int c = (int)(e & 0x1ffffu);
-      const bool obj = c < p.N, dif = (e >> 30 & 1u) != 0u;
-      __syncthreads();   // the previous channel's gains have been used
-      if (tid < kMaxSpeakers) {
-        const int l = tid, ld = obj ? p.N : p.M;
+    const unsigned *order = p.mix_order + (size_t)k * C + c0 + nlisted;
+    for (int i0 = 0; i0 < ndense; i0 += kMixChunk) {
+      const int cnt = min(kMixChunk, ndense - i0);
+      __syncthreads();   // the previous chunk has been used (and the barrier is initialised)
+      if (tid < 32) {
+        unsigned e = 0u;
+        if (tid < cnt) { e = order[i0 + tid]; sent[tid] = e; }
+        if (tid == 0)
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar_addr), "r"(cnt * XW * 4) : "memory");
+        __syncwarp();
+        if (tid < cnt) {
+          const float *src = p.xin + (size_t)(e & 0x1ffffu) * p.xs + (t - tid);
+          asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                       ::"r"((unsigned)__cvta_generic_to_shared(xt + tid * XW)), "l"(src), "r"(XW * 4), "r"(bar_addr) : "memory");
+        }
+      }
+      // gains of the chunk: entry (channel j, loudspeaker l) -> pair layout (g0[2i], g0[2i+1], dg[2i], dg[2i+1])
+      for (int idx = tid; idx < cnt * kMaxSpeakers; idx += kMixTile) {
+        const int j = idx / kMaxSpeakers, l = idx - j * kMaxSpeakers;
+        const unsigned e = order[i0 + j];
+        const int c = (int)(e & 0x1ffffu);
+        const bool obj = c < p.N;
+        const int ld = obj ? p.N : p.M;
         float g0 = 0.f, g1 = 0.f, q0 = 0.f, q1 = 0.f;
         if (l < L) {
           const float *g = (obj ? p.g_dir + (size_t)k * L * ld + c : p.g_ds + (size_t)k * L * ld + (c - p.N));
           g0 = g[(size_t)l * ld]; g1 = g[(size_t)(L + l) * ld];
-          if (dif) {
+          if (e >> 30 & 1u) {
             const float *q = p.g_dif + (size_t)k * L * p.N + c;
             q0 = q[(size_t)l * p.N]; q1 = q[(size_t)(L + l) * p.N];
           }
         }
-        const int o = 4 * (l >> 1) + (l & 1);           // pair layout: (g0[2i], g0[2i+1], dg[2i], dg[2i+1])
-        sgd[o] = g0; sgd[o + 2] = g1 - g0;
-        sgq[o] = q0; sgq[o + 2] = q1 - q0;
+        float *o = sg + j * 4 * kMaxSpeakers + 4 * (l >> 1) + (l & 1);
+        o[0] = g0; o[2] = g1 - g0;
+        o[2 * kMaxSpeakers] = q0; o[2 * kMaxSpeakers + 2] = q1 - q0;
       }
-      const float4 dl = *reinterpret_cast<const float4 *>(p.mix_recs + ((size_t)k * C + c) * kMixRecWords);
-      const float *xr = p.xin + (size_t)c * p.xs + p.hist + t;
-      const f32x2 x2 = delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
+      if (tid < cnt * 4) {
+        const int j = tid >> 2;
+        sdl[tid] = p.mix_recs[((size_t)k * C + (order[i0 + j] & 0x1ffffu)) * kMixRecWords + (tid & 3)];
+      }
       __syncthreads();
+      mbar_wait(bar_addr, phase);
+      phase ^= 1u;
+      for (int j = 0; j < cnt; j++) {
+        const float *xr = xt + j * XW + p.hist + tid;
+        const float4 dl = *reinterpret_cast<const float4 *>(sdl + 4 * j);
+        const f32x2 x2 = delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
+        const float4 *g4 = reinterpret_cast<const float4 *>(sg + j * 4 * kMaxSpeakers);
 #pragma unroll
-      for (int j = 0; j < kMaxSpeakers / 2; j++) {
-        const float4 g = reinterpret_cast<const float4 *>(sgd)[j];
-        float ga, gb;
-        unpack2(fma2(rg2, pack2(g.z, g.w), pack2(g.x, g.y)), ga, gb);
-        acc[2 * j] = fma2(splat2(ga), x2, acc[2 * j]);
-        acc[2 * j + 1] = fma2(splat2(gb), x2, acc[2 * j + 1]);
-      }
-      if (dif) {
-        const f32x2 x0 = splat2(xr[0]);
+        for (int i = 0; i < kMaxSpeakers / 2; i++) {
+          const float4 g = g4[i];
+          float ga, gb;
+          unpack2(fma2(rg2, pack2(g.z, g.w), pack2(g.x, g.y)), ga, gb);
+          fma2_acc(acc[2 * i], splat2(ga), x2);
+          fma2_acc(acc[2 * i + 1], splat2(gb), x2);
+        }
+        if (sent[j] >> 30 & 1u) {
+          const f32x2 x0 = splat2(xr[0]);
 #pragma unroll
-        for (int j = 0; j < kMaxSpeakers / 2; j++) {
-          const float4 q = reinterpret_cast<const float4 *>(sgq)[j];
-          accQ[j] = fma2(fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0, accQ[j]);
+          for (int i = 0; i < kMaxSpeakers / 2; i++) {
+            const float4 q = g4[kMaxSpeakers / 2 + i];
+            fma2_acc(accQ[i], fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0);
+          }
         }
       }
     }
@@ -943,6 +970,10 @@ void launch_bus_gather(const Layout &p, int T, cudaStream_t st)
 }
 
 size_t mix_smem_bytes(int hist);
+static size_t mix_dense_smem_bytes(int hist)
+{
+  return (size_t)kMixChunk * ((hist + kMixTile) + 4 * kMaxSpeakers + 4) * sizeof(float);
+}
 void launch_mix_prep(const Layout &p, int T, cudaStream_t st)
 {
   const int C = p.N + p.M, per = (C + p.S - 1) / p.S;
@@ -955,7 +986,7 @@ void launch_mix(const Layout &p, int T, cudaStream_t st)
 {
   dim3 grid(T * p.B / kMixTile, p.S);
   mix_kernel<<<grid, kMixTile, mix_smem_bytes(p.hist), st>>>(p, T);
-  mix_dense_kernel<<<T * p.B / kMixTile, kMixTile, 0, st>>>(p, T);
+  mix_dense_kernel<<<T * p.B / kMixTile, kMixTile, mix_dense_smem_bytes(p.hist), st>>>(p, T);
 }
 void launch_bus_sum(const Layout &p, int T, cudaStream_t st)   // only launches with S > 1
 {
@@ -2026,6 +2057,8 @@ static int ilog2(int v)
 cudaError_t configure_mix(int hist, int B)
 {
   cudaError_t e = cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(mix_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_dense_smem_bytes(hist));
   if (e != cudaSuccess) return e;
   dispatch_logb(ilog2(B), [&](auto lb) {
     e = cudaFuncSetAttribute(bus_fdl_kernel<decltype(lb)::value>, cudaFuncAttributeMaxDynamicSharedMemorySize,
