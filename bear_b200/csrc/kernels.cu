@@ -471,7 +471,7 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 // mix_prep_kernel: the record and the sort key of every (period, channel).
 // Record (kMixRecWords = 8 + 4 kMixSlots words):
 //   [0..3]   per-ear delay ramp in samples: d0L, ddL, d0R, ddR (validated, then clamped to the history)
-//   [4]      number of slots | has_diffuse << 8        [5], [6] loudspeaker of slots 0..3, 4.. (bytes)
+//   [4]      number of slots | has_diffuse << 8        [5], [6] loudspeaker of slots 0..3, 4.. (bytes; 255 = unused)
 //   [8..]    direct gains, slot pairs:  (g0[2i], g0[2i+1], dg[2i], dg[2i+1]),  i = 0 .. kMixSlots/2 - 1
 //   then     diffuse gains, same layout (objects only)
 // Key: bit 31 dense | loudspeaker mask << 1 | has_diffuse.
@@ -499,10 +499,13 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
   }
   const float *gd = (obj ? p.g_dir : p.g_ds) + (size_t)k * L * ld + ci;   // [slot k: L rows][slot k+1: L rows]
   const float *gq = p.g_dif + (size_t)k * L * ld + ci;
-  // one pass over the loudspeakers, eight at a time (their table entries are loaded before any is
-  // tested); a non-zero one takes the next slot and its (start, delta) pairs go straight to the record
+  // one pass over the loudspeakers from the last to the first, eight at a time (their table entries are
+  // loaded before any is tested); a non-zero one takes the next slot and its (start, delta) pairs go
+  // straight to the record.  Slots are in DESCENDING loudspeaker order: the channels are sorted by the
+  // mask as a number, so neighbours in the sorted order share their highest loudspeakers, i.e. their
+  // first slots, which mix_kernel then keeps accumulating across the run boundary.
   unsigned mask = 0u, any_q = 0u, cnt = 0u, spk[2] = {0u, 0u};
-  for (int l0 = 0; l0 < L; l0 += 8) {
+  for (int l0 = (L - 1) & ~7; l0 >= 0; l0 -= 8) {
     float va[8], vb[8], qa[8], qb[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) {
@@ -511,7 +514,7 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
       qa[i] = obj ? gq[(size_t)l * ld] : 0.f; qb[i] = obj ? gq[(size_t)(L + l) * ld] : 0.f;
     }
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
+    for (int i = 7; i >= 0; i--) {
       if (l0 + i < L) {
         const bool nzq = qa[i] != 0.f || qb[i] != 0.f;
         if (va[i] != 0.f || vb[i] != 0.f || nzq) {
@@ -536,6 +539,7 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
     return;
   }
   keys[c] = mask << 1 | any_q;
+  for (unsigned s = cnt; s < (unsigned)kMixSlots; s++) spk[s >> 2] |= 0xffu << (8 * (s & 3u));   // 255: slot not needed
   reinterpret_cast<uint4 *>(rec)[1] = make_uint4(cnt | any_q << 8, spk[0], spk[1], 0u);
   for (unsigned s = cnt; s < (unsigned)kMixSlots; s++) {   // unused slots hold zero gains
     float *e = rec + 8 + 4 * (s >> 1) + (s & 1u);
@@ -668,34 +672,46 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
   for (int i = 0; i < kMixSlots; i++) acc[i] = 0ull;
 #pragma unroll
   for (int i = 0; i < kMixSlots / 2; i++) accQ[i] = 0ull;
-  unsigned nact = 0u, spk_lo = 0u, spk_hi = 0u;   // slots in use and their loudspeakers (same in all threads)
+  unsigned slot_spk[kMixSlots];                   // loudspeaker a slot is summing for, 255 = none (same in all threads)
+#pragma unroll
+  for (int i = 0; i < kMixSlots; i++) slot_spk[i] = 255u;
   int run_left = 0;                               // channels of the current run still to come
-  bool qdirty = false;
-  // end of a run: the slot sums are added to the bus rows of their loudspeakers with reductions
-  // (red.global.add: nothing comes back, so the thread does not wait for L2; every address belongs to
-  // one thread, whose stores and reductions to it are performed in program order -- the result does not
-  // depend on timing)
-  auto flush = [&]() {
+  unsigned qdirty = 0u;                           // slots that have seen a channel with diffuse gains
+  // A slot is closed when the next run needs it for another loudspeaker (and at the end): its sums are
+  // added to the bus rows of its loudspeaker with reductions (red.global.add: nothing comes back, so the
+  // thread does not wait for L2; every address belongs to one thread, whose stores and reductions to it
+  // are performed in program order -- the result does not depend on timing).  Slots whose loudspeaker
+  // the next run shares, or which it does not use, simply go on.
+  auto close_slot = [&](int i) {
+    const unsigned l = slot_spk[i];
+    float vL, vR;
+    unpack2(acc[i], vL, vR);
+    float *pd = od + (size_t)(2 * l) * os;
+    atomicAdd(pd, vL);
+    atomicAdd(pd + os, vR);
+    if (qdirty >> i & 1u) {
+      float qa, qb;
+      unpack2(accQ[i >> 1], qa, qb);
+      atomicAdd(oq + (size_t)l * os, (i & 1) ? qb : qa);
+      accQ[i >> 1] = (i & 1) ? pack2(qa, 0.f) : pack2(0.f, qb);
+      qdirty &= ~(1u << i);
+    }
+    acc[i] = 0ull;
+  };
+  auto retarget = [&](unsigned spk_lo, unsigned spk_hi) {
 #pragma unroll
     for (int i = 0; i < kMixSlots; i++) {
-      if (i < (int)nact) {
-        const unsigned l = ((i < 4 ? spk_lo : spk_hi) >> (8 * (i & 3))) & 0xffu;
-        float vL, vR;
-        unpack2(acc[i], vL, vR);
-        float *pd = od + (size_t)(2 * l) * os;
-        atomicAdd(pd, vL);
-        atomicAdd(pd + os, vR);
-        if (qdirty) {
-          float qa, qb;
-          unpack2(accQ[i >> 1], qa, qb);
-          atomicAdd(oq + (size_t)l * os, (i & 1) ? qb : qa);
-        }
+      const unsigned want = ((i < 4 ? spk_lo : spk_hi) >> (8 * (i & 3))) & 0xffu;
+      if (want != 255u && want != slot_spk[i]) {
+        if (slot_spk[i] != 255u) close_slot(i);
+        slot_spk[i] = want;
       }
-      acc[i] = 0ull;
     }
+  };
+  auto flush = [&]() {
 #pragma unroll
-    for (int i = 0; i < kMixSlots / 2; i++) accQ[i] = 0ull;
-    qdirty = false;
+    for (int i = 0; i < kMixSlots; i++)
+      if (slot_spk[i] != 255u) close_slot(i);
   };
 
   const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
@@ -760,10 +776,9 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
     const float *rec = rc0 + st * kMixChunk * kMixRecWords;
     f32x2 x2n = lagrange(rec, xr);
     for (int j = 0; j < cnt;) {
-      if (run_left == 0) {   // a new loudspeaker set: close the run, take the slot map and length of this one
-        flush();
+      if (run_left == 0) {   // a new loudspeaker set: re-target the slots that change, take the run's length
         const uint4 meta = *reinterpret_cast<const uint4 *>(rec + 4);
-        nact = meta.x & 0xffu; spk_lo = meta.y; spk_hi = meta.z;
+        retarget(meta.y, meta.z);
         run_left = (int)(sord[st][j] >> 17 & 0xfffu) + 1;
       }
       const int jend = min(cnt, j + run_left);
@@ -783,7 +798,7 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
         }
         if (sord[st][j] >> 30 & 1u) {
           const f32x2 x0 = splat2(xr[0]);
-          qdirty = true;
+          qdirty = (1u << kMixSlots) - 1u;
 #pragma unroll
           for (int i = 0; i < kMixSlots / 2; i++) {
             const float4 q = r4[2 + kMixSlots / 2 + i];
