@@ -167,7 +167,7 @@ struct bear_cuda_renderer {
   cudaStream_t result_stream = nullptr;    // the stream a chunk's output is complete on (render stream, or conv_stream)
   std::vector<cudaEvent_t> mix_events;     // one per chunk: its bus rows are written
   cudaEvent_t ev_call = nullptr;
-  int shared_chunks = 4;                   // chunks a shared-scene call is cut into (BEAR_CUDA_SHARED_CHUNKS overrides)
+  int shared_chunks = 1;                   // chunks a shared-scene call is cut into (BEAR_CUDA_SHARED_CHUNKS overrides)
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -661,10 +661,14 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   };
   if (chunk <= 0 || chunk > T) chunk = T;
   const bool shared_scene = p.W > 1;
-  // A shared scene is issued in at least four chunks: the exchange (ordering collective, gather of the
-  // peers' rows over NVLink) and the convolution of chunk c then run on a second stream under the mix of
-  // chunk c+1 -- the mix keeps the SMs busy, the gather the NVLink ports.  (Per-kernel profiling keeps
-  // everything on one stream so that its event pairs mean something.)
+  // A shared scene that is issued in chunks (chunk_blocks, the upload chunks of the host-buffer calls, or
+  // BEAR_CUDA_SHARED_CHUNKS) runs the exchange (ordering collective, gather of the peers' rows over
+  // NVLink) and the convolution of chunk c on a second stream under the mix of chunk c+1 -- the mix keeps
+  // the SMs busy, the gather the NVLink ports.  A device-resident call is NOT cut into chunks by default:
+  // measured at 1024 objects on 2 and 8 GPUs, every kernel loses more to the shorter launches (and the
+  // convolution to fewer periods per BRIR view) than the overlap returns (1.71 -> 1.78 / 2.00 ms for 2 / 4
+  // chunks on 2 GPUs; 0.847 -> 0.845 / 0.987 ms on 8).  (Per-kernel profiling keeps everything on one
+  // stream so that its event pairs mean something.)
   if (shared_scene && chunk == T && T >= 64 && r->shared_chunks > 1)
     chunk = (int)round_up((size_t)(T + r->shared_chunks - 1) / r->shared_chunks, 8);
   const int nchunks_total = (T + chunk - 1) / chunk;

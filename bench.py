@@ -527,9 +527,9 @@ def run_ours(args, rank, world, local_rank):
                 "nvlink_bytes_read_per_rank_per_step": int(3 * nl * fB * (world - 1)),
                 "nccl_reduce_bytes_per_step": int(2 * fB),
                 "ms_per_step": sum(v[0] for k, v in prof.items() if k == "exchange") / max(args.steps, 1),
-                "note": "exchange = the one-word NCCL all-reduce that orders the ranks before the rows are read + the "
-                        "NCCL reduce of the stereo partial mixes (CUDA events on rank 0's stream: includes waiting for "
-                        "the slowest rank); bus_gather_kernel is counted under mix_aux_kernels"}
+                "note": "exchange = the one-word NCCL all-reduce that orders the ranks (includes waiting for the "
+                        "slowest rank's mix) + bus_gather_kernel (the peers' rows over NVLink) + the NCCL reduce of the "
+                        "stereo partial mixes; CUDA events on rank 0's stream in the per-kernel pass"}
         line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_single(args)
