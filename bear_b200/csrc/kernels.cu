@@ -499,13 +499,8 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
   }
   const float *gd = (obj ? p.g_dir : p.g_ds) + (size_t)k * L * ld + ci;   // [slot k: L rows][slot k+1: L rows]
   const float *gq = p.g_dif + (size_t)k * L * ld + ci;
-  // one pass over the loudspeakers from the last to the first, eight at a time (their table entries are
-  // loaded before any is tested); a non-zero one takes the next slot and its (start, delta) pairs go
-  // straight to the record.  Slots are in DESCENDING loudspeaker order: the channels are sorted by the
-  // mask as a number, so neighbours in the sorted order share their highest loudspeakers, i.e. their
-  // first slots, which mix_kernel then keeps accumulating across the run boundary.
-  unsigned mask = 0u, any_q = 0u, cnt = 0u, spk[2] = {0u, 0u};
-  for (int l0 = (L - 1) & ~7; l0 >= 0; l0 -= 8) {
+  unsigned mask = 0u, any_q = 0u;
+  for (int l0 = 0; l0 < L; l0 += 8) {   // eight loudspeakers' table entries are loaded before any is tested
     float va[8], vb[8], qa[8], qb[8];
 #pragma unroll
     for (int i = 0; i < 8; i++) {
@@ -514,36 +509,53 @@ __global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
       qa[i] = obj ? gq[(size_t)l * ld] : 0.f; qb[i] = obj ? gq[(size_t)(L + l) * ld] : 0.f;
     }
 #pragma unroll
-    for (int i = 7; i >= 0; i--) {
+    for (int i = 0; i < 8; i++) {
       if (l0 + i < L) {
         const bool nzq = qa[i] != 0.f || qb[i] != 0.f;
-        if (va[i] != 0.f || vb[i] != 0.f || nzq) {
-          mask |= 1u << (l0 + i);
-          if (cnt < (unsigned)kMixSlots) {
-            float *e = rec + 8 + 4 * (cnt >> 1) + (cnt & 1u);     // pair layout: (g0[2i], g0[2i+1], dg[2i], dg[2i+1])
-            e[0] = va[i]; e[2] = vb[i] - va[i];
-            e[2 * kMixSlots] = qa[i]; e[2 * kMixSlots + 2] = qb[i] - qa[i];
-            spk[cnt >> 2] |= (unsigned)(l0 + i) << (8 * (cnt & 3u));
-          }
-          cnt++;
-        }
+        if (va[i] != 0.f || vb[i] != 0.f || nzq) mask |= 1u << (l0 + i);
         if (nzq) any_q = 1u;
       }
     }
   }
+  const int ns = __popc(mask);
   unsigned *keys = p.mix_keys + (size_t)k * C;
-  reinterpret_cast<float4 *>(rec)[0] = dl;
-  if (cnt > (unsigned)kMixSlots) {
+  if (ns > kMixSlots) {
     keys[c] = 0x80000000u | any_q;
+    reinterpret_cast<float4 *>(rec)[0] = dl;
     reinterpret_cast<uint4 *>(rec)[1] = make_uint4(255u | any_q << 8, 0u, 0u, 0u);
     return;
   }
   keys[c] = mask << 1 | any_q;
-  for (unsigned s = cnt; s < (unsigned)kMixSlots; s++) spk[s >> 2] |= 0xffu << (8 * (s & 3u));   // 255: slot not needed
-  reinterpret_cast<uint4 *>(rec)[1] = make_uint4(cnt | any_q << 8, spk[0], spk[1], 0u);
-  for (unsigned s = cnt; s < (unsigned)kMixSlots; s++) {   // unused slots hold zero gains
-    float *e = rec + 8 + 4 * (s >> 1) + (s & 1u);
-    e[0] = 0.f; e[2] = 0.f; e[2 * kMixSlots] = 0.f; e[2 * kMixSlots + 2] = 0.f;
+  // Slots in DESCENDING loudspeaker order: the channels are sorted by the mask as a number, so neighbours
+  // in the sorted order share their highest loudspeakers, i.e. their first slots, which mix_kernel can
+  // keep accumulating across a run boundary.  (The second, gathering pass re-reads <= 6 x 4 entries that
+  // the first left in L1; writing them out of the first pass with scattered stores measured slower.)
+  float g0[kMixSlots], dg[kMixSlots], q0[kMixSlots], dq[kMixSlots];
+  unsigned spk[2] = {0u, 0u};
+  unsigned m = mask;
+#pragma unroll
+  for (int s = 0; s < kMixSlots; s++) {
+    g0[s] = dg[s] = q0[s] = dq[s] = 0.f;
+    unsigned l = 255u;                       // 255: slot not needed
+    if (m) {
+      l = 31u - (unsigned)__clz(m);
+      m &= ~(1u << l);
+      const float a = gd[(size_t)l * ld], b = gd[(size_t)(L + l) * ld];
+      g0[s] = a; dg[s] = b - a;
+      if (obj) {
+        const float qa = gq[(size_t)l * ld], qb = gq[(size_t)(L + l) * ld];
+        q0[s] = qa; dq[s] = qb - qa;
+      }
+    }
+    spk[s >> 2] |= l << (8 * (s & 3));
+  }
+  float4 *r4 = reinterpret_cast<float4 *>(rec);
+  r4[0] = dl;
+  reinterpret_cast<uint4 *>(rec)[1] = make_uint4((unsigned)ns | any_q << 8, spk[0], spk[1], 0u);
+#pragma unroll
+  for (int i = 0; i < kMixSlots / 2; i++) {
+    r4[2 + i] = make_float4(g0[2 * i], g0[2 * i + 1], dg[2 * i], dg[2 * i + 1]);
+    r4[2 + kMixSlots / 2 + i] = make_float4(q0[2 * i], q0[2 * i + 1], dq[2 * i], dq[2 * i + 1]);
   }
 }
 
@@ -634,6 +646,10 @@ constexpr int kMixStages = BEAR_MIX_STAGES;      // chunks in flight: the one be
 #ifndef BEAR_MIX_MINBLOCKS
 #define BEAR_MIX_MINBLOCKS 7
 #endif
+// KEEP: at a run boundary only the slots whose loudspeaker changes are closed (worth it when runs are
+// short: few channels per CTA); otherwise all slots are closed and start from zero (cheaper per run
+// boundary when runs are long -- measured 1.94 against 2.05 ms at 1024 channels per CTA).
+template <bool KEEP>
 __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layout p, int T)
 {
   extern __shared__ __align__(16) float smx[];
@@ -702,10 +718,17 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
 #pragma unroll
     for (int i = 0; i < kMixSlots; i++) {
       const unsigned want = ((i < 4 ? spk_lo : spk_hi) >> (8 * (i & 3))) & 0xffu;
-      if (want != 255u && want != slot_spk[i]) {
+      if (KEEP ? (want != 255u && want != slot_spk[i]) : true) {
         if (slot_spk[i] != 255u) close_slot(i);
         slot_spk[i] = want;
       }
+    }
+    if (!KEEP) {   // every slot starts the run from zero, whatever the branches above did
+#pragma unroll
+      for (int i = 0; i < kMixSlots; i++) acc[i] = 0ull;
+#pragma unroll
+      for (int i = 0; i < kMixSlots / 2; i++) accQ[i] = 0ull;
+      qdirty = 0u;
     }
   };
   auto flush = [&]() {
@@ -1000,7 +1023,9 @@ void launch_mix_prep(const Layout &p, int T, cudaStream_t st)
 void launch_mix(const Layout &p, int T, cudaStream_t st)
 {
   dim3 grid(T * p.B / kMixTile, p.S);
-  mix_kernel<<<grid, kMixTile, mix_smem_bytes(p.hist), st>>>(p, T);
+  const int per = (p.N + p.M + p.S - 1) / p.S;   // channels per CTA
+  if (per <= 256) mix_kernel<true><<<grid, kMixTile, mix_smem_bytes(p.hist), st>>>(p, T);
+  else mix_kernel<false><<<grid, kMixTile, mix_smem_bytes(p.hist), st>>>(p, T);
   mix_dense_kernel<<<T * p.B / kMixTile, kMixTile, mix_dense_smem_bytes(p.hist), st>>>(p, T);
 }
 void launch_bus_sum(const Layout &p, int T, cudaStream_t st)   // only launches with S > 1
@@ -2071,7 +2096,9 @@ static int ilog2(int v)
 
 cudaError_t configure_mix(int hist, int B)
 {
-  cudaError_t e = cudaFuncSetAttribute(mix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
+  cudaError_t e = cudaFuncSetAttribute(mix_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(mix_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_smem_bytes(hist));
   if (e != cudaSuccess) return e;
   e = cudaFuncSetAttribute(mix_dense_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)mix_dense_smem_bytes(hist));
   if (e != cudaSuccess) return e;
