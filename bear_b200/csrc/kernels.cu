@@ -688,18 +688,18 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
   for (int i = 0; i < kMixSlots; i++) acc[i] = 0ull;
 #pragma unroll
   for (int i = 0; i < kMixSlots / 2; i++) accQ[i] = 0ull;
-  unsigned slot_spk[kMixSlots];                   // loudspeaker a slot is summing for, 255 = none (same in all threads)
+  // Slot state, the same in all threads.  KEEP: the loudspeaker of every slot (255 = none); otherwise the
+  // number of slots in use and their loudspeakers as the record packs them.
+  unsigned slot_spk[kMixSlots];
 #pragma unroll
   for (int i = 0; i < kMixSlots; i++) slot_spk[i] = 255u;
+  unsigned nact = 0u, cur_lo = 0u, cur_hi = 0u;
   int run_left = 0;                               // channels of the current run still to come
   unsigned qdirty = 0u;                           // slots that have seen a channel with diffuse gains
-  // A slot is closed when the next run needs it for another loudspeaker (and at the end): its sums are
-  // added to the bus rows of its loudspeaker with reductions (red.global.add: nothing comes back, so the
-  // thread does not wait for L2; every address belongs to one thread, whose stores and reductions to it
-  // are performed in program order -- the result does not depend on timing).  Slots whose loudspeaker
-  // the next run shares, or which it does not use, simply go on.
-  auto close_slot = [&](int i) {
-    const unsigned l = slot_spk[i];
+  // Slot sums are added to the bus rows of their loudspeaker with reductions (red.global.add: nothing
+  // comes back, so the thread does not wait for L2; every address belongs to one thread, whose stores and
+  // reductions to it are performed in program order -- the result does not depend on timing).
+  auto close_slot = [&](int i, unsigned l) {
     float vL, vR;
     unpack2(acc[i], vL, vR);
     float *pd = od + (size_t)(2 * l) * os;
@@ -709,21 +709,20 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
       float qa, qb;
       unpack2(accQ[i >> 1], qa, qb);
       atomicAdd(oq + (size_t)l * os, (i & 1) ? qb : qa);
-      accQ[i >> 1] = (i & 1) ? pack2(qa, 0.f) : pack2(0.f, qb);
-      qdirty &= ~(1u << i);
-    }
-    acc[i] = 0ull;
-  };
-  auto retarget = [&](unsigned spk_lo, unsigned spk_hi) {
-#pragma unroll
-    for (int i = 0; i < kMixSlots; i++) {
-      const unsigned want = ((i < 4 ? spk_lo : spk_hi) >> (8 * (i & 3))) & 0xffu;
-      if (KEEP ? (want != 255u && want != slot_spk[i]) : true) {
-        if (slot_spk[i] != 255u) close_slot(i);
-        slot_spk[i] = want;
+      if (KEEP) {
+        accQ[i >> 1] = (i & 1) ? pack2(qa, 0.f) : pack2(0.f, qb);
+        qdirty &= ~(1u << i);
       }
     }
-    if (!KEEP) {   // every slot starts the run from zero, whatever the branches above did
+    if (KEEP) acc[i] = 0ull;
+  };
+  // all slots in use are closed and start from zero
+  auto close_all = [&]() {
+#pragma unroll
+    for (int i = 0; i < kMixSlots; i++)
+      if (KEEP ? slot_spk[i] != 255u : i < (int)nact)
+        close_slot(i, KEEP ? slot_spk[i] : ((i < 4 ? cur_lo : cur_hi) >> (8 * (i & 3))) & 0xffu);
+    if (!KEEP) {
 #pragma unroll
       for (int i = 0; i < kMixSlots; i++) acc[i] = 0ull;
 #pragma unroll
@@ -731,11 +730,24 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
       qdirty = 0u;
     }
   };
-  auto flush = [&]() {
+  // a run with a new loudspeaker set begins.  KEEP: a slot is closed only if the run needs it for another
+  // loudspeaker; slots whose loudspeaker it shares, or which it does not use, simply go on
+  auto retarget = [&](const uint4 meta) {
+    if (KEEP) {
 #pragma unroll
-    for (int i = 0; i < kMixSlots; i++)
-      if (slot_spk[i] != 255u) close_slot(i);
+      for (int i = 0; i < kMixSlots; i++) {
+        const unsigned want = ((i < 4 ? meta.y : meta.z) >> (8 * (i & 3))) & 0xffu;
+        if (want != 255u && want != slot_spk[i]) {
+          if (slot_spk[i] != 255u) close_slot(i, slot_spk[i]);
+          slot_spk[i] = want;
+        }
+      }
+    } else {
+      close_all();
+      nact = meta.x & 0xffu; cur_lo = meta.y; cur_hi = meta.z;
+    }
   };
+  auto flush = [&]() { close_all(); };
 
   const unsigned bar0 = (unsigned)__cvta_generic_to_shared(&bars[0]);
   if (tid == 0) {
@@ -800,8 +812,7 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
     f32x2 x2n = lagrange(rec, xr);
     for (int j = 0; j < cnt;) {
       if (run_left == 0) {   // a new loudspeaker set: re-target the slots that change, take the run's length
-        const uint4 meta = *reinterpret_cast<const uint4 *>(rec + 4);
-        retarget(meta.y, meta.z);
+        retarget(*reinterpret_cast<const uint4 *>(rec + 4));
         run_left = (int)(sord[st][j] >> 17 & 0xfffu) + 1;
       }
       const int jend = min(cnt, j + run_left);
