@@ -397,15 +397,18 @@ __device__ __forceinline__ f32x2 delayed_read2(const float *__restrict__ xa, flo
   const float ua = __fadd_rd(ha, 8388608.0f), ub = __fadd_rd(hb, 8388608.0f);
   const float fa = ua - 8388608.0f, fb = ub - 8388608.0f;
   const int ia = __float_as_int(ua) & 0x7fffff, ib = __float_as_int(ub) & 0x7fffff;
-  const f32x2 s = add2(splat2(1.5f), sub2(d, pack2(fa, fb)));
-  // c0 = -(s-1)(s-2)(s-3)/6, c1 = s(s-2)(s-3)/2, c2 = -s(s-1)(s-3)/2, c3 = s(s-1)(s-2)/6 with the shared
-  // factors a = s(s-3) and b = (s-1)(s-2) taken out: 10 packed operations for the eight coefficients
-  const f32x2 s1 = add2(s, splat2(-1.0f)), s2 = add2(s, splat2(-2.0f)), s3 = add2(s, splat2(-3.0f));
-  const f32x2 a = mul2(s, s3), b = mul2(s1, s2);
-  const f32x2 c0 = mul2(b, mul2(s3, splat2(-1.0f / 6.0f)));
-  const f32x2 c1 = mul2(a, mul2(s2, splat2(0.5f)));
-  const f32x2 c2 = mul2(a, mul2(s1, splat2(-0.5f)));
-  const f32x2 c3 = mul2(b, mul2(s, splat2(1.0f / 6.0f)));
+  // position among the four nodes: s = 1.5 + mu with mu = d - floor(d + .5) in [-.5, .5).  With m2 = mu^2,
+  // s (s-3) = m2 - 2.25 and (s-1)(s-2) = m2 - 0.25, so
+  //   c0 = -(s-1)(s-2)(s-3)/6 = (m2 - .25) (.25 - mu/6)      c1 =  s(s-2)(s-3)/2 = (m2 - 2.25) (mu/2 - .25)
+  //   c3 =  s(s-1)(s-2)/6     = (m2 - .25) (.25 + mu/6)      c2 = -s(s-1)(s-3)/2 = (m2 - 2.25) (-mu/2 - .25)
+  // : 12 packed operations for the eight coefficients of both ears
+  const f32x2 mu = sub2(d, pack2(fa, fb));
+  const f32x2 m2 = mul2(mu, mu);
+  const f32x2 a = add2(m2, splat2(-2.25f)), b = add2(m2, splat2(-0.25f));
+  const f32x2 c0 = mul2(b, fma2(mu, splat2(-1.0f / 6.0f), splat2(0.25f)));
+  const f32x2 c1 = mul2(a, fma2(mu, splat2(0.5f), splat2(-0.25f)));
+  const f32x2 c2 = mul2(a, fma2(mu, splat2(-0.5f), splat2(-0.25f)));
+  const f32x2 c3 = mul2(b, fma2(mu, splat2(1.0f / 6.0f), splat2(0.25f)));
   const float *qa = xa - ia, *qb = xb - ib;
   f32x2 acc = mul2(c0, pack2(qa[0], qb[0]));
   acc = fma2(c1, pack2(qa[-1], qb[-1]), acc);
