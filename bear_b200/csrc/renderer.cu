@@ -717,6 +717,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       // every rank's bus rows of this chunk are complete before anyone reads them
       mark(BEAR_CUDA_KERNEL_EXCHANGE);
       NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, sb));
+      mark(BEAR_CUDA_KERNEL_GATHER);
       launch_bus_gather(p, n, sb);
       if (p.l1 > p.l0) launches++;
     }
@@ -1514,7 +1515,7 @@ int bear_cuda_get_profile(bear_cuda_renderer *r, bear_cuda_kernel_profile *out, 
     static const char *names[BEAR_CUDA_NUM_KERNELS] = {"mix_kernel", "hoa_mix_kernel", "decorrelate_kernel",
                                                        "bus_fdl_kernel", "cmac_kernel", "ifft_out_kernel",
                                                        "carry_kernel", "control_kernel", "mix_aux_kernels",
-                                                       "exchange"};
+                                                       "exchange", "bus_gather_kernel"};
     for (int k = 0; k < BEAR_CUDA_NUM_KERNELS; k++) {
       std::snprintf(out[k].name, sizeof(out[k].name), "%s", names[k]);
       out[k].total_ms = r->prof_ms[k];
@@ -1596,6 +1597,8 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
     for (cudaEvent_t &e : r->mix_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     r->bus_sum = r->dalloc<float>((size_t)3 * p.L * p.cs);
     r->comm_root = root;
+    if (const char *env = std::getenv("BEAR_CUDA_COMM_ALLREDUCE"))   // experiments: all-reduce instead of reduce to the root
+      if (std::atoi(env)) r->comm_root = -1;
     uint32_t l0 = 0, l1 = 0;
     bear_cuda_comm_speaker_range(rank, world, (uint32_t)p.L, &l0, &l1);
     p.W = (int)world; p.rank = (int)rank; p.l0 = (int)l0; p.l1 = (int)l1;

@@ -97,7 +97,7 @@ EXPORTS = (
     "bear_cuda_comm_blob", "bear_cuda_comm_connect", "bear_cuda_comm_speaker_range",
 )
 STATIC_SCRATCH_BYTES = 4 << 20
-NUM_KERNELS = 10
+NUM_KERNELS = 11
 COMM_BLOB_BYTES = 256
 
 

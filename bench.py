@@ -527,9 +527,11 @@ def run_ours(args, rank, world, local_rank):
                 "nvlink_bytes_read_per_rank_per_step": int(3 * nl * fB * (world - 1)),
                 "nccl_reduce_bytes_per_step": int(2 * fB),
                 "ms_per_step": sum(v[0] for k, v in prof.items() if k == "exchange") / max(args.steps, 1),
-                "note": "exchange = the one-word NCCL all-reduce that orders the ranks (includes waiting for the "
-                        "slowest rank's mix) + bus_gather_kernel (the peers' rows over NVLink) + the NCCL reduce of the "
-                        "stereo partial mixes; CUDA events on rank 0's stream in the per-kernel pass"}
+                "gather_ms_per_step": sum(v[0] for k, v in prof.items() if k == "bus_gather_kernel") / max(args.steps, 1),
+                "note": "ms_per_step = the one-word NCCL all-reduce that orders the ranks (includes waiting for the "
+                        "slowest rank's mix) + the NCCL reduce of the stereo partial mixes; gather_ms_per_step = "
+                        "bus_gather_kernel (the peers' rows over NVLink); CUDA events on rank 0's stream in the "
+                        "per-kernel pass"}
         line.update(extras)
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_single(args)

@@ -306,8 +306,9 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
 #define BEAR_CUDA_KERNEL_CARRY 6
 #define BEAR_CUDA_KERNEL_CONTROL 7
 #define BEAR_CUDA_KERNEL_MIX_AUX 8   /* mix_prep_kernel (+ bus_sum_kernel in short launches) */
-#define BEAR_CUDA_KERNEL_EXCHANGE 9  /* cross-GPU barrier and stereo reduce of a shared scene (NCCL) */
-#define BEAR_CUDA_NUM_KERNELS 10
+#define BEAR_CUDA_KERNEL_EXCHANGE 9  /* cross-GPU ordering collective and stereo reduce of a shared scene (NCCL) */
+#define BEAR_CUDA_KERNEL_GATHER 10   /* bus_gather_kernel: the peers' bus rows over NVLink */
+#define BEAR_CUDA_NUM_KERNELS 11
 
 typedef struct bear_cuda_kernel_profile {
   char name[32];
