@@ -1942,8 +1942,9 @@ void launch_frames(const Layout &p, const void *frames, int format, int frame_ch
 
 void launch_carry(const CarryPlan &plan, cudaStream_t st)
 {
-  const long long cols = (long long)plan.fdl_channels * plan.fdl_B;
-  carry_kernel<<<plan.row_start[plan.n] + (int)((cols + 255) / 256), 256, 0, st>>>(plan);
+  const long long cols = (long long)plan.fdl_channels * plan.fdl_B;   // 0: a plan without the delay line
+  const int grid = plan.row_start[plan.n] + (int)((cols + 255) / 256);
+  if (grid > 0) carry_kernel<<<grid, 256, 0, st>>>(plan);
 }
 
 // ----------------------------------------------------------------------------------------------

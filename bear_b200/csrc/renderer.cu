@@ -168,6 +168,12 @@ struct bear_cuda_renderer {
   std::vector<cudaEvent_t> mix_events;     // one per chunk: its bus rows are written
   cudaEvent_t ev_call = nullptr;
   int shared_chunks = 1;                   // chunks a shared-scene call is cut into (BEAR_CUDA_SHARED_CHUNKS overrides)
+  // pipelined calls of a shared scene (bear_cuda_process_device_pipelined): the exchange + convolution of
+  // call s stay queued on conv_stream while the mix of call s+1 runs on the render stream
+  bool pipelined_pending = false;          // conv_stream holds work the render stream has not waited for
+  cudaEvent_t ev_barrier = nullptr;        // the ordering collective of the last pipelined call has completed
+  int32_t *sh_view[2] = {nullptr, nullptr};   // the convolution side's own copies of the view / static-delay tables
+  float *sh_dstat[2] = {nullptr, nullptr};
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -228,6 +234,7 @@ struct bear_cuda_renderer {
   {
     cudaSetDevice(device);
     if (stream) cudaStreamSynchronize(stream);
+    if (conv_stream) cudaStreamSynchronize(conv_stream);
     for (void *p : allocs) cudaFree(p);
     for (auto &c : ev_pending)
       for (cudaEvent_t e : c) cudaEventDestroy(e);
@@ -235,6 +242,7 @@ struct bear_cuda_renderer {
     if (comm) nccl().CommDestroy(comm);
     for (cudaEvent_t e : mix_events) cudaEventDestroy(e);
     if (ev_call) cudaEventDestroy(ev_call);
+    if (ev_barrier) cudaEventDestroy(ev_barrier);
     if (conv_stream) cudaStreamDestroy(conv_stream);
     for (int w = 0; w < kMaxRanks; w++)
       if (peer_bus[w][0] && w != lay.rank) cudaIpcCloseMemHandle(peer_bus[w][0]);
@@ -636,6 +644,17 @@ static size_t table_bytes_per_period(const Layout &p)
   return sizeof(float) * ((size_t)2 * p.L * p.N + 2 * p.N + (size_t)p.L * p.M + 2 * p.M + 2 * p.L + (size_t)p.A * p.H + 1);
 }
 
+// After pipelined calls the convolution side may still be running on conv_stream: every other entry
+// point first makes the render stream wait for it, and is then what it always was.
+void join_pipelined(bear_cuda_renderer *r)
+{
+  if (!r->pipelined_pending) return;
+  CK(cudaEventRecord(r->ev_call, r->conv_stream));
+  CK(cudaStreamWaitEvent(r->stream, r->ev_call, 0));
+  r->pipelined_pending = false;
+  r->result_stream = r->stream;
+}
+
 // Queue the kernels for T blocks whose audio and tables are already in the staging areas.
 // A call may be issued in chunks of `chunk` periods (all kernels of chunk c, then chunk c+1, ...;
 // chunk <= 0: all at once): every intermediate buffer is indexed by the period number within the
@@ -644,10 +663,14 @@ static size_t table_bytes_per_period(const Layout &p)
 // `after_chunk(c, k0, n)` after it.  Nothing here allocates unless per-kernel profiling is on.
 template <class Before, class After>
 void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk, After &&after_chunk,
-                  bool device_tables = false)
+                  bool device_tables = false, bool pipelined = false)
 {
   Layout &p = r->lay;
   cudaStream_t st = r->stream;
+  // pipelined: the convolution side of this call is left running when the call returns (one chunk, no HOA
+  // bus on this rank -- its history would be shared by both sides --, no per-kernel profiling)
+  const bool pipe = pipelined && p.W > 1 && p.H == 0 && !r->profiling && (chunk <= 0 || chunk >= T);
+  if (!pipe) join_pipelined(r);
   std::vector<cudaEvent_t> chain;
   std::vector<int> ids;
   auto mark = [&](int kernel_id) {
@@ -672,10 +695,11 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   if (shared_scene && chunk == T && T >= 64 && r->shared_chunks > 1)
     chunk = (int)round_up((size_t)(T + r->shared_chunks - 1) / r->shared_chunks, 8);
   const int nchunks_total = (T + chunk - 1) / chunk;
-  const bool overlap = shared_scene && !r->profiling && r->conv_stream && nchunks_total > 1 &&
-                       nchunks_total <= (int)r->mix_events.size();
+  const bool overlap = pipe || (shared_scene && !r->profiling && r->conv_stream && nchunks_total > 1 &&
+                                nchunks_total <= (int)r->mix_events.size());
   cudaStream_t sb = overlap ? r->conv_stream : st;   // exchange + convolution side
   r->result_stream = sb;
+  Layout pc = p;   // what the convolution side sees (filled in below)
   // bus rows of this call; a renderer that shares a scene alternates between its two sets, so that a
   // peer still reading the previous call's rows is never overwritten (one barrier per chunk suffices)
   float *const bus = r->bus[r->parity];
@@ -693,7 +717,16 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   p.bps = (size_t)chunk * p.B;
   uint64_t launches = 0;
   if (device_tables) { launch_validate_views(p, T, st); launches++; }
-  if (overlap) {   // the convolution side starts after everything queued so far (the previous call's carry)
+  if (pipe) {
+    // the bus rows this call writes were read by the peers two calls ago: their gathers are over once the
+    // ordering collective of the previous call has completed here
+    if (r->pipelined_pending) CK(cudaStreamWaitEvent(st, r->ev_barrier, 0));
+    // the convolution side works on its own copies of the tables it reads, so that the caller may write
+    // the next call's tables as soon as this call has been queued
+    const int par = r->parity;
+    CK(cudaMemcpyAsync(r->sh_view[par], p.view, (size_t)(T + 1) * sizeof(int32_t), cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(r->sh_dstat[par], p.d_stat, (size_t)(T + 2) * 2 * p.L * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  } else if (overlap) {   // the convolution side starts after everything queued so far (the previous call's carry)
     CK(cudaEventRecord(r->ev_call, st));
     CK(cudaStreamWaitEvent(sb, r->ev_call, 0));
   }
@@ -713,22 +746,23 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       CK(cudaEventRecord(r->mix_events[nchunks], st));
       CK(cudaStreamWaitEvent(sb, r->mix_events[nchunks], 0));
     }
+    pc = p;
+    if (pipe) { pc.view = r->sh_view[r->parity]; pc.d_stat = r->sh_dstat[r->parity]; }
     if (shared_scene) {
       // every rank's bus rows of this chunk are complete before anyone reads them
       mark(BEAR_CUDA_KERNEL_EXCHANGE);
       NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, sb));
+      if (pipe) CK(cudaEventRecord(r->ev_barrier, sb));
       mark(BEAR_CUDA_KERNEL_GATHER);
-      launch_bus_gather(p, n, sb);
+      launch_bus_gather(pc, n, sb);
       if (p.l1 > p.l0) launches++;
     }
-    if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(p, n, sb); launches++; }
-    if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(p, n, sb); launches++; }
-    p.KS = cmac_splits_for(r, n);
-    p.ks_dev = cmac_groups_by_view(p, n);
-    mark(BEAR_CUDA_KERNEL_CMAC); launches += launch_cmac(p, n, sb);
-    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(p, n, sb); launches++;
-    p.KS = r->ks_cfg;
-    p.ks_dev = 0;
+    if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(pc, n, sb); launches++; }
+    if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(pc, n, sb); launches++; }
+    pc.KS = cmac_splits_for(r, n);
+    pc.ks_dev = cmac_groups_by_view(pc, n);
+    mark(BEAR_CUDA_KERNEL_CMAC); launches += launch_cmac(pc, n, sb);
+    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(pc, n, sb); launches++;
     if (shared_scene) {
       // the stereo partial mixes of the ranks are summed (north_star: "only per-block stereo partial
       // mixes are summed with NCCL"), chunk by chunk so that the sum of chunk c runs under chunk c+1
@@ -747,33 +781,43 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
     k0 += n;
   }
   p.k0 = 0;
-  if (overlap) {   // the carry moves state both sides use: it follows both
+  if (overlap && !pipe) {   // the carry moves state both sides use: it follows both
     CK(cudaEventRecord(r->ev_call, sb));
     CK(cudaStreamWaitEvent(st, r->ev_call, 0));
   }
   mark(BEAR_CUDA_KERNEL_CARRY);
 
-  CarryPlan plan{};
-  int n = 0, rows = 0;
-  auto add = [&](float *base, int nrows, long long stride, int count, long long shift) {
+  // Two groups of state: what the mix side reads (input history, the tables' last period) and what the
+  // convolution side reads (bus prefix, decorrelator outputs, delay line).  Normally one kernel moves
+  // both; a pipelined call moves each on its own stream.
+  CarryPlan plan{}, plan_conv{};
+  int n = 0, rows = 0, nc = 0, rows_c = 0;
+  auto add_to = [&](CarryPlan &pl, int &cnt, int &nrows_total, float *base, int nrows, long long stride, int count, long long shift) {
     if (nrows <= 0 || count <= 0) return;
-    plan.e[n] = CarryRow{base, nrows, stride, count, shift};
-    plan.row_start[n] = rows;
-    rows += nrows;
-    n++;
+    pl.e[cnt] = CarryRow{base, nrows, stride, count, shift};
+    pl.row_start[cnt] = nrows_total;
+    nrows_total += nrows;
+    cnt++;
+  };
+  auto add = [&](float *base, int nrows, long long stride, int count, long long shift) {
+    add_to(plan, n, rows, base, nrows, stride, count, shift);
+  };
+  auto add_conv = [&](float *base, int nrows, long long stride, int count, long long shift) {
+    if (pipe) add_to(plan_conv, nc, rows_c, base, nrows, stride, count, shift);
+    else add_to(plan, n, rows, base, nrows, stride, count, shift);
   };
   const long long TB = (long long)T * p.B;
   add(p.xin, p.N + p.M + p.H, (long long)p.xs, p.hist, TB);
   if (shared_scene) {
     // the last period of the gathered rows is the overlap-save prefix of the next call (the rows the
     // peers read have no history: every call's columns are gathered once)
-    add(r->bus_sum + (size_t)2 * p.l0 * p.cs, 2 * (p.l1 - p.l0), (long long)p.cs, p.B, TB);
-    if (p.dif) add(r->bus_sum + (size_t)(2 * p.L + p.l0) * p.cs, p.l1 - p.l0, (long long)p.cs, p.B, TB);
+    add_conv(r->bus_sum + (size_t)2 * p.l0 * p.cs, 2 * (p.l1 - p.l0), (long long)p.cs, p.B, TB);
+    if (p.dif) add_conv(r->bus_sum + (size_t)(2 * p.L + p.l0) * p.cs, p.l1 - p.l0, (long long)p.cs, p.B, TB);
   } else {
     if (p.N + p.M > 0) add(bus, 2 * p.L, (long long)p.cs, p.B, TB);
     if (p.N > 0) add(bus + (size_t)2 * p.L * p.cs, p.L, (long long)p.cs, p.B, TB);
   }
-  if (p.dif) add(p.w, p.L, (long long)p.ws, p.B + p.hist, TB);
+  if (p.dif) add_conv(p.w, p.L, (long long)p.ws, p.B + p.hist, TB);
   if (p.H > 0) {
     add(p.amb, p.A, (long long)p.ws, p.B + p.hist, TB);
     add(p.g_hoa, 1, 0, p.A * p.H, (long long)T * p.A * p.H);
@@ -791,14 +835,22 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   add(reinterpret_cast<float *>(p.view), 1, 0, 1, T);
   plan.n = n;
   plan.row_start[n] = rows;
-  plan.fdl = p.fdl;
-  plan.fdl_stride = (long long)p.R * p.B;
-  plan.fdl_channels = p.CH;
-  plan.fdl_B = p.B;
-  plan.fdl_P = p.P;
-  plan.fdl_T = T;
+  CarryPlan &fdl_plan = pipe ? plan_conv : plan;
+  fdl_plan.fdl = p.fdl;
+  fdl_plan.fdl_stride = (long long)p.R * p.B;
+  fdl_plan.fdl_channels = p.CH;
+  fdl_plan.fdl_B = p.B;
+  fdl_plan.fdl_P = p.P;
+  fdl_plan.fdl_T = T;
   launch_carry(plan, st);
   launches++;
+  if (pipe) {
+    plan_conv.n = nc;
+    plan_conv.row_start[nc] = rows_c;
+    launch_carry(plan_conv, sb);
+    launches++;
+    r->pipelined_pending = true;
+  }
   mark(-1);
   if (r->profiling) {
     r->ev_pending.push_back(std::move(chain));
@@ -810,15 +862,16 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   if (shared_scene) r->parity ^= 1;
 }
 
-void run_pipeline(bear_cuda_renderer *r, int T, bool device_tables = false)
+void run_pipeline(bear_cuda_renderer *r, int T, bool device_tables = false, bool pipelined = false)
 {
-  run_pipeline(r, T, r->chunk, [](int, int, int) {}, [](int, int, int) {}, device_tables);
+  run_pipeline(r, T, r->chunk, [](int, int, int) {}, [](int, int, int) {}, device_tables, pipelined);
 }
 
 // Error bits raised by the kernels of the calls queued so far (a table delay out of range, a view
 // index out of range on the device-resident path); synchronises the render stream.
 void fetch_kernel_errors(bear_cuda_renderer *r)
 {
+  join_pipelined(r);
   CK(cudaMemcpyAsync(r->h_err, r->lay.err_flag, sizeof(int), cudaMemcpyDeviceToHost, r->stream));
   CK(cudaStreamSynchronize(r->stream));
   const int bits = r->h_err[0];
@@ -832,13 +885,14 @@ void fetch_kernel_errors(bear_cuda_renderer *r)
 }
 
 template <class F>
-int guarded(bear_cuda_renderer *r, F &&f)
+int guarded(bear_cuda_renderer *r, F &&f, bool join = true)
 {
   std::string *err = r ? &r->error : &g_create_error;
   try {
     if (r) {
       cudaError_t e = cudaSetDevice(r->device);
       if (e != cudaSuccess) throw CudaFail{std::string("cudaSetDevice: ") + cudaGetErrorString(e)};
+      if (join) join_pipelined(r);   // no entry point but the pipelined one leaves or finds work on the second stream
     }
     f();
     return BEAR_CUDA_OK;
@@ -1397,6 +1451,23 @@ int bear_cuda_process_device(bear_cuda_renderer *r, uint32_t T)
   });
 }
 
+int bear_cuda_process_device_pipelined(bear_cuda_renderer *r, uint32_t T)
+{
+  if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  return guarded(r, [&] {
+    r->shadow_valid = false;
+    if (T == 0 || (int)T > r->lay.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
+    run_pipeline(r, (int)T, true, true);
+  }, false);
+}
+
+int bear_cuda_result_stream(bear_cuda_renderer *r, void **stream)
+{
+  if (!r || !stream) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
+  *stream = r->conv_stream ? r->conv_stream : r->stream;
+  return BEAR_CUDA_OK;
+}
+
 int bear_cuda_process_device_static_scratch(bear_cuda_renderer *r, uint32_t T)
 {
   if (!r) return BEAR_CUDA_ERR_INVALID_ARGUMENT;
@@ -1593,12 +1664,15 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
     if (const char *env = std::getenv("BEAR_CUDA_SHARED_CHUNKS")) r->shared_chunks = std::max(1, std::atoi(env));
     CK(cudaStreamCreateWithFlags(&r->conv_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&r->ev_call, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&r->ev_barrier, cudaEventDisableTiming));
+    for (int b = 0; b < 2; b++) {
+      r->sh_view[b] = r->dalloc<int32_t>((size_t)p.Tmax + 1);
+      r->sh_dstat[b] = r->dalloc<float>((size_t)(p.Tmax + 2) * 2 * p.L);
+    }
     r->mix_events.resize(std::max<size_t>(r->done_events.size(), 4));
     for (cudaEvent_t &e : r->mix_events) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     r->bus_sum = r->dalloc<float>((size_t)3 * p.L * p.cs);
     r->comm_root = root;
-    if (const char *env = std::getenv("BEAR_CUDA_COMM_ALLREDUCE"))   // experiments: all-reduce instead of reduce to the root
-      if (std::atoi(env)) r->comm_root = -1;
     uint32_t l0 = 0, l1 = 0;
     bear_cuda_comm_speaker_range(rank, world, (uint32_t)p.L, &l0, &l1);
     p.W = (int)world; p.rank = (int)rank; p.l0 = (int)l0; p.l1 = (int)l1;

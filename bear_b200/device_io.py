@@ -61,8 +61,13 @@ class DeviceBuffers:
     def output(self, T):
         return self.audio_out[:, :T * self.r.B]
 
-    def read_output(self, T):
-        with torch.cuda.stream(self.stream):
+    def read_output(self, T, pipelined=False):
+        """Copy the output of the last call to the host.  pipelined: the call was
+        process_device_pipelined, whose output completes on the renderer's result stream."""
+        st = self.stream
+        if pipelined:
+            st = torch.cuda.ExternalStream(self.r.result_stream(), device=self.device)
+        with torch.cuda.stream(st):
             out = self.output(T).cpu()
-        self.stream.synchronize()
+        st.synchronize()
         return out.numpy()

@@ -95,6 +95,7 @@ EXPORTS = (
     "bear_cuda_process_device_static_scratch", "bear_cuda_control_tables", "bear_cuda_reset",
     "bear_cuda_create_shared", "bear_cuda_process_batch_frames",
     "bear_cuda_comm_blob", "bear_cuda_comm_connect", "bear_cuda_comm_speaker_range",
+    "bear_cuda_process_device_pipelined", "bear_cuda_result_stream",
 )
 STATIC_SCRATCH_BYTES = 4 << 20
 NUM_KERNELS = 11
@@ -137,6 +138,8 @@ def lib():
         l.bear_cuda_get_device_io.argtypes = [vp, C.POINTER(DeviceIO)]
         l.bear_cuda_process_device.argtypes = [vp, u32]
         l.bear_cuda_process_device_static_scratch.argtypes = [vp, u32]
+        l.bear_cuda_process_device_pipelined.argtypes = [vp, u32]
+        l.bear_cuda_result_stream.argtypes = [vp, C.POINTER(C.c_void_p)]
         l.bear_cuda_synchronize.argtypes = [vp]
         l.bear_cuda_reset.argtypes = [vp]
         l.bear_cuda_get_info.argtypes = [vp, C.POINTER(Info)]
@@ -418,6 +421,18 @@ class Renderer:
 
     def process_device(self, T):
         self._check(self._l.bear_cuda_process_device(self._h, T))
+
+    def process_device_pipelined(self, T):
+        """bear_cuda_process_device that leaves the exchange + convolution of its periods queued on the
+        renderer's second stream (shared scenes; see include/bear_cuda.h for the rules).  The output is
+        complete on result_stream()."""
+        self._check(self._l.bear_cuda_process_device_pipelined(self._h, T))
+
+    def result_stream(self):
+        """cudaStream_t (an int) on which the output of a pipelined call completes."""
+        st = C.c_void_p()
+        self._check(self._l.bear_cuda_result_stream(self._h, C.byref(st)))
+        return st.value or 0
 
     def set_profiling(self, enable):
         self._check(self._l.bear_cuda_set_profiling(self._h, int(enable)))

@@ -61,6 +61,8 @@ def parse_args():
     ap.add_argument("--cpu-sample-blocks", type=int, default=0, help="blocks of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="only the headline workload")
+    ap.add_argument("--no-pipeline", action="store_true",
+                    help="N > 1: plain bear_cuda_process_device calls instead of the pipelined ones")
     ap.add_argument("--chunk-blocks", type=int, default=0, help="periods per launch group (0 = library default)")
     ap.add_argument("--cmac-splits", type=int, default=0, help="partial spectra per period (0 = library default)")
     ap.add_argument("--object-splits", type=int, default=0, help="mix CTAs per tile (0 = library default)")
@@ -286,7 +288,8 @@ def workload_config(args, T, world, instances=None):
          "audio_seconds_per_step": T * B / FS,
          "data_file": "synthetic default shape (180 views x 24 x 2 x 2976 taps, 128-tap decorrelators)",
          "sharding": ("object groups; bus rows of 24/N loudspeakers gathered from the peers over NVLink, NCCL reduce "
-                      "of the stereo partial mixes (bear_cuda_comm_connect)") if world > 1 else "single GPU",
+                      "of the stereo partial mixes (bear_cuda_comm_connect); the exchange + convolution of a step run "
+                      "beside the mix of the next one (pipelined calls)") if world > 1 else "single GPU",
          "l2": "inputs larger than L2 (audio + tables streamed per step >> 126 MB)"}
     if instances:
         c["cpu_instances"] = instances
@@ -328,6 +331,9 @@ class Leg:
     def step_resident(self):
         self.r.process_device(self.T)
 
+    def step_pipelined(self):
+        self.r.process_device_pipelined(self.T)
+
     def step_e2e(self):
         self.r.process_batch(self.h_audio, None, None, self.h_tb, output=self.h_out)
 
@@ -355,6 +361,11 @@ def run_ours(args, rank, world, local_rank):
         parallel.connect_renderers(r, rank, world, root=0)
     leg.make_resident()
     stream = leg.stream
+    # a shared scene is rendered with pipelined calls: the exchange + convolution of step s run on the
+    # renderer's second stream beside the mix of step s+1 (the per-kernel pass below runs unpipelined)
+    pipelined = world > 1 and not args.no_pipeline
+    result_stream = torch.cuda.ExternalStream(r.result_stream(), device=torch.device("cuda", local_rank))
+    step = leg.step_pipelined if pipelined else leg.step_resident
 
     def barrier():
         r.synchronize()
@@ -368,6 +379,7 @@ def run_ours(args, rank, world, local_rank):
         e0.record(stream)
         for _ in range(steps):
             fn()
+        stream.wait_stream(result_stream)    # the end of the last step's convolution side
         e1.record(stream)
         e1.synchronize()
         barrier()
@@ -382,13 +394,14 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         clocks.start()
     for _ in range(100):      # a fixed count: every rank must issue the same number of collectives
-        leg.step_resident()
+        step()
     r.synchronize()
     for _ in range(max(3, args.warmup)):
-        leg.step_resident()
+        step()
     launches0 = r.get_info().launches_total
-    ms = timed(leg.step_resident, args.steps)
+    ms = timed(step, args.steps)
     launches = r.get_info().launches_total - launches0
+    ms_joined = timed(leg.step_resident, args.steps) if pipelined else ms   # the same steps, one after the other
     # per-kernel times: a second pass with an event pair around every kernel (the events themselves
     # cost a little, so the headline above is taken without them)
     r.set_profiling(True)
@@ -526,6 +539,8 @@ def run_ours(args, rank, world, local_rank):
             line["exchange"] = {
                 "nvlink_bytes_read_per_rank_per_step": int(3 * nl * fB * (world - 1)),
                 "nccl_reduce_bytes_per_step": int(2 * fB),
+                "calls": "bear_cuda_process_device_pipelined" if pipelined else "bear_cuda_process_device",
+                "ms_per_step_unpipelined": ms_joined / args.steps,
                 "ms_per_step": sum(v[0] for k, v in prof.items() if k == "exchange") / max(args.steps, 1),
                 "gather_ms_per_step": sum(v[0] for k, v in prof.items() if k == "bus_gather_kernel") / max(args.steps, 1),
                 "note": "ms_per_step = the one-word NCCL all-reduce that orders the ranks (includes waiting for the "

@@ -270,6 +270,24 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
 void bear_cuda_comm_speaker_range(uint32_t rank, uint32_t world, uint32_t num_virtual_loudspeakers,
                                   uint32_t *begin, uint32_t *end);
 
+/* Pipelined calls of a shared scene (no counterpart in the reference, whose process() returns with the
+ * period's output written, renderer.hpp:45-52).  Same work and same results as bear_cuda_process_device,
+ * but the call returns with the exchange and the convolution of its T periods still queued on a second
+ * stream, so that the mix of the next call's periods runs beside them: with W GPUs the convolution
+ * side is short and mostly waits for its peers, and this hides that wait.  Rules:
+ *   - the staging areas (audio, tables) may be rewritten on the render stream (bear_cuda_device_io.stream)
+ *     as soon as the call has returned: the convolution side works on its own copies of the tables;
+ *   - the output of call s is complete on the stream bear_cuda_result_stream returns, in stream order
+ *     after the call; read it there before queueing call s+1 (the output rows are reused every call);
+ *   - any other entry point first lets the render stream wait for the pending convolution side, and
+ *     behaves as documented from then on; bear_cuda_synchronize waits for both streams;
+ *   - a renderer that is not connected, has HOA inputs on this rank, a chunk_blocks limit below T, or
+ *     per-kernel profiling switched on runs the call exactly as bear_cuda_process_device does. */
+int bear_cuda_process_device_pipelined(bear_cuda_renderer *r, uint32_t T);
+/* The stream on which the output of a bear_cuda_process_device_pipelined call completes (the renderer's
+ * second stream once connected, else the render stream); no counterpart in the reference. */
+int bear_cuda_result_stream(bear_cuda_renderer *r, void **stream);
+
 /* ---- introspection --------------------------------------------------------------------------- */
 
 typedef struct bear_cuda_info {

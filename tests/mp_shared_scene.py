@@ -46,6 +46,24 @@ def main():
         mine["hoa_gains"] = np.zeros((2 * T, ctl.A, 0), np.float32)
 
     failures = []
+
+    def check(label, got, want_args, receives):
+        if receives:
+            Nw, Mw, Hw, hoa_w, tb_w = want_args
+            with Renderer(data, Nw, Mw, Hw, B, max_batch_blocks=T, device=local) as whole:
+                want = whole.render(obj, ds, hoa_w, tb_w)
+            err = float(np.abs(got - want).max())
+            print("rank %d %s: max-abs vs one GPU %.3e, peak %.3f" % (rank, label, err, np.abs(want).max()), flush=True)
+            if not (err <= 1e-5 and np.abs(want).max() > 0.05):
+                failures.append((label, err))
+            if rank == 0:
+                from oracle import bear_ref
+                ref = bear_ref.RefRenderer(data, Nw, Mw, Hw, B).render(obj, ds, hoa_w, tb_w.blocks())
+                err = float(np.abs(got - ref).max())
+                print("rank 0 %s: max-abs vs oracle %.3e" % (label, err), flush=True)
+                if err > 1e-5:
+                    failures.append((label, "oracle", err))
+
     for root, chunk in ((0, 0), (-1, 7)):
         with Renderer(data, n, m, h, B, max_batch_blocks=T, device=local, chunk_blocks=chunk) as r:
             parallel.connect_renderers(r, rank, world, root=root)
@@ -63,21 +81,44 @@ def main():
             r.synchronize()
             second = io.read_output(T) if receives else None
         dist.barrier()
-        if receives:
-            got = np.concatenate([first, second], axis=1)
-            with Renderer(data, N, M, H, B, max_batch_blocks=T, device=local) as whole:
-                want = whole.render(obj, ds, hoa, tb)
-            err = float(np.abs(got - want).max())
-            print("rank %d root %d chunk %d: max-abs vs one GPU %.3e, peak %.3f" % (rank, root, chunk, err, np.abs(want).max()), flush=True)
-            if not (err <= 1e-5 and np.abs(want).max() > 0.05):
-                failures.append((root, chunk, err))
-            if rank == 0:
-                from oracle import bear_ref
-                ref = bear_ref.RefRenderer(data, N, M, H, B).render(obj, ds, hoa, tb.blocks())
-                err = float(np.abs(got - ref).max())
-                print("rank 0 root %d: max-abs vs oracle %.3e" % (root, err), flush=True)
-                if err > 1e-5:
-                    failures.append((root, "oracle", err))
+        check("root %d chunk %d" % (root, chunk), np.concatenate([first, second], axis=1) if receives else None,
+              (N, M, H, hoa, tb), receives)
+        dist.barrier()
+
+    # Pipelined calls (bear_cuda_process_device_pipelined): the convolution side of call s is still queued
+    # when the inputs of call s+1 are written and its mix starts.  Five calls of 8 periods; the scene has no
+    # HOA (a rank with HOA inputs runs these calls unpipelined, which the second pass covers: HOA on rank 0).
+    for with_hoa in (False, True):
+        hh = h if with_hoa else 0
+        tb_p, mine_p = control.BlockTables(tb), control.BlockTables(mine)
+        if not with_hoa:
+            tb_p["hoa_gains"] = np.zeros((2 * T, ctl.A, 0), np.float32)
+        if not hh:
+            mine_p["hoa_gains"] = np.zeros((2 * T, ctl.A, 0), np.float32)
+        Tc = 8
+        with Renderer(data, n, m, hh, B, max_batch_blocks=Tc, device=local) as r:
+            parallel.connect_renderers(r, rank, world, root=0)
+            io = device_io.DeviceBuffers(r, device_index=local)
+
+            def load(c):
+                a, b = c * Tc * B, (c + 1) * Tc * B
+                rows = [obj[sl, a:b]] + ([ds[:, a:b]] if m else []) + ([hoa[:, a:b]] if hh else [])
+                io.load_audio(np.concatenate(rows))
+                io.load_tables(mine_p.slice(c * Tc, (c + 1) * Tc))
+
+            outs = []
+            ncalls = 2 * T // Tc
+            load(0)
+            r.process_device_pipelined(Tc)
+            for c in range(1, ncalls):
+                load(c)   # queued on the render stream while call c-1's convolution side is still running
+                outs.append(io.read_output(Tc, pipelined=True))
+                r.process_device_pipelined(Tc)
+            outs.append(io.read_output(Tc, pipelined=True))
+            r.synchronize()
+        dist.barrier()
+        check("pipelined hoa=%d" % with_hoa, np.concatenate(outs, axis=1) if rank == 0 else None,
+              (N, M, H if with_hoa else 0, hoa if with_hoa else None, tb_p), rank == 0)
         dist.barrier()
     flag = torch.tensor([len(failures)])
     dist.all_reduce(flag)
