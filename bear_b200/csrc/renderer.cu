@@ -1457,7 +1457,17 @@ int bear_cuda_process_device_pipelined(bear_cuda_renderer *r, uint32_t T)
   return guarded(r, [&] {
     r->shadow_valid = false;
     if (T == 0 || (int)T > r->lay.Tmax) throw InvalidArgument{"T must be in 1..max_batch_blocks"};
+    if (r->conv_stream && !r->pipelined_pending) {
+      // reads of the previous output that the caller queued on the result stream come first
+      CK(cudaEventRecord(r->ev_call, r->conv_stream));
+      CK(cudaStreamWaitEvent(r->stream, r->ev_call, 0));
+    }
     run_pipeline(r, (int)T, true, true);
+    if (!r->pipelined_pending && r->conv_stream) {
+      // the call ran unpipelined (see the header for when): its output is still promised on the result stream
+      CK(cudaEventRecord(r->ev_call, r->stream));
+      CK(cudaStreamWaitEvent(r->conv_stream, r->ev_call, 0));
+    }
   }, false);
 }
 
