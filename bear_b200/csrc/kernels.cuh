@@ -120,7 +120,7 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 void launch_mix_prep(const Layout &p, int T, cudaStream_t st);
 void launch_mix(const Layout &p, int T, cudaStream_t st);
 void launch_bus_sum(const Layout &p, int T, cudaStream_t st);
-void launch_bus_gather(const Layout &p, int T, cudaStream_t st);
+void launch_bus_gather(const Layout &p, int T, cudaStream_t st, bool thin = false);
 void launch_validate_views(const Layout &p, int T, cudaStream_t st);
 void launch_hoa_mix(const Layout &p, int T, cudaStream_t st);
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st);

@@ -135,6 +135,8 @@ struct FilterBank {
   }
 };
 
+constexpr int kBusSets = 3;   // sets of bus rows a shared scene cycles through (see run_pipeline)
+
 struct bear_cuda_renderer {
   std::shared_ptr<FilterBank> bank;
   bear_cuda_config cfg{};
@@ -150,8 +152,9 @@ struct bear_cuda_renderer {
   std::vector<cudaEvent_t> done_events;    // one per rendered chunk
   bool tables_on_device = false;           // bear_cuda_control_tables filled the staging tables
   int s_cfg = 0;                           // configured object splits (0 = per launch)
-  float *bus[2] = {nullptr, nullptr};      // direct + diffuse bus rows [3L][cs]; [1] only while sharing a scene
-  int parity = 0;                          // which of the two the current call writes
+  float *bus[kBusSets] = {};               // direct + diffuse bus rows [3L][cs]; [1...] only while sharing a scene
+  uint64_t shared_calls = 0;               // calls made as part of a shared scene
+  int parity = 0;                          // which of the sets the current call writes (kBusSets once shared)
   int *h_err = nullptr;                    // pinned copy of the kernels' error flags
   cudaEvent_t ev_order = nullptr;          // orders the copy stream behind the render stream
   float2 *static_scratch = nullptr;        // device address of the library's built-in scratch array
@@ -159,7 +162,7 @@ struct bear_cuda_renderer {
   // one scene shared with other GPUs (bear_cuda_comm_connect)
   NcclComm comm = nullptr;
   int comm_root = -1;                      // rank that receives the mix, -1 = every rank
-  float *peer_bus[kMaxRanks][2] = {};      // every rank's bus rows (cudaIpc mappings), [rank] = own
+  float *peer_bus[kMaxRanks][kBusSets] = {};   // every rank's bus rows (cudaIpc mappings), [rank] = own
   float *bus_sum = nullptr;                // [3L][cs] rows of this rank's loudspeakers summed over the ranks
   int *d_barrier = nullptr;                // payload of the cross-rank barrier
   size_t comm_bytes_per_period = 0;        // largest upload per period among the ranks (same chunking everywhere)
@@ -171,9 +174,10 @@ struct bear_cuda_renderer {
   // pipelined calls of a shared scene (bear_cuda_process_device_pipelined): the exchange + convolution of
   // call s stay queued on conv_stream while the mix of call s+1 runs on the render stream
   bool pipelined_pending = false;          // conv_stream holds work the render stream has not waited for
-  cudaEvent_t ev_barrier = nullptr;        // the ordering collective of the last pipelined call has completed
-  int32_t *sh_view[2] = {nullptr, nullptr};   // the convolution side's own copies of the view / static-delay tables
-  float *sh_dstat[2] = {nullptr, nullptr};
+  cudaEvent_t ev_barrier[2] = {nullptr, nullptr};   // the ordering collective of pipelined call c has completed: [c & 1]
+  int32_t *sh_view[kBusSets] = {};         // the convolution side's own copies of the view / static-delay tables
+  float *sh_dstat[kBusSets] = {};
+  bool shared_bus = false;                 // the bus rows are the kBusSets sets that peers may map
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -230,6 +234,14 @@ struct bear_cuda_renderer {
     return static_cast<T *>(p);
   }
 
+  void dfree(void *p)
+  {
+    allocs.erase(std::remove(allocs.begin(), allocs.end(), p), allocs.end());
+    for (auto it = state_allocs.begin(); it != state_allocs.end(); ++it)
+      if (it->first == p) { device_bytes -= it->second; state_allocs.erase(it); break; }
+    cudaFree(p);
+  }
+
   ~bear_cuda_renderer()
   {
     cudaSetDevice(device);
@@ -242,7 +254,7 @@ struct bear_cuda_renderer {
     if (comm) nccl().CommDestroy(comm);
     for (cudaEvent_t e : mix_events) cudaEventDestroy(e);
     if (ev_call) cudaEventDestroy(ev_call);
-    if (ev_barrier) cudaEventDestroy(ev_barrier);
+    for (cudaEvent_t e : ev_barrier) if (e) cudaEventDestroy(e);
     if (conv_stream) cudaStreamDestroy(conv_stream);
     for (int w = 0; w < kMaxRanks; w++)
       if (peer_bus[w][0] && w != lay.rank) cudaIpcCloseMemHandle(peer_bus[w][0]);
@@ -496,8 +508,7 @@ bear_cuda_renderer *create_with_bank(const bear_cuda_config &cfg, std::shared_pt
   p.cs = round_up(p.B + TB, 4);
   // both bus-row sets in one allocation: a renderer that shares a scene alternates between them from
   // call to call (its peers read the rows over NVLink), a renderer on its own uses the first
-  r->bus[0] = r->dalloc<float>((size_t)2 * 3 * p.L * p.cs);
-  r->bus[1] = r->bus[0] + (size_t)3 * p.L * p.cs;
+  r->bus[0] = r->dalloc<float>((size_t)3 * p.L * p.cs);   // (bear_cuda_comm_blob replaces it by kBusSets sets)
   p.cdir = r->bus[0];
   p.qdif = r->bus[0] + (size_t)2 * p.L * p.cs;
   p.peer_cdir[0] = p.cdir; p.peer_qdif[0] = p.qdif;
@@ -700,8 +711,8 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   cudaStream_t sb = overlap ? r->conv_stream : st;   // exchange + convolution side
   r->result_stream = sb;
   Layout pc = p;   // what the convolution side sees (filled in below)
-  // bus rows of this call; a renderer that shares a scene alternates between its two sets, so that a
-  // peer still reading the previous call's rows is never overwritten (one barrier per chunk suffices)
+  // bus rows of this call; a renderer that shares a scene cycles through kBusSets sets, so that a peer
+  // still reading an earlier call's rows is never overwritten (one barrier per chunk suffices)
   float *const bus = r->bus[r->parity];
   p.cdir = bus;
   p.qdif = bus + (size_t)2 * p.L * p.cs;
@@ -720,7 +731,10 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   if (pipe) {
     // the bus rows this call writes were read by the peers two calls ago: their gathers are over once the
     // ordering collective of the previous call has completed here
-    if (r->pipelined_pending) CK(cudaStreamWaitEvent(st, r->ev_barrier, 0));
+    // (three sets: the set written now was last read in call c-3, and every peer had finished that
+    // gather when it entered the ordering collective of call c-2 -- the event recorded two calls ago,
+    // long complete, so the mix never waits for its peers)
+    CK(cudaStreamWaitEvent(st, r->ev_barrier[r->shared_calls & 1], 0));
     // the convolution side works on its own copies of the tables it reads, so that the caller may write
     // the next call's tables as soon as this call has been queued
     const int par = r->parity;
@@ -752,9 +766,9 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       // every rank's bus rows of this chunk are complete before anyone reads them
       mark(BEAR_CUDA_KERNEL_EXCHANGE);
       NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, sb));
-      if (pipe) CK(cudaEventRecord(r->ev_barrier, sb));
+      if (pipe) CK(cudaEventRecord(r->ev_barrier[r->shared_calls & 1], sb));
       mark(BEAR_CUDA_KERNEL_GATHER);
-      launch_bus_gather(pc, n, sb);
+      launch_bus_gather(pc, n, sb, pipe);
       if (p.l1 > p.l0) launches++;
     }
     if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(pc, n, sb); launches++; }
@@ -859,7 +873,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   CK(cudaGetLastError());
   r->launches += launches;
   r->calls++;
-  if (shared_scene) r->parity ^= 1;
+  if (shared_scene) { r->parity = (r->parity + 1) % kBusSets; r->shared_calls++; }
 }
 
 void run_pipeline(bear_cuda_renderer *r, int T, bool device_tables = false, bool pipelined = false)
@@ -1624,6 +1638,18 @@ int bear_cuda_comm_blob(bear_cuda_renderer *r, uint32_t rank, void *blob)
     b.magic = kCommMagic; b.B = (uint32_t)p.B; b.Tmax = (uint32_t)p.Tmax; b.L = (uint32_t)p.L;
     b.cs = p.cs;
     b.N = (uint32_t)p.N; b.M = (uint32_t)p.M; b.H = (uint32_t)p.H; b.rank = rank;
+    if (!r->shared_bus) {
+      // peers map ONE allocation: the kBusSets sets of bus rows the calls cycle through
+      if (r->calls != 0) throw InvalidArgument{"connect before the first process call (or after bear_cuda_reset)"};
+      CK(cudaStreamSynchronize(r->stream));
+      r->dfree(r->bus[0]);
+      const size_t set = (size_t)3 * r->lay.L * r->lay.cs;
+      r->bus[0] = r->dalloc<float>(kBusSets * set);
+      for (int k = 1; k < kBusSets; k++) r->bus[k] = r->bus[0] + k * set;
+      r->lay.cdir = r->bus[0];
+      r->lay.qdif = r->bus[0] + (size_t)2 * r->lay.L * r->lay.cs;
+      r->shared_bus = true;
+    }
     CK(cudaIpcGetMemHandle(&b.bus, r->bus[0]));
     if (rank == 0) NCK(nccl().GetUniqueId(&b.id));
     std::memcpy(blob, &b, sizeof b);
@@ -1667,15 +1693,16 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
         CK(cudaIpcOpenMemHandle(&base, bl[w].bus, cudaIpcMemLazyEnablePeerAccess));
         r->peer_bus[w][0] = static_cast<float *>(base);
       }
-      r->peer_bus[w][1] = r->peer_bus[w][0] + (size_t)3 * p.L * p.cs;
+      for (int k = 1; k < kBusSets; k++) r->peer_bus[w][k] = r->peer_bus[w][0] + (size_t)k * 3 * p.L * p.cs;
     }
     NCK(nccl().CommInitRank(&r->comm, (int)world, bl[0].id, (int)rank));
     r->d_barrier = r->dalloc<int>(4);
     if (const char *env = std::getenv("BEAR_CUDA_SHARED_CHUNKS")) r->shared_chunks = std::max(1, std::atoi(env));
     CK(cudaStreamCreateWithFlags(&r->conv_stream, cudaStreamNonBlocking));
     CK(cudaEventCreateWithFlags(&r->ev_call, cudaEventDisableTiming));
-    CK(cudaEventCreateWithFlags(&r->ev_barrier, cudaEventDisableTiming));
-    for (int b = 0; b < 2; b++) {
+    if (!r->shared_bus) throw InvalidArgument{"bear_cuda_comm_blob comes first"};
+    for (cudaEvent_t &e : r->ev_barrier) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    for (int b = 0; b < kBusSets; b++) {
       r->sh_view[b] = r->dalloc<int32_t>((size_t)p.Tmax + 1);
       r->sh_dstat[b] = r->dalloc<float>((size_t)(p.Tmax + 2) * 2 * p.L);
     }
