@@ -1017,42 +1017,50 @@ __global__ void __launch_bounds__(256) bus_gather_kernel(Layout p, int T)
 }
 // The same sums by one small CTA per SM that stays resident for the whole launch (pipelined calls): the
 // gather is bound by NVLink, not by the SMs, and in this form it leaves six of an SM's seven mix_kernel
-// slots to the next call's mix, which runs beside it.  Two float4 per rank in flight per thread.
-__global__ void __launch_bounds__(128) bus_gather_thin_kernel(Layout p, int T)
+// slots to the next call's mix, which runs beside it.  About 16 float4 in flight per thread whatever
+// the number of ranks (W ranks x 16/W elements).
+template <int W>
+__global__ void __launch_bounds__(128, 6) bus_gather_thin_kernel(Layout p, int T)
 {
+  constexpr int U = 16 / W;
   const int nl = p.l1 - p.l0;
   const unsigned per_row = (unsigned)((size_t)T * p.B / 4), total = 3u * nl * per_row;
   const unsigned stride = gridDim.x * 128;
-  for (unsigned j0 = blockIdx.x * 128 + threadIdx.x; j0 < total; j0 += 2 * stride) {
-    float4 v[2][kMaxRanks];
-    size_t off[2];
-    bool dir[2], on[2];
+  for (unsigned j0 = blockIdx.x * 128 + threadIdx.x; j0 < total; j0 += U * stride) {
+    float4 v[U][W];
+    size_t off[U];
+    bool dir[U], on[U];
 #pragma unroll
-    for (int u = 0; u < 2; u++) {
+    for (int u = 0; u < U; u++) {
       const unsigned j = j0 + u * stride;
       on[u] = j < total;
       const unsigned r = on[u] ? j / per_row : 0, i = on[u] ? j - r * per_row : 0;
       dir[u] = r < 2u * nl;
       off[u] = (size_t)(dir[u] ? 2 * p.l0 + r : p.l0 + (r - 2 * nl)) * p.cs + (size_t)(p.k0 + 1) * p.B + 4 * (size_t)i;
 #pragma unroll
-      for (int w = 0; w < kMaxRanks; w++)
-        if (w < p.W && on[u]) v[u][w] = *reinterpret_cast<const float4 *>((dir[u] ? p.peer_cdir[w] : p.peer_qdif[w]) + off[u]);
+      for (int w = 0; w < W; w++)
+        if (on[u]) v[u][w] = *reinterpret_cast<const float4 *>((dir[u] ? p.peer_cdir[w] : p.peer_qdif[w]) + off[u]);
     }
 #pragma unroll
-    for (int u = 0; u < 2; u++) {
+    for (int u = 0; u < U; u++) {
       if (!on[u]) continue;
       float4 a = v[u][0];
 #pragma unroll
-      for (int w = 1; w < kMaxRanks; w++)
-        if (w < p.W) { a.x += v[u][w].x; a.y += v[u][w].y; a.z += v[u][w].z; a.w += v[u][w].w; }
+      for (int w = 1; w < W; w++) { a.x += v[u][w].x; a.y += v[u][w].y; a.z += v[u][w].z; a.w += v[u][w].w; }
       *reinterpret_cast<float4 *>(const_cast<float *>(dir[u] ? p.cin : p.qin) + off[u]) = a;
     }
   }
 }
+template <int W>
+static void launch_bus_gather_thin(const Layout &p, int T, cudaStream_t st)
+{
+  if (p.W == W) bus_gather_thin_kernel<W><<<148, 128, 0, st>>>(p, T);
+  else if constexpr (W < kMaxRanks) launch_bus_gather_thin<W + 1>(p, T, st);
+}
 void launch_bus_gather(const Layout &p, int T, cudaStream_t st, bool thin)
 {
   if (p.l1 <= p.l0) return;
-  if (thin) bus_gather_thin_kernel<<<148, 128, 0, st>>>(p, T);
+  if (thin) launch_bus_gather_thin<2>(p, T, st);
   else bus_gather_kernel<<<dim3((T * p.B + 1023) / 1024, 3 * (p.l1 - p.l0)), 256, 0, st>>>(p, T);
 }
 
