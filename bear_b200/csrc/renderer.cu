@@ -178,6 +178,12 @@ struct bear_cuda_renderer {
   int32_t *sh_view[kBusSets] = {};         // the convolution side's own copies of the view / static-delay tables
   float *sh_dstat[kBusSets] = {};
   bool shared_bus = false;                 // the bus rows are the kBusSets sets that peers may map
+  // development aid (BEAR_CUDA_TIMELINE=<path prefix>): when each side of the pipelined calls reached
+  // each kernel, in ms since the first mark, written to <prefix>.rank<r> by bear_cuda_synchronize
+  struct TimelineMark { cudaEvent_t e; int kernel; int side; uint64_t call; };
+  std::vector<TimelineMark> timeline;
+  std::string timeline_path;
+  cudaEvent_t timeline_base = nullptr;
   int chunk = 0;                           // periods per launch group (0 = whole call)
   int h2d_chunk = 0;                       // periods per upload chunk of the host-buffer path
   std::vector<void *> allocs;
@@ -684,7 +690,20 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   if (!pipe) join_pipelined(r);
   std::vector<cudaEvent_t> chain;
   std::vector<int> ids;
-  auto mark = [&](int kernel_id) {
+  auto mark = [&](int kernel_id, int side = 0) {
+    if (pipe && !r->timeline_path.empty()) {
+      cudaEvent_t e;
+      if (!r->timeline_base) { CK(cudaEventCreate(&r->timeline_base)); CK(cudaEventRecord(r->timeline_base, st)); }
+      if (r->timeline.size() >= 800) {
+        for (size_t i = 0; i < 400; i++) r->ev_free.push_back(r->timeline[i].e);
+        r->timeline.erase(r->timeline.begin(), r->timeline.begin() + 400);
+      }
+      if (r->ev_free.empty()) CK(cudaEventCreate(&e));
+      else { e = r->ev_free.back(); r->ev_free.pop_back(); }
+      CK(cudaEventRecord(e, side ? r->conv_stream : st));
+      r->timeline.push_back({e, kernel_id, side, r->shared_calls});
+      return;
+    }
     if (!r->profiling) return;
     cudaEvent_t e;
     if (r->ev_free.empty()) CK(cudaEventCreate(&e));
@@ -764,23 +783,23 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
     if (pipe) { pc.view = r->sh_view[r->parity]; pc.d_stat = r->sh_dstat[r->parity]; }
     if (shared_scene) {
       // every rank's bus rows of this chunk are complete before anyone reads them
-      mark(BEAR_CUDA_KERNEL_EXCHANGE);
+      mark(BEAR_CUDA_KERNEL_EXCHANGE, 1);
       NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, sb));
       if (pipe) CK(cudaEventRecord(r->ev_barrier[r->shared_calls & 1], sb));
-      mark(BEAR_CUDA_KERNEL_GATHER);
+      mark(BEAR_CUDA_KERNEL_GATHER, 1);
       launch_bus_gather(pc, n, sb, pipe);
       if (p.l1 > p.l0) launches++;
     }
-    if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE); launch_decorrelate(pc, n, sb); launches++; }
-    if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL); launch_bus_fdl(pc, n, sb); launches++; }
+    if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE, 1); launch_decorrelate(pc, n, sb); launches++; }
+    if (p.l1 > p.l0 || p.H > 0) { mark(BEAR_CUDA_KERNEL_BUS_FDL, 1); launch_bus_fdl(pc, n, sb); launches++; }
     pc.KS = cmac_splits_for(r, n);
     pc.ks_dev = cmac_groups_by_view(pc, n);
-    mark(BEAR_CUDA_KERNEL_CMAC); launches += launch_cmac(pc, n, sb);
-    mark(BEAR_CUDA_KERNEL_IFFT_OUT); launch_ifft_out(pc, n, sb); launches++;
+    mark(BEAR_CUDA_KERNEL_CMAC, 1); launches += launch_cmac(pc, n, sb);
+    mark(BEAR_CUDA_KERNEL_IFFT_OUT, 1); launch_ifft_out(pc, n, sb); launches++;
     if (shared_scene) {
       // the stereo partial mixes of the ranks are summed (north_star: "only per-block stereo partial
       // mixes are summed with NCCL"), chunk by chunk so that the sum of chunk c runs under chunk c+1
-      mark(BEAR_CUDA_KERNEL_EXCHANGE);
+      mark(BEAR_CUDA_KERNEL_EXCHANGE, 1);
       NCK(nccl().GroupStart());
       for (int e = 0; e < 2; e++) {
         float *row = p.out + (size_t)e * p.os + (size_t)k0 * p.B;
@@ -861,7 +880,9 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   if (pipe) {
     plan_conv.n = nc;
     plan_conv.row_start[nc] = rows_c;
+    mark(BEAR_CUDA_KERNEL_CARRY, 1);
     launch_carry(plan_conv, sb);
+    mark(-1, 1);
     launches++;
     r->pipelined_pending = true;
   }
@@ -883,11 +904,30 @@ void run_pipeline(bear_cuda_renderer *r, int T, bool device_tables = false, bool
 
 // Error bits raised by the kernels of the calls queued so far (a table delay out of range, a view
 // index out of range on the device-resident path); synchronises the render stream.
+void dump_timeline(bear_cuda_renderer *r)
+{
+  if (r->timeline.empty()) return;
+  static const char *names[] = {"mix", "hoa_mix", "decorrelate", "bus_fdl", "cmac", "ifft_out", "carry", "control",
+                                "mix_aux", "exchange", "gather"};
+  if (FILE *f = std::fopen((r->timeline_path + ".rank" + std::to_string(r->lay.rank)).c_str(), "a")) {
+    std::fprintf(f, "# %zu marks: call side kernel-that-follows ms\n", r->timeline.size());
+    for (auto &m : r->timeline) {
+      float ms = 0.f;
+      if (cudaEventElapsedTime(&ms, r->timeline_base, m.e) != cudaSuccess) { cudaGetLastError(); continue; }
+      std::fprintf(f, "%llu %d %s %.4f\n", (unsigned long long)m.call, m.side, m.kernel < 0 ? "end" : names[m.kernel], ms);
+    }
+    std::fclose(f);
+  }
+  for (auto &m : r->timeline) r->ev_free.push_back(m.e);
+  r->timeline.clear();
+}
+
 void fetch_kernel_errors(bear_cuda_renderer *r)
 {
   join_pipelined(r);
   CK(cudaMemcpyAsync(r->h_err, r->lay.err_flag, sizeof(int), cudaMemcpyDeviceToHost, r->stream));
   CK(cudaStreamSynchronize(r->stream));
+  dump_timeline(r);
   const int bits = r->h_err[0];
   if (!bits) return;
   CK(cudaMemsetAsync(r->lay.err_flag, 0, sizeof(int), r->stream));
@@ -1698,7 +1738,14 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
     NCK(nccl().CommInitRank(&r->comm, (int)world, bl[0].id, (int)rank));
     r->d_barrier = r->dalloc<int>(4);
     if (const char *env = std::getenv("BEAR_CUDA_SHARED_CHUNKS")) r->shared_chunks = std::max(1, std::atoi(env));
-    CK(cudaStreamCreateWithFlags(&r->conv_stream, cudaStreamNonBlocking));
+    if (const char *env = std::getenv("BEAR_CUDA_TIMELINE")) r->timeline_path = env;
+    {
+      int least = 0, greatest = 0;
+      CK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+      const char *env = std::getenv("BEAR_CUDA_CONV_PRIORITY");
+      const int prio = env && std::atoi(env) ? greatest : 0;
+      CK(cudaStreamCreateWithPriority(&r->conv_stream, cudaStreamNonBlocking, prio));
+    }
     CK(cudaEventCreateWithFlags(&r->ev_call, cudaEventDisableTiming));
     if (!r->shared_bus) throw InvalidArgument{"bear_cuda_comm_blob comes first"};
     for (cudaEvent_t &e : r->ev_barrier) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
