@@ -1064,6 +1064,52 @@ void launch_bus_gather(const Layout &p, int T, cudaStream_t st, bool thin)
   else bus_gather_kernel<<<dim3((T * p.B + 1023) / 1024, 3 * (p.l1 - p.l0)), 256, 0, st>>>(p, T);
 }
 
+// peer_sync_kernel: one warp; lane w looks after rank w.  Everything this GPU wrote before the launch
+// (kernel boundary) is made visible system-wide before the counters are stored; a lane that waits
+// reads its counter with acquire semantics, so kernels launched after this one see the peers' data.
+// A peer that never arrives raises the error flag after ~2 s instead of hanging the GPU.
+__global__ void __launch_bounds__(32) peer_sync_kernel(PeerSync s)
+{
+  const int w = threadIdx.x;
+  if (w >= s.W) return;
+  if (s.signal >> w & 1) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.s32 [%0], %1;" ::"l"(s.flags[w] + s.rank), "r"(s.value) : "memory");
+  }
+  if (s.wait >> w & 1) {
+    const long long t0 = clock64();
+    for (;;) {
+      int v;
+      asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(s.flags[s.rank] + w) : "memory");
+      if (v - s.value >= 0) break;
+      if (clock64() - t0 > (4LL << 30)) { atomicOr(s.err, kErrPeerTimeout); break; }
+    }
+  }
+}
+void launch_peer_sync(const PeerSync &s, cudaStream_t st) { peer_sync_kernel<<<1, 32, 0, st>>>(s); }
+
+// out_sum_kernel: the stereo result of a shared scene on the rank that receives it = the sum of the
+// partial mixes every rank's ifft_out_kernel stored into this GPU's inbox.  grid (ceil(n/1024), 2) x 256.
+__global__ void __launch_bounds__(256) out_sum_kernel(float *out, const float *inbox, size_t os, int W, size_t col0, size_t n)
+{
+  const size_t i = ((size_t)blockIdx.x * 256 + threadIdx.x) * 4;
+  if (i >= n) return;
+  const size_t off = (size_t)blockIdx.y * os + col0 + i;
+  float4 v[kMaxRanks];
+#pragma unroll
+  for (int w = 0; w < kMaxRanks; w++)
+    if (w < W) v[w] = *reinterpret_cast<const float4 *>(inbox + (size_t)w * 2 * os + off);
+  float4 a = v[0];
+#pragma unroll
+  for (int w = 1; w < kMaxRanks; w++)
+    if (w < W) { a.x += v[w].x; a.y += v[w].y; a.z += v[w].z; a.w += v[w].w; }
+  *reinterpret_cast<float4 *>(out + off) = a;
+}
+void launch_out_sum(float *out, const float *inbox, size_t os, int W, size_t col0, size_t n, cudaStream_t st)
+{
+  out_sum_kernel<<<dim3((unsigned)((n + 1023) / 1024), 2), 256, 0, st>>>(out, inbox, os, W, col0, n);
+}
+
 size_t mix_smem_bytes(int hist);
 static size_t mix_dense_smem_bytes(int hist)
 {

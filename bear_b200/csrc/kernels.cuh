@@ -20,6 +20,7 @@ constexpr int kMaxRanks = 8;      // GPUs that can share one scene (bear_cuda_co
 // bits of Layout::err_flag (checked by the host after a call has finished)
 constexpr int kErrDelayRange = 1; // a table delay is negative or beyond history_samples - 4
 constexpr int kErrViewRange = 2;  // a brir_index on the device-resident path is outside [0, V)
+constexpr int kErrPeerTimeout = 4;  // a peer GPU did not reach a synchronisation point of a shared scene in ~2 s
 #ifndef BEAR_CMAC_GROUP
 #define BEAR_CMAC_GROUP 5
 #endif
@@ -121,6 +122,19 @@ void launch_mix_prep(const Layout &p, int T, cudaStream_t st);
 void launch_mix(const Layout &p, int T, cudaStream_t st);
 void launch_bus_sum(const Layout &p, int T, cudaStream_t st);
 void launch_bus_gather(const Layout &p, int T, cudaStream_t st, bool thin = false);
+
+// Synchronisation between the GPUs of a shared scene through flags in each other's memory: rank w's
+// flag array has one counter per rank, written by that rank with a system-scope release store.
+struct PeerSync {
+  int *flags[kMaxRanks];     // [w]: rank w's flag array (this rank's own, or the cudaIpc mapping of a peer's)
+  int W, rank;
+  int value;                 // the counter value of this synchronisation point (same on every rank)
+  unsigned signal, wait;     // bit w: store `value` into rank w's array / spin until rank w's counter has reached it
+  int *err;
+};
+void launch_peer_sync(const PeerSync &s, cudaStream_t st);
+// out[e][col0 + i] = sum over ranks w of inbox[w][e][col0 + i], i < n (rank order: the result does not depend on timing)
+void launch_out_sum(float *out, const float *inbox, size_t os, int W, size_t col0, size_t n, cudaStream_t st);
 void launch_validate_views(const Layout &p, int T, cudaStream_t st);
 void launch_hoa_mix(const Layout &p, int T, cudaStream_t st);
 void launch_decorrelate(const Layout &p, int T, cudaStream_t st);

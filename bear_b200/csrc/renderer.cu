@@ -60,7 +60,6 @@ struct NcclApi {
   int (*GroupEnd)() = nullptr;
   const char *(*GetErrorString)(int) = nullptr;
 };
-constexpr int kNcclInt32 = 2, kNcclFloat32 = 7, kNcclSum = 0;
 
 const NcclApi &nccl()
 {
@@ -164,7 +163,6 @@ struct bear_cuda_renderer {
   int comm_root = -1;                      // rank that receives the mix, -1 = every rank
   float *peer_bus[kMaxRanks][kBusSets] = {};   // every rank's bus rows (cudaIpc mappings), [rank] = own
   float *bus_sum = nullptr;                // [3L][cs] rows of this rank's loudspeakers summed over the ranks
-  int *d_barrier = nullptr;                // payload of the cross-rank barrier
   size_t comm_bytes_per_period = 0;        // largest upload per period among the ranks (same chunking everywhere)
   cudaStream_t conv_stream = nullptr;      // shared scene: exchange + convolution of chunk c run here, under the mix of chunk c+1
   cudaStream_t result_stream = nullptr;    // the stream a chunk's output is complete on (render stream, or conv_stream)
@@ -178,6 +176,11 @@ struct bear_cuda_renderer {
   int32_t *sh_view[kBusSets] = {};         // the convolution side's own copies of the view / static-delay tables
   float *sh_dstat[kBusSets] = {};
   bool shared_bus = false;                 // the bus rows are the kBusSets sets that peers may map
+  // the rest of the allocation the peers map: an inbox for the ranks' stereo partial mixes (used on the
+  // rank that receives the result) and two arrays of counters (rows complete / partial mix stored)
+  size_t inbox_off = 0, flags_off = 0;     // in floats from bus[0]
+  float *peer_base[kMaxRanks] = {};        // = peer_bus[w][0]
+  int bar_count = 0, out_count = 0;        // synchronisation points passed so far (same on every rank)
   // development aid (BEAR_CUDA_TIMELINE=<path prefix>): when each side of the pipelined calls reached
   // each kernel, in ms since the first mark, written to <prefix>.rank<r> by bear_cuda_synchronize
   struct TimelineMark { cudaEvent_t e; int kernel; int side; uint64_t call; };
@@ -661,6 +664,18 @@ static size_t table_bytes_per_period(const Layout &p)
   return sizeof(float) * ((size_t)2 * p.L * p.N + 2 * p.N + (size_t)p.L * p.M + 2 * p.M + 2 * p.L + (size_t)p.A * p.H + 1);
 }
 
+constexpr unsigned all_ranks = 0xffu;   // (masked by W in the kernel)
+// A synchronisation point of a shared scene: which counter array (offset in ints), which value, whom to
+// tell and whom to wait for.
+PeerSync peer_sync(const bear_cuda_renderer *r, int array, int value, unsigned signal, unsigned wait)
+{
+  PeerSync s{};
+  for (int w = 0; w < r->lay.W; w++) s.flags[w] = reinterpret_cast<int *>(r->peer_base[w] + r->flags_off) + array;
+  s.W = r->lay.W; s.rank = r->lay.rank; s.value = value; s.signal = signal; s.wait = wait;
+  s.err = r->lay.err_flag;
+  return s;
+}
+
 // After pipelined calls the convolution side may still be running on conv_stream: every other entry
 // point first makes the render stream wait for it, and is then what it always was.
 void join_pipelined(bear_cuda_renderer *r)
@@ -784,7 +799,8 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
     if (shared_scene) {
       // every rank's bus rows of this chunk are complete before anyone reads them
       mark(BEAR_CUDA_KERNEL_EXCHANGE, 1);
-      NCK(nccl().AllReduce(r->d_barrier, r->d_barrier, 1, kNcclInt32, kNcclSum, r->comm, sb));
+      launch_peer_sync(peer_sync(r, 0, ++r->bar_count, all_ranks, all_ranks), sb);
+      launches++;
       if (pipe) CK(cudaEventRecord(r->ev_barrier[r->shared_calls & 1], sb));
       mark(BEAR_CUDA_KERNEL_GATHER, 1);
       launch_bus_gather(pc, n, sb, pipe);
@@ -795,18 +811,28 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
     pc.KS = cmac_splits_for(r, n);
     pc.ks_dev = cmac_groups_by_view(pc, n);
     mark(BEAR_CUDA_KERNEL_CMAC, 1); launches += launch_cmac(pc, n, sb);
+    // with a receiving rank, every rank stores its stereo partial mix straight into that rank's inbox
+    // (ordinary stores over NVLink), tells it so, and the receiver adds the W partial mixes up
+    const bool to_inbox = shared_scene && r->comm_root >= 0;
+    if (to_inbox) pc.out = r->peer_base[r->comm_root] + r->inbox_off + (size_t)p.rank * 2 * p.os;
     mark(BEAR_CUDA_KERNEL_IFFT_OUT, 1); launch_ifft_out(pc, n, sb); launches++;
-    if (shared_scene) {
-      // the stereo partial mixes of the ranks are summed (north_star: "only per-block stereo partial
-      // mixes are summed with NCCL"), chunk by chunk so that the sum of chunk c runs under chunk c+1
+    if (to_inbox) {
+      mark(BEAR_CUDA_KERNEL_EXCHANGE, 1);
+      const bool receiver = p.rank == r->comm_root;
+      launch_peer_sync(peer_sync(r, 32, ++r->out_count, 1u << r->comm_root, receiver ? all_ranks : 0u), sb);
+      launches++;
+      if (receiver) {
+        launch_out_sum(p.out, r->bus[0] + r->inbox_off, p.os, p.W, (size_t)k0 * p.B, (size_t)n * p.B, sb);
+        launches++;
+      }
+    } else if (shared_scene) {
+      // no receiving rank: the stereo partial mixes are all-reduced (north_star: "only per-block stereo
+      // partial mixes are summed with NCCL"), chunk by chunk so that the sum of chunk c runs under chunk c+1
       mark(BEAR_CUDA_KERNEL_EXCHANGE, 1);
       NCK(nccl().GroupStart());
       for (int e = 0; e < 2; e++) {
         float *row = p.out + (size_t)e * p.os + (size_t)k0 * p.B;
-        if (r->comm_root >= 0)
-          NCK(nccl().Reduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm_root, r->comm, sb));
-        else
-          NCK(nccl().AllReduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm, sb));
+        NCK(nccl().AllReduce(row, row, (size_t)n * p.B, kNcclFloat32, kNcclSum, r->comm, sb));
       }
       NCK(nccl().GroupEnd());
     }
@@ -932,6 +958,8 @@ void fetch_kernel_errors(bear_cuda_renderer *r)
   if (!bits) return;
   CK(cudaMemsetAsync(r->lay.err_flag, 0, sizeof(int), r->stream));
   r->h_err[0] = 0;
+  if (bits & kErrPeerTimeout) throw CudaFail{"shared scene: a peer GPU did not reach a synchronisation point within ~2 s "
+                                             "(every rank must make the same sequence of process calls)"};
   if (bits & kErrViewRange) throw InvalidArgument{"brir_index out of range (device tables); view 0 was rendered instead"};
   throw InvalidArgument{"a table delay is negative or longer than history_samples - 4 samples (" +
                         std::to_string(r->lay.hist - 4) + "); it was clamped for this call -- create the renderer "
@@ -1684,7 +1712,12 @@ int bear_cuda_comm_blob(bear_cuda_renderer *r, uint32_t rank, void *blob)
       CK(cudaStreamSynchronize(r->stream));
       r->dfree(r->bus[0]);
       const size_t set = (size_t)3 * r->lay.L * r->lay.cs;
-      r->bus[0] = r->dalloc<float>(kBusSets * set);
+      r->inbox_off = round_up(kBusSets * set, 64);
+      r->flags_off = r->inbox_off + round_up((size_t)kMaxRanks * 2 * r->lay.os, 64);
+      // (not render state: bear_cuda_reset leaves the counters alone, they only ever grow)
+      r->bus[0] = r->dalloc<float>(r->flags_off + 64, false);
+      CK(cudaMemsetAsync(r->bus[0], 0, (r->flags_off + 64) * sizeof(float), r->stream));
+      CK(cudaStreamSynchronize(r->stream));
       for (int k = 1; k < kBusSets; k++) r->bus[k] = r->bus[0] + k * set;
       r->lay.cdir = r->bus[0];
       r->lay.qdif = r->bus[0] + (size_t)2 * r->lay.L * r->lay.cs;
@@ -1734,9 +1767,9 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
         r->peer_bus[w][0] = static_cast<float *>(base);
       }
       for (int k = 1; k < kBusSets; k++) r->peer_bus[w][k] = r->peer_bus[w][0] + (size_t)k * 3 * p.L * p.cs;
+      r->peer_base[w] = r->peer_bus[w][0];
     }
     NCK(nccl().CommInitRank(&r->comm, (int)world, bl[0].id, (int)rank));
-    r->d_barrier = r->dalloc<int>(4);
     if (const char *env = std::getenv("BEAR_CUDA_SHARED_CHUNKS")) r->shared_chunks = std::max(1, std::atoi(env));
     if (const char *env = std::getenv("BEAR_CUDA_TIMELINE")) r->timeline_path = env;
     {
