@@ -48,6 +48,7 @@ bool mix_hist_too_large(int hist)
 // system's.  Only what the render path uses is bound; the constants are NCCL 2.x ABI (nccl.h).
 struct NcclUniqueId { char internal[128]; };
 typedef void *NcclComm;
+constexpr int kNcclFloat32 = 7, kNcclSum = 0;
 struct NcclApi {
   void *handle = nullptr;
   int (*GetVersion)(int *) = nullptr;
