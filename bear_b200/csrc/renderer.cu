@@ -804,7 +804,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       launches++;
       if (pipe) CK(cudaEventRecord(r->ev_barrier[r->shared_calls & 1], sb));
       mark(BEAR_CUDA_KERNEL_GATHER, 1);
-      launch_bus_gather(pc, n, sb, pipe);
+      launch_bus_gather(pc, n, sb, pipe && p.W >= 4);   // (two ranks: too few loads in flight in the thin form)
       if (p.l1 > p.l0) launches++;
     }
     if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE, 1); launch_decorrelate(pc, n, sb); launches++; }
@@ -1776,8 +1776,10 @@ int bear_cuda_comm_connect(bear_cuda_renderer *r, uint32_t rank, uint32_t world,
     {
       int least = 0, greatest = 0;
       CK(cudaDeviceGetStreamPriorityRange(&least, &greatest));
+      // the exchange + convolution side is the latency chain of a pipelined call: its (small) kernels go
+      // first whenever a mix CTA retires.  BEAR_CUDA_CONV_PRIORITY=0 switches that off (experiments).
       const char *env = std::getenv("BEAR_CUDA_CONV_PRIORITY");
-      const int prio = env && std::atoi(env) ? greatest : 0;
+      const int prio = env && !std::atoi(env) ? 0 : greatest;
       CK(cudaStreamCreateWithPriority(&r->conv_stream, cudaStreamNonBlocking, prio));
     }
     CK(cudaEventCreateWithFlags(&r->ev_call, cudaEventDisableTiming));
