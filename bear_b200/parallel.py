@@ -66,7 +66,7 @@ def connect_renderers(renderer, rank, world, root=0, group=None):
     """Make the ranks' CUDA renderers one (bear_cuda_comm_connect): the comm blobs travel through
     torch.distributed (any backend -- they are 256 bytes of host data); from then on the exchange is
     the library's own: bus rows read from the peers' memory over NVLink, stereo partial mixes summed
-    with NCCL on the renderers' streams.  root < 0: every rank receives the mix."""
+    on the root (root < 0: all-reduced with NCCL, every rank receives the mix)."""
     import torch.distributed as dist
     blobs = [None] * world
     dist.all_gather_object(blobs, renderer.comm_blob(rank), group=group)

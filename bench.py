@@ -8,7 +8,7 @@ yaw stepping 2 degrees per period so that every period crossfades to a new BRIR 
 pass of the hot path over 10 s of that scene (1872 periods).  With --gpus N the scene is sharded by
 object group, 1024 / N objects per rank (strong scaling): every rank mixes its objects onto the 48 + 24
 bus rows, convolves 24 / N of the loudspeakers on the sum of all ranks' rows (read from the peers over
-NVLink) and the stereo partial mixes are summed with NCCL -- all of it inside the library
+NVLink) and the stereo partial mixes are summed on rank 0 -- all of it inside the library
 (bear_cuda_comm_connect); torch.distributed only carries the 256-byte set-up blobs and the timing
 barrier.  `--workload cfg2_ht` is BASELINE configs[1] (64 moving Objects per GPU, period 512, weak
 scaling), the headline of round 1; at N = 1 it is also reported as the extra key `configs1_64_objects`.
@@ -287,8 +287,8 @@ def workload_config(args, T, world, instances=None):
     c = {"workload": text, "objects_total": total, "objects_per_gpu": total // world, "period": B, "periods_per_step": T,
          "audio_seconds_per_step": T * B / FS,
          "data_file": "synthetic default shape (180 views x 24 x 2 x 2976 taps, 128-tap decorrelators)",
-         "sharding": ("object groups; bus rows of 24/N loudspeakers gathered from the peers over NVLink, NCCL reduce "
-                      "of the stereo partial mixes (bear_cuda_comm_connect); the exchange + convolution of a step run "
+         "sharding": ("object groups; bus rows of 24/N loudspeakers gathered from the peers over NVLink, stereo partial "
+                      "mixes stored into rank 0's inbox and summed there (bear_cuda_comm_connect); the exchange + convolution of a step run "
                       "beside the mix of the next one (pipelined calls)") if world > 1 else "single GPU",
          "l2": "inputs larger than L2 (audio + tables streamed per step >> 126 MB)"}
     if instances:
@@ -538,13 +538,13 @@ def run_ours(args, rank, world, local_rank):
             # bytes each rank pulls over NVLink per step: its nl loudspeakers' 3 bus rows from W - 1 peers
             line["exchange"] = {
                 "nvlink_bytes_read_per_rank_per_step": int(3 * nl * fB * (world - 1)),
-                "nccl_reduce_bytes_per_step": int(2 * fB),
+                "nvlink_bytes_stored_to_root_per_rank_per_step": int(2 * fB),
                 "calls": "bear_cuda_process_device_pipelined" if pipelined else "bear_cuda_process_device",
                 "ms_per_step_unpipelined": ms_joined / args.steps,
                 "ms_per_step": sum(v[0] for k, v in prof.items() if k == "exchange") / max(args.steps, 1),
                 "gather_ms_per_step": sum(v[0] for k, v in prof.items() if k == "bus_gather_kernel") / max(args.steps, 1),
-                "note": "ms_per_step = the one-word NCCL all-reduce that orders the ranks (includes waiting for the "
-                        "slowest rank's mix) + the NCCL reduce of the stereo partial mixes; gather_ms_per_step = "
+                "note": "ms_per_step = the counter exchange that orders the ranks (includes waiting for the slowest "
+                        "rank's mix) + the sum of the stereo partial mixes on rank 0; gather_ms_per_step = "
                         "bus_gather_kernel (the peers' rows over NVLink); CUDA events on rank 0's stream in the "
                         "per-kernel pass"}
         line.update(extras)

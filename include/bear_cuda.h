@@ -248,13 +248,17 @@ int bear_cuda_synchronize(bear_cuda_renderer *r);
  *   - every rank mixes its channels onto its own copy of the 2L + L bus rows (per-ear delays, gain
  *     ramps: the part whose cost grows with the object count);
  *   - rank g then runs decorrelators, static delays, FFTs and the partitioned BRIR multiply-accumulate
- *     for loudspeakers [g L / W, (g+1) L / W) only, on the SUM of all ranks' rows, which its kernels
- *     read from the peers' memory over NVLink while they assemble the FFT windows (cudaIpc mappings,
- *     ordinary loads; a one-word NCCL all-reduce orders the ranks before the rows are read);
- *   - the stereo partial mixes are summed with NCCL (ncclReduce to `root`, or ncclAllReduce when root
- *     is negative) on the renderer's stream, per chunk of periods, so `output` / audio_out of the root
- *     (of every rank) holds the whole scene's render.  On other ranks the process calls accept
- *     output == NULL.
+ *     for loudspeakers [g L / W, (g+1) L / W) only, on the SUM of all ranks' rows, which it gathers
+ *     from the peers' memory over NVLink (cudaIpc mappings, ordinary loads).  The ranks are ordered by
+ *     counters they store into each other's memory (release / acquire at system scope): a rank reads
+ *     a peer's rows once that peer's counter says they are complete;
+ *   - with root >= 0 every rank stores its stereo partial mix straight into an inbox on the root
+ *     (ordinary stores over NVLink) and the root adds the W partial mixes up in rank order; with
+ *     root < 0 the partial mixes are all-reduced with NCCL and every rank holds the result.  Either
+ *     way per chunk of periods, so `output` / audio_out of the root (of every rank) holds the whole
+ *     scene's render.  On other ranks the process calls accept output == NULL.
+ *   A rank that does not reach a synchronisation point within ~2 s makes its peers' next
+ *   bear_cuda_synchronize (or host-buffer call) fail with BEAR_CUDA_ERR_CUDA instead of hanging.
  * Every rank must make the same sequence of process calls (same T, same chunking).  NCCL is bound at
  * run time (dlopen of libnccl.so.2: the copy already in the process, e.g. PyTorch's, else the
  * system's); a renderer that is never connected does not need it.
@@ -324,7 +328,7 @@ int bear_cuda_get_info(const bear_cuda_renderer *r, bear_cuda_info *info);
 #define BEAR_CUDA_KERNEL_CARRY 6
 #define BEAR_CUDA_KERNEL_CONTROL 7
 #define BEAR_CUDA_KERNEL_MIX_AUX 8   /* mix_prep_kernel (+ bus_sum_kernel in short launches) */
-#define BEAR_CUDA_KERNEL_EXCHANGE 9  /* cross-GPU ordering collective and stereo reduce of a shared scene (NCCL) */
+#define BEAR_CUDA_KERNEL_EXCHANGE 9  /* cross-GPU synchronisation and the sum of the stereo partial mixes of a shared scene */
 #define BEAR_CUDA_KERNEL_GATHER 10   /* bus_gather_kernel: the peers' bus rows over NVLink */
 #define BEAR_CUDA_NUM_KERNELS 11
 
