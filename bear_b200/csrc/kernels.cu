@@ -1941,13 +1941,19 @@ __global__ void __launch_bounds__(256) carry_kernel(CarryPlan plan)
   int e = 0;
   while (e + 1 < plan.n && (int)blockIdx.x >= plan.row_start[e + 1]) e++;
   const CarryRow r = plan.e[e];
-  float *row = r.base + (size_t)(blockIdx.x - plan.row_start[e]) * r.stride;
-  for (int c0 = 0; c0 < r.count; c0 += blockDim.x) {
+  const long long first = (long long)(blockIdx.x - plan.row_start[e]) * r.stride;
+  float *row = r.base + first;
+  const int count = r.total > 0 ? (int)min((long long)r.count, r.total - first) : r.count;
+  if (r.shift >= count) {   // source and destination apart: a plain copy (table slots, long calls)
+    for (int i = threadIdx.x; i < count; i += blockDim.x) row[i] = row[i + r.shift];
+    return;
+  }
+  for (int c0 = 0; c0 < count; c0 += blockDim.x) {
     const int i = c0 + threadIdx.x;
     float v = 0.f;
-    if (i < r.count) v = row[i + r.shift];
+    if (i < count) v = row[i + r.shift];
     __syncthreads();
-    if (i < r.count) row[i] = v;
+    if (i < count) row[i] = v;
     __syncthreads();
   }
 }

@@ -104,6 +104,7 @@ struct CarryRow {
   long long stride;   // floats between rows
   int count;          // floats to move per row
   long long shift;    // source offset (floats) relative to destination
+  long long total;    // > 0: the rows are pieces of ONE run of `total` floats (the last piece is shorter)
 };
 constexpr int kMaxCarry = 16;
 struct CarryPlan {

@@ -854,7 +854,15 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
   int n = 0, rows = 0, nc = 0, rows_c = 0;
   auto add_to = [&](CarryPlan &pl, int &cnt, int &nrows_total, float *base, int nrows, long long stride, int count, long long shift) {
     if (nrows <= 0 || count <= 0) return;
-    pl.e[cnt] = CarryRow{base, nrows, stride, count, shift};
+    constexpr int piece = 1024;
+    if (nrows == 1 && shift >= count && count > 2 * piece) {
+      // one long run whose source and destination do not overlap (a table's last slot): cut into pieces,
+      // one CTA each, instead of one CTA walking it 256 floats at a time
+      nrows = (count + piece - 1) / piece;
+      pl.e[cnt] = CarryRow{base, nrows, piece, piece, shift, count};
+    } else {
+      pl.e[cnt] = CarryRow{base, nrows, stride, count, shift, 0};
+    }
     pl.row_start[cnt] = nrows_total;
     nrows_total += nrows;
     cnt++;
