@@ -478,87 +478,113 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 //   [8..]    direct gains, slot pairs:  (g0[2i], g0[2i+1], dg[2i], dg[2i+1]),  i = 0 .. kMixSlots/2 - 1
 //   then     diffuse gains, same layout (objects only)
 // Key: bit 31 dense | loudspeaker mask << 1 | has_diffuse.
-// grid: (ceil((N+M)/128), periods); block 128; one thread per channel (coalesced table reads).
-__global__ void __launch_bounds__(128) mix_prep_kernel(Layout p, int T)
+// grid: (ceil(N/128) + ceil(M/128), periods); block 128; one thread per channel (coalesced table reads),
+// a CTA holds channels of one kind.  The kernel is bound by memory transactions, not by bytes, so the
+// scattered accesses go through shared memory: while a thread walks its 4 L table entries (high
+// loudspeakers first) it pushes the (start, delta) values of the non-zero ones onto its own stack in
+// shared memory -- gathering them from global memory afterwards cost up to 24 lines per load -- and the
+// 128-byte records are exchanged through shared memory so that the CTA writes them as contiguous lines.
+constexpr int kPrepThreads = 128;
+__global__ void __launch_bounds__(kPrepThreads) mix_prep_kernel(Layout p, int T)
 {
-  const int c = blockIdx.x * 128 + threadIdx.x, k = p.k0 + blockIdx.y;
+  __shared__ float stack[4 * kMixSlots][kPrepThreads];            // [4 s + {g0, g1, q0, q1}][thread]
+  __shared__ float4 recs[kPrepThreads * (kMixRecWords / 4)];
+  const int tid = threadIdx.x, k = p.k0 + blockIdx.y;
   const int C = p.N + p.M, L = p.L;
-  if (c >= C) return;
-  const bool obj = c < p.N;
-  const int ci = obj ? c : c - p.N, ld = obj ? p.N : p.M;
-  float *rec = p.mix_recs + ((size_t)k * C + c) * kMixRecWords;
-  // delays of periods k-1 (slot k) and k (slot k+1), seconds -> samples
-  const float *ds = (obj ? p.d_dir : p.d_ds) + (size_t)k * 2 * ld + 2 * ci;
-  const float dmax = (float)(p.hist - 4);
-  float4 dl;
-  {
-    float a0 = ds[0] * p.fs, a1 = ds[2 * ld] * p.fs, b0 = ds[1] * p.fs, b1 = ds[2 * ld + 1] * p.fs;
-    // a table delay outside [0, history - 4] cannot be rendered (the reference allows up to 1 s,
-    // per_ear_delay.cpp:25): flagged, reported by the call, and clamped so that no read leaves the tile
-    if (!(a1 >= 0.f && a1 <= dmax) || !(b1 >= 0.f && b1 <= dmax)) atomicOr(p.err_flag, kErrDelayRange);
-    a0 = fminf(fmaxf(a0, 0.f), dmax); a1 = fminf(fmaxf(a1, 0.f), dmax);
-    b0 = fminf(fmaxf(b0, 0.f), dmax); b1 = fminf(fmaxf(b1, 0.f), dmax);
-    dl = make_float4(a0, a1 - a0, b0, b1 - b0);
-  }
-  const float *gd = (obj ? p.g_dir : p.g_ds) + (size_t)k * L * ld + ci;   // [slot k: L rows][slot k+1: L rows]
-  const float *gq = p.g_dif + (size_t)k * L * ld + ci;
-  unsigned mask = 0u, any_q = 0u;
-  for (int l0 = 0; l0 < L; l0 += 8) {   // eight loudspeakers' table entries are loaded before any is tested
-    float va[8], vb[8], qa[8], qb[8];
+  const int nbo = (p.N + kPrepThreads - 1) / kPrepThreads;
+  const bool obj = (int)blockIdx.x < nbo;
+  const int cb = (obj ? blockIdx.x : blockIdx.x - nbo) * kPrepThreads, ld = obj ? p.N : p.M;
+  const int cnt = min(kPrepThreads, ld - cb);
+  const bool on = tid < cnt;
+  const int ci = cb + tid, c = obj ? ci : p.N + ci;
+  constexpr int Q = kMixRecWords / 4;
+  float4 rec[Q];
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-      const int l = min(l0 + i, L - 1);
-      va[i] = gd[(size_t)l * ld]; vb[i] = gd[(size_t)(L + l) * ld];
-      qa[i] = obj ? gq[(size_t)l * ld] : 0.f; qb[i] = obj ? gq[(size_t)(L + l) * ld] : 0.f;
+  for (int i = 0; i < Q; i++) rec[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (on) {
+    const float *gd = (obj ? p.g_dir : p.g_ds) + (size_t)k * L * ld + ci;   // [slot k: L rows][slot k+1: L rows]
+    const float *gq = p.g_dif + (size_t)k * L * ld + ci;
+    unsigned mask = 0u, any_q = 0u;
+    int ns = 0;
+    unsigned spk[2] = {0u, 0u};
+    for (int l0 = ((L - 1) & ~7); l0 >= 0; l0 -= 8) {   // eight loudspeakers' table entries are loaded before any is tested
+      float va[8], vb[8], qa[8], qb[8];
+#pragma unroll
+      for (int i = 0; i < 8; i++) {
+        const int l = min(l0 + i, L - 1);
+        va[i] = gd[(size_t)l * ld]; vb[i] = gd[(size_t)(L + l) * ld];
+        qa[i] = obj ? gq[(size_t)l * ld] : 0.f; qb[i] = obj ? gq[(size_t)(L + l) * ld] : 0.f;
+      }
+#pragma unroll
+      for (int i = 7; i >= 0; i--) {
+        if (l0 + i < L) {
+          const bool nzq = qa[i] != 0.f || qb[i] != 0.f;
+          if (va[i] != 0.f || vb[i] != 0.f || nzq) {
+            mask |= 1u << (l0 + i);
+            if (ns < kMixSlots) {   // slots in DESCENDING loudspeaker order (see below)
+              stack[4 * ns + 0][tid] = va[i]; stack[4 * ns + 1][tid] = vb[i];
+              stack[4 * ns + 2][tid] = qa[i]; stack[4 * ns + 3][tid] = qb[i];
+              spk[ns >> 2] |= (unsigned)(l0 + i) << (8 * (ns & 3));
+            }
+            ns++;
+          }
+          if (nzq) any_q = 1u;
+        }
+      }
     }
+    // delays of periods k-1 (slot k) and k (slot k+1), seconds -> samples
+    const float *ds = (obj ? p.d_dir : p.d_ds) + (size_t)k * 2 * ld + 2 * ci;
+    const float dmax = (float)(p.hist - 4);
+    {
+      float a0 = ds[0] * p.fs, a1 = ds[2 * ld] * p.fs, b0 = ds[1] * p.fs, b1 = ds[2 * ld + 1] * p.fs;
+      // a table delay outside [0, history - 4] cannot be rendered (the reference allows up to 1 s,
+      // per_ear_delay.cpp:25): flagged, reported by the call, and clamped so that no read leaves the tile
+      if (!(a1 >= 0.f && a1 <= dmax) || !(b1 >= 0.f && b1 <= dmax)) atomicOr(p.err_flag, kErrDelayRange);
+      a0 = fminf(fmaxf(a0, 0.f), dmax); a1 = fminf(fmaxf(a1, 0.f), dmax);
+      b0 = fminf(fmaxf(b0, 0.f), dmax); b1 = fminf(fmaxf(b1, 0.f), dmax);
+      rec[0] = make_float4(a0, a1 - a0, b0, b1 - b0);
+    }
+    unsigned *keys = p.mix_keys + (size_t)k * C;
+    if (ns > kMixSlots) {
+      keys[c] = 0x80000000u | any_q;
+      rec[1] = make_float4(__uint_as_float(255u | any_q << 8), 0.f, 0.f, 0.f);
+    } else {
+      keys[c] = mask << 1 | any_q;
+      // Slots in DESCENDING loudspeaker order: the channels are sorted by the mask as a number, so
+      // neighbours in the sorted order share their highest loudspeakers, i.e. their first slots, which
+      // mix_kernel can keep accumulating across a run boundary.
+      float g0[kMixSlots], dg[kMixSlots], q0[kMixSlots], dq[kMixSlots];
 #pragma unroll
-    for (int i = 0; i < 8; i++) {
-      if (l0 + i < L) {
-        const bool nzq = qa[i] != 0.f || qb[i] != 0.f;
-        if (va[i] != 0.f || vb[i] != 0.f || nzq) mask |= 1u << (l0 + i);
-        if (nzq) any_q = 1u;
+      for (int s = 0; s < kMixSlots; s++) {
+        g0[s] = dg[s] = q0[s] = dq[s] = 0.f;
+        if (s < ns) {
+          const float a = stack[4 * s + 0][tid], b = stack[4 * s + 1][tid];
+          g0[s] = a; dg[s] = b - a;
+          const float qa = stack[4 * s + 2][tid], qb = stack[4 * s + 3][tid];
+          q0[s] = qa; dq[s] = qb - qa;
+        } else {
+          spk[s >> 2] |= 255u << (8 * (s & 3));   // 255: slot not needed
+        }
+      }
+      rec[1] = make_float4(__uint_as_float((unsigned)ns | any_q << 8), __uint_as_float(spk[0]), __uint_as_float(spk[1]), 0.f);
+#pragma unroll
+      for (int i = 0; i < kMixSlots / 2; i++) {
+        rec[2 + i] = make_float4(g0[2 * i], g0[2 * i + 1], dg[2 * i], dg[2 * i + 1]);
+        rec[2 + kMixSlots / 2 + i] = make_float4(q0[2 * i], q0[2 * i + 1], dq[2 * i], dq[2 * i + 1]);
       }
     }
   }
-  const int ns = __popc(mask);
-  unsigned *keys = p.mix_keys + (size_t)k * C;
-  if (ns > kMixSlots) {
-    keys[c] = 0x80000000u | any_q;
-    reinterpret_cast<float4 *>(rec)[0] = dl;
-    reinterpret_cast<uint4 *>(rec)[1] = make_uint4(255u | any_q << 8, 0u, 0u, 0u);
-    return;
-  }
-  keys[c] = mask << 1 | any_q;
-  // Slots in DESCENDING loudspeaker order: the channels are sorted by the mask as a number, so neighbours
-  // in the sorted order share their highest loudspeakers, i.e. their first slots, which mix_kernel can
-  // keep accumulating across a run boundary.  (The second, gathering pass re-reads <= 6 x 4 entries that
-  // the first left in L1; writing them out of the first pass with scattered stores measured slower.)
-  float g0[kMixSlots], dg[kMixSlots], q0[kMixSlots], dq[kMixSlots];
-  unsigned spk[2] = {0u, 0u};
-  unsigned m = mask;
+  // 16-byte piece i of thread t's record sits at piece (i + t) mod 8 of its 128 bytes: a quarter warp's
+  // stores then hit eight different bank groups
+  static_assert(Q == 8, "record swizzle assumes 8 pieces of 16 bytes");
 #pragma unroll
-  for (int s = 0; s < kMixSlots; s++) {
-    g0[s] = dg[s] = q0[s] = dq[s] = 0.f;
-    unsigned l = 255u;                       // 255: slot not needed
-    if (m) {
-      l = 31u - (unsigned)__clz(m);
-      m &= ~(1u << l);
-      const float a = gd[(size_t)l * ld], b = gd[(size_t)(L + l) * ld];
-      g0[s] = a; dg[s] = b - a;
-      if (obj) {
-        const float qa = gq[(size_t)l * ld], qb = gq[(size_t)(L + l) * ld];
-        q0[s] = qa; dq[s] = qb - qa;
-      }
-    }
-    spk[s >> 2] |= l << (8 * (s & 3));
-  }
-  float4 *r4 = reinterpret_cast<float4 *>(rec);
-  r4[0] = dl;
-  reinterpret_cast<uint4 *>(rec)[1] = make_uint4((unsigned)ns | any_q << 8, spk[0], spk[1], 0u);
+  for (int i = 0; i < Q; i++) recs[tid * Q + ((i + tid) & (Q - 1))] = rec[i];
+  __syncthreads();
+  float4 *dst = reinterpret_cast<float4 *>(p.mix_recs + ((size_t)k * C + (obj ? cb : p.N + cb)) * kMixRecWords);
 #pragma unroll
-  for (int i = 0; i < kMixSlots / 2; i++) {
-    r4[2 + i] = make_float4(g0[2 * i], g0[2 * i + 1], dg[2 * i], dg[2 * i + 1]);
-    r4[2 + kMixSlots / 2 + i] = make_float4(q0[2 * i], q0[2 * i + 1], dq[2 * i], dq[2 * i + 1]);
+  for (int it = 0; it < Q; it++) {
+    const int idx = it * kPrepThreads + tid, t = idx / Q, ph = idx % Q;
+    if (t < cnt) dst[t * Q + ((ph - t) & (Q - 1))] = recs[idx];
   }
 }
 
@@ -1118,7 +1144,8 @@ static size_t mix_dense_smem_bytes(int hist)
 void launch_mix_prep(const Layout &p, int T, cudaStream_t st)
 {
   const int C = p.N + p.M, per = (C + p.S - 1) / p.S;
-  mix_prep_kernel<<<dim3((C + 127) / 128, T), 128, 0, st>>>(p, T);
+  const dim3 grid((p.N + kPrepThreads - 1) / kPrepThreads + (p.M + kPrepThreads - 1) / kPrepThreads, T);
+  mix_prep_kernel<<<grid, kPrepThreads, 0, st>>>(p, T);
   int n2 = 1;
   while (n2 < per) n2 <<= 1;
   mix_order_kernel<<<dim3(T, p.S), 256, (size_t)n2 * sizeof(unsigned long long), st>>>(p, T);
