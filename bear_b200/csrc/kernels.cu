@@ -596,37 +596,78 @@ __global__ void __launch_bounds__(kPrepThreads) mix_prep_kernel(Layout p, int T)
 // grid: (periods, S); block 256; dynamic shared memory: 8 bytes x the next power of two >= channels per split.
 __global__ void __launch_bounds__(256) mix_order_kernel(Layout p, int T)
 {
-  extern __shared__ unsigned long long skey[];
+  extern __shared__ __align__(16) unsigned sk[];   // [n2] sort words, then [n2] the keys by local channel
   const int k = p.k0 + blockIdx.x, s = blockIdx.y;
   const int C = p.N + p.M;
   const int per = (C + p.S - 1) / p.S;
   const int c0 = min(C, s * per), c1 = min(C, c0 + per), len = c1 - c0;
-  int n2 = 1;
-  while (n2 < len) n2 <<= 1;
+  int n2 = 1, bits = 0;
+  while (n2 < len) { n2 <<= 1; bits++; }
+  unsigned *kraw = sk + n2;
   const unsigned *keys = p.mix_keys + (size_t)k * C;
-  for (int i = threadIdx.x; i < n2; i += 256)
-    skey[i] = i < len ? ((unsigned long long)keys[c0 + i] << 32 | (unsigned)(c0 + i)) : ~0ull;
+  // One 32-bit word per channel: (sort value of its loudspeaker set) << bits | local channel.  Up to 256
+  // channels the 24-bit set itself fits (dense channels count as the full set and sort last), so the order
+  // is the numeric order of the sets, which the slot-keeping form of mix_kernel relies on; beyond that
+  // a (32 - bits)-bit hash of the set stands in -- all that matters there is that equal sets end up
+  // next to each other (two sets with one hash merely split each other's runs; runs are detected on
+  // the real keys below).  The diffuse flag is not part of the order: it does not separate runs.
+  const bool exact = 24 + bits <= 32;
+  const unsigned top = 0xffffffffu >> bits;        // sort value of the dense channels
+  for (int i = threadIdx.x; i < n2; i += 256) {
+    unsigned w = 0xffffffffu, key = 0xffffffffu;
+    if (i < len) {
+      key = keys[c0 + i];
+      const unsigned set = key >> 1 & 0xffffffu;
+      unsigned h = exact ? set : min((set * 2654435761u) >> bits, top - 1u);
+      if (key >> 31) h = exact ? 0xffffffu : top;
+      w = h << bits | (unsigned)i;
+    }
+    sk[i] = w;
+    kraw[i] = key;
+  }
   __syncthreads();
-  for (int size = 2; size <= n2; size <<= 1)
-    for (int stride = size >> 1; stride > 0; stride >>= 1) {
-      for (int i = threadIdx.x; i < n2 / 2; i += 256) {
-        const int lo = 2 * i - (i & (stride - 1)), hi = lo + stride;
-        const bool up = (lo & size) == 0;
-        const unsigned long long a = skey[lo], b = skey[hi];
-        if ((a > b) == up) { skey[lo] = b; skey[hi] = a; }
+  // Bitonic network, two consecutive strides (2h, h) per pass: a thread holds the four elements
+  // b + {0, h, 2h, 3h} in registers for both compare-exchange steps, which halves the trips through
+  // shared memory and the barriers (30 instead of 55 passes for 1024 channels).
+  auto cswap = [](unsigned &a, unsigned &b, bool up) {
+    const unsigned lo = min(a, b), hi = max(a, b);
+    a = up ? lo : hi; b = up ? hi : lo;
+  };
+  for (int size = 2; size <= n2; size <<= 1) {
+    int stride = size >> 1;
+    for (; stride >= 2; stride >>= 2) {
+      const int h = stride >> 1;
+      for (int g = threadIdx.x; g < n2 / 4; g += 256) {
+        const int b = (g / h) * 4 * h + (g % h);
+        const bool up = (b & size) == 0;
+        unsigned e0 = sk[b], e1 = sk[b + h], e2 = sk[b + 2 * h], e3 = sk[b + 3 * h];
+        cswap(e0, e2, up); cswap(e1, e3, up);
+        cswap(e0, e1, up); cswap(e2, e3, up);
+        sk[b] = e0; sk[b + h] = e1; sk[b + 2 * h] = e2; sk[b + 3 * h] = e3;
       }
       __syncthreads();
     }
+    if (stride == 1) {   // an odd number of strides: the last one on its own
+      for (int i = threadIdx.x; i < n2 / 2; i += 256) {
+        const bool up = (2 * i & size) == 0;
+        uint2 v = reinterpret_cast<uint2 *>(sk)[i];
+        cswap(v.x, v.y, up);
+        reinterpret_cast<uint2 *>(sk)[i] = v;
+      }
+      __syncthreads();
+    }
+  }
+  const unsigned lmask = (unsigned)n2 - 1u;
   unsigned *order = p.mix_order + (size_t)k * C + c0;
   int ndense = 0;
   for (int i = threadIdx.x; i < len; i += 256) {
-    const unsigned key = (unsigned)(skey[i] >> 32), c = (unsigned)skey[i];
-    const unsigned prev = i ? (unsigned)(skey[i - 1] >> 32) : ~0u;
+    const unsigned li = sk[i] & lmask, key = kraw[li], c = (unsigned)c0 + li;
+    const unsigned prev = i ? kraw[sk[i - 1] & lmask] : ~0u;
     const unsigned start = (i == 0 || (key >> 1) != (prev >> 1)) ? 1u : 0u;
     unsigned run = 0u;
     if (start) {   // the first channel of a run carries its length (runs are short: a handful of channels)
       int j = i + 1;
-      while (j < len && (unsigned)(skey[j] >> 33) == key >> 1) j++;
+      while (j < len && kraw[sk[j] & lmask] >> 1 == key >> 1) j++;
       run = (unsigned)(j - i - 1);
     }
     order[i] = c | run << 17 | (key & 1u) << 30 | start << 31;
