@@ -636,9 +636,9 @@ __global__ void __launch_bounds__(256) mix_order_kernel(Layout p, int T)
   for (int size = 2; size <= n2; size <<= 1) {
     int stride = size >> 1;
     for (; stride >= 2; stride >>= 2) {
-      const int h = stride >> 1;
+      const int h = stride >> 1, lh = 31 - __clz(h);
       for (int g = threadIdx.x; g < n2 / 4; g += 256) {
-        const int b = (g / h) * 4 * h + (g % h);
+        const int b = ((g >> lh) << (lh + 2)) + (g & (h - 1));
         const bool up = (b & size) == 0;
         unsigned e0 = sk[b], e1 = sk[b + h], e2 = sk[b + 2 * h], e3 = sk[b + 3 * h];
         cswap(e0, e2, up); cswap(e1, e3, up);
@@ -660,17 +660,32 @@ __global__ void __launch_bounds__(256) mix_order_kernel(Layout p, int T)
   const unsigned lmask = (unsigned)n2 - 1u;
   unsigned *order = p.mix_order + (size_t)k * C + c0;
   int ndense = 0;
-  for (int i = threadIdx.x; i < len; i += 256) {
-    const unsigned li = sk[i] & lmask, key = kraw[li], c = (unsigned)c0 + li;
-    const unsigned prev = i ? kraw[sk[i - 1] & lmask] : ~0u;
-    const unsigned start = (i == 0 || (key >> 1) != (prev >> 1)) ? 1u : 0u;
-    unsigned run = 0u;
-    if (start) {   // the first channel of a run carries its length (runs are short: a handful of channels)
-      int j = i + 1;
-      while (j < len && kraw[sk[j] & lmask] >> 1 == key >> 1) j++;
-      run = (unsigned)(j - i - 1);
+  for (int i0 = 0; i0 < len; i0 += 256) {   // (uniform trip count: the ballot below needs whole warps)
+    const int i = i0 + threadIdx.x;
+    const bool valid = i < len;
+    unsigned key = 0u, c = 0u, start = 0u;
+    if (valid) {
+      const unsigned li = sk[i] & lmask;
+      key = kraw[li]; c = (unsigned)c0 + li;
+      const unsigned prev = i ? kraw[sk[i - 1] & lmask] : ~0u;
+      start = (i == 0 || (key >> 1) != (prev >> 1)) ? 1u : 0u;
     }
-    order[i] = c | run << 17 | (key & 1u) << 30 | start << 31;
+    // the first channel of a run carries its length: up to the next run start among the warp's 32
+    // consecutive positions, else to the end of those and on for as long as the set stays the same
+    const unsigned starts = __ballot_sync(0xffffffffu, start != 0u);
+    unsigned run = 0u;
+    if (start) {
+      const unsigned lane = threadIdx.x & 31u, rest = lane == 31u ? 0u : starts >> (lane + 1u);
+      int j;
+      if (rest) {
+        j = i + __ffs(rest);
+      } else {
+        j = (i | 31) + 1;
+        while (j < len && kraw[sk[j] & lmask] >> 1 == key >> 1) j++;
+      }
+      run = (unsigned)(min(j, len) - i - 1);
+    }
+    if (valid) order[i] = c | run << 17 | (key & 1u) << 30 | start << 31;
     ndense += key >> 31;
   }
   __shared__ int sdense;
