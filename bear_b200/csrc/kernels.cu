@@ -902,11 +902,11 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
       }
       const int jend = min(cnt, j + run_left);
       run_left -= jend - j;
-      // the channels of the run that are in this chunk: nothing in here depends on the gains
-      for (; j < jend; j++, rec += kMixRecWords, xr += XW) {
-        const f32x2 x2 = x2n;
-        if (j + 1 < cnt) x2n = lagrange(rec + kMixRecWords, xr + XW);   // the next channel's reads, ahead of this one's sums
-        const float4 *r4 = reinterpret_cast<const float4 *>(rec);
+      // the channels of the run that are in this chunk: nothing in here depends on the gains.  Two per
+      // trip, so that the delayed samples of the channel after the current one (whose reads are issued
+      // ahead of the current one's sums) alternate between two names instead of being moved
+      auto channel = [&](int jj, const float *rc, const float *xp, const f32x2 x2) {
+        const float4 *r4 = reinterpret_cast<const float4 *>(rc);
 #pragma unroll
         for (int i = 0; i < kMixSlots / 2; i++) {   // all slots, used or not (unused ones hold zero gains): no branch
           const float4 g = r4[2 + i];
@@ -915,8 +915,8 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
           fma2_acc(acc[2 * i], splat2(ga), x2);
           fma2_acc(acc[2 * i + 1], splat2(gb), x2);
         }
-        if (sord[st][j] >> 30 & 1u) {
-          const f32x2 x0 = splat2(xr[0]);
+        if (sord[st][jj] >> 30 & 1u) {
+          const f32x2 x0 = splat2(xp[0]);
           qdirty = (1u << kMixSlots) - 1u;
 #pragma unroll
           for (int i = 0; i < kMixSlots / 2; i++) {
@@ -924,6 +924,18 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
             fma2_acc(accQ[i], fma2(rg2, pack2(q.z, q.w), pack2(q.x, q.y)), x0);
           }
         }
+      };
+      for (; j + 1 < jend; j += 2, rec += 2 * kMixRecWords, xr += 2 * XW) {
+        const f32x2 x2b = lagrange(rec + kMixRecWords, xr + XW);
+        channel(j, rec, xr, x2n);
+        if (j + 2 < cnt) x2n = lagrange(rec + 2 * kMixRecWords, xr + 2 * XW);
+        channel(j + 1, rec + kMixRecWords, xr + XW, x2b);
+      }
+      if (j < jend) {
+        const f32x2 x2 = x2n;
+        if (j + 1 < cnt) x2n = lagrange(rec + kMixRecWords, xr + XW);
+        channel(j, rec, xr, x2);
+        j++; rec += kMixRecWords; xr += XW;
       }
     }
     __syncwarp();
