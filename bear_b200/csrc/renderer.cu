@@ -804,7 +804,7 @@ void run_pipeline(bear_cuda_renderer *r, int T, int chunk, Before &&before_chunk
       launches++;
       if (pipe) CK(cudaEventRecord(r->ev_barrier[r->shared_calls & 1], sb));
       mark(BEAR_CUDA_KERNEL_GATHER, 1);
-      launch_bus_gather(pc, n, sb, pipe && p.W >= 4);   // (two ranks: too few loads in flight in the thin form)
+      launch_bus_gather(pc, n, sb, pipe && p.W > 4);   // (measured: the thin form pays from 8 ranks; at 2 and 4 the wide one is faster)
       if (p.l1 > p.l0) launches++;
     }
     if (p.dif && p.l1 > p.l0) { mark(BEAR_CUDA_KERNEL_DECORRELATE, 1); launch_decorrelate(pc, n, sb); launches++; }
