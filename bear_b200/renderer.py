@@ -391,11 +391,15 @@ class Renderer:
         if tr.shape != (self.N + self.M + self.H,):
             raise ValueError("tracks must have one entry per input channel")
         keep = [frames, tr]
-        out = np.empty((2, T * self.B), np.float32) if output is None else output
+        if output is False:       # a rank of a shared scene that does not receive the mix
+            out, out_ptr, out_stride = None, None, 0
+        else:
+            out = np.empty((2, T * self.B), np.float32) if output is None else output
+            out_ptr, out_stride = C.c_void_p(out.ctypes.data), out.strides[0] // 4
         t = self._tables_struct(tables, keep)
         self._check(self._l.bear_cuda_process_batch_frames(
             self._h, T, C.c_void_p(frames.ctypes.data), self.FRAME_FORMATS[fmt], int(frame_channels),
-            tr.ctypes.data_as(_i32p), C.byref(t), C.c_void_p(out.ctypes.data), out.strides[0] // 4))
+            tr.ctypes.data_as(_i32p), C.byref(t), out_ptr, out_stride))
         return out
 
     def render(self, objects, direct_speakers, hoa, tables, batch=None, output=None):

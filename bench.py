@@ -61,6 +61,7 @@ def parse_args():
     ap.add_argument("--cpu-sample-blocks", type=int, default=0, help="blocks of the CPU sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true", help="only the headline workload")
+    ap.add_argument("--no-frames-e2e", action="store_true", help="skip the 16-bit-frames form of the e2e call")
     ap.add_argument("--no-pipeline", action="store_true",
                     help="N > 1: plain bear_cuda_process_device calls instead of the pipelined ones")
     ap.add_argument("--chunk-blocks", type=int, default=0, help="periods per launch group (0 = library default)")
@@ -425,6 +426,21 @@ def run_ours(args, rank, world, local_rank):
     e2e_prof = {k: v[0] / max(v[1], 1) for k, v in r.get_profile(reset=True).items() if v[1]}
     r.set_profiling(False)
 
+    # the same call fed with the file's interleaved 16-bit PCM frames (bear_cuda_process_batch_frames):
+    # half the audio bytes over PCIe, de-interleaving and conversion on the device, same tables
+    ms_s16 = None
+    if not args.no_frames_e2e:
+        from bear_b200.renderer import pinned_empty
+        h_frames = pinned_empty((T * B, mine), np.int16)
+        for c0 in range(0, mine, 64):   # (in pieces: the float intermediates of the whole scene are 2 GB each)
+            h_frames[:, c0:c0 + 64] = np.clip(np.round(leg.audio[c0:c0 + 64].T * 32768.0), -32768, 32767)
+        tracks = np.arange(mine, dtype=np.int32)
+        step_s16 = lambda: r.process_batch_frames(h_frames, tracks, leg.h_tb, output=leg.h_out)
+        step_s16()
+        ms_s16 = timed(step_s16, e2e_steps)
+        s16_bytes = h_frames.nbytes + sum(v.nbytes for v in leg.tb.values())
+        del h_frames
+
     # the PCIe floor of that call: the same bytes copied host->device from pinned memory, nothing else
     h_flat = torch.from_numpy(leg.h_audio.reshape(-1))
     d_flat = torch.empty(leg.h2d // 4, dtype=torch.float32, device="cuda")
@@ -531,6 +547,11 @@ def run_ours(args, rank, world, local_rank):
                     "h2d_copy_only_ms": ms_copy, "h2d_copy_only_gbs_per_gpu": leg.h2d / ms_copy * 1e-6,
                     "api": "bear_cuda_process_batch (pinned host buffers; every rank uploads its objects, rank 0 "
                            "receives the mix)"},
+            "e2e_s16_frames": None if ms_s16 is None else {
+                "value": total * audio_s * e2e_steps / (ms_s16 * 1e-3), "unit": UNIT, "ms_per_step": ms_s16 / e2e_steps,
+                "h2d_bytes_per_step": int(s16_bytes * world), "d2h_bytes_per_step": d2h_all,
+                "api": "bear_cuda_process_batch_frames: the same step from interleaved 16-bit PCM frames as a file "
+                       "reader holds them (quantised audio, so not the headline e2e)"},
             "gpu_launches": int(launches),
             "clocks": clk,
         }
