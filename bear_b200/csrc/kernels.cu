@@ -1161,7 +1161,7 @@ void launch_bus_gather(const Layout &p, int T, cudaStream_t st, bool thin)
 // peer_sync_kernel: one warp; lane w looks after rank w.  Everything this GPU wrote before the launch
 // (kernel boundary) is made visible system-wide before the counters are stored; a lane that waits
 // reads its counter with acquire semantics, so kernels launched after this one see the peers' data.
-// A peer that never arrives raises the error flag after ~2 s instead of hanging the GPU.
+// A peer that never arrives raises the error flag after ~20 s instead of hanging the GPU.
 __global__ void __launch_bounds__(32) peer_sync_kernel(PeerSync s)
 {
   const int w = threadIdx.x;
@@ -1176,7 +1176,7 @@ __global__ void __launch_bounds__(32) peer_sync_kernel(PeerSync s)
       int v;
       asm volatile("ld.acquire.sys.global.s32 %0, [%1];" : "=r"(v) : "l"(s.flags[s.rank] + w) : "memory");
       if (v - s.value >= 0) break;
-      if (clock64() - t0 > (4LL << 30)) { atomicOr(s.err, kErrPeerTimeout); break; }
+      if (clock64() - t0 > kPeerTimeoutCycles) { atomicOr(s.err, kErrPeerTimeout); break; }
     }
   }
 }

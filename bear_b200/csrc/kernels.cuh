@@ -20,7 +20,8 @@ constexpr int kMaxRanks = 8;      // GPUs that can share one scene (bear_cuda_co
 // bits of Layout::err_flag (checked by the host after a call has finished)
 constexpr int kErrDelayRange = 1; // a table delay is negative or beyond history_samples - 4
 constexpr int kErrViewRange = 2;  // a brir_index on the device-resident path is outside [0, V)
-constexpr int kErrPeerTimeout = 4;  // a peer GPU did not reach a synchronisation point of a shared scene in ~2 s
+constexpr int kErrPeerTimeout = 4;  // a peer GPU did not reach a synchronisation point of a shared scene in ~20 s
+constexpr long long kPeerTimeoutCycles = 40LL << 30;   // SM clock cycles (1.9 GHz: 22 s): host work between calls may differ by seconds from rank to rank
 #ifndef BEAR_CMAC_GROUP
 #define BEAR_CMAC_GROUP 5
 #endif

@@ -967,7 +967,7 @@ void fetch_kernel_errors(bear_cuda_renderer *r)
   if (!bits) return;
   CK(cudaMemsetAsync(r->lay.err_flag, 0, sizeof(int), r->stream));
   r->h_err[0] = 0;
-  if (bits & kErrPeerTimeout) throw CudaFail{"shared scene: a peer GPU did not reach a synchronisation point within ~2 s "
+  if (bits & kErrPeerTimeout) throw CudaFail{"shared scene: a peer GPU did not reach a synchronisation point within ~20 s "
                                              "(every rank must make the same sequence of process calls)"};
   if (bits & kErrViewRange) throw InvalidArgument{"brir_index out of range (device tables); view 0 was rendered instead"};
   throw InvalidArgument{"a table delay is negative or longer than history_samples - 4 samples (" +

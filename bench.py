@@ -394,6 +394,7 @@ def run_ours(args, rank, world, local_rank):
     clocks = ClockSampler(local_rank)
     if rank == 0:
         clocks.start()
+    barrier()                 # the ranks' host-side set-up took different times: start the shared calls together
     for _ in range(100):      # a fixed count: every rank must issue the same number of collectives
         step()
     r.synchronize()
@@ -415,6 +416,7 @@ def run_ours(args, rank, world, local_rank):
     # ---- end to end: pinned host buffers through the host-buffer entry point -------------------
     leg.make_pinned(receives=(rank == 0))
     e2e_steps = max(3, min(args.steps, 10))
+    barrier()
     for _ in range(2):
         leg.step_e2e()
     ms_e2e = timed(leg.step_e2e, e2e_steps)
@@ -436,6 +438,7 @@ def run_ours(args, rank, world, local_rank):
             h_frames[:, c0:c0 + 64] = np.clip(np.round(leg.audio[c0:c0 + 64].T * 32768.0), -32768, 32767)
         tracks = np.arange(mine, dtype=np.int32)
         step_s16 = lambda: r.process_batch_frames(h_frames, tracks, leg.h_tb, output=leg.h_out)
+        barrier()
         step_s16()
         ms_s16 = timed(step_s16, e2e_steps)
         s16_bytes = h_frames.nbytes + sum(v.nbytes for v in leg.tb.values())

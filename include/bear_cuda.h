@@ -257,7 +257,7 @@ int bear_cuda_synchronize(bear_cuda_renderer *r);
  *     root < 0 the partial mixes are all-reduced with NCCL and every rank holds the result.  Either
  *     way per chunk of periods, so `output` / audio_out of the root (of every rank) holds the whole
  *     scene's render.  On other ranks the process calls accept output == NULL.
- *   A rank that does not reach a synchronisation point within ~2 s makes its peers' next
+ *   A rank that does not reach a synchronisation point within ~20 s makes its peers' next
  *   bear_cuda_synchronize (or host-buffer call) fail with BEAR_CUDA_ERR_CUDA instead of hanging.
  * Every rank must make the same sequence of process calls (same T, same chunking).  NCCL is bound at
  * run time (dlopen of libnccl.so.2: the copy already in the process, e.g. PyTorch's, else the
