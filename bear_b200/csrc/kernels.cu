@@ -3,21 +3,32 @@
 // FFTs (DESIGN.md "Kernels").
 //
 // Signal flow per call of T periods (reference: visr_bear/src/dsp.cpp:117-205):
-//   mix_kernel        x -> per-ear Lagrange-3 delay -> ramped gain mix -> direct bus partials (48 ch)
-//                     x -> ramped gain mix -> diffuse partials (24 ch)          [a2,a3,a4,a7]
+//   mix_prep_kernel   per (period, channel): delay ramps in samples, the set of loudspeakers with a non-zero
+//                     gain, a 128-byte record of <= 6 (start, delta) gain slots; sort key = the set
+//   mix_order_kernel  channels of a period sorted by set -> runs of channels that share their slots
+//   mix_kernel        x -> per-ear Lagrange-3 delay -> ramped gain mix -> direct bus (48 rows)
+//                     x -> ramped gain mix -> diffuse bus (24 rows); slot sums added per run   [a2,a3,a4,a7]
+//   mix_dense_kernel  the same for channels with more than 6 non-zero loudspeakers (extent)
+//   bus_sum_kernel    short launches split their channels over several CTAs per tile: partial rows summed
 //   hoa_mix_kernel    hoa in -> ramped matrix -> ambisonic bus (16 ch)                 [a10]
 //   decorrelate_kernel  diffuse bus -> overlap-save FFT conv with the decorrelators    [a5]
-//   bus_fdl_kernel    direct partials + static-delayed decorrelator outputs -> 48 ch bus -> rFFT(2B)
+//   bus_fdl_kernel    direct bus + static-delayed decorrelator outputs -> 48 ch bus -> rFFT(2B)
 //                     -> frequency-domain delay line; HOA bus (fixed delay commuted in front of
 //                     the decode filters) -> rFFT(2B) -> FDL                           [a6,a8,a12]
-//   view_group_kernel periods of the launch sorted by BRIR view -> work items of <= 6 periods
+//   view_group_kernel periods of the launch sorted by BRIR view -> work items of <= 5 periods
 //   cmac_kernel       Y[e] = sum_{l,p} FDL[2l+e][k-p] * H[view][2l+e][p] (+ HOA decode terms),
 //                     for the new view and, in a view-change block, the old one; one filter load
 //                     serves all periods of a work item                               [a9,a11]
 //   ifft_out_kernel   sum partial spectra -> irFFT -> overlap-save discard -> view crossfade -> out [a9,a13]
 //   carry_kernel      moves histories / table state / the last P delay-line spectra to the front
 //   unpack_kernel     single-period host call: scatters the packed upload (audio + tables)
+//   frames_kernel     interleaved file frames (float / 16-, 24-, 32-bit PCM) -> planar input rows
 //   control_kernel    optional: the Control graph's table producers on the device      [a15]
+//   validate_views_kernel  device-resident tables: view indices checked before they index the filters
+// One scene on several GPUs (bear_cuda_comm_connect): peer_sync_kernel (counters in the peers' memory),
+//   bus_gather_kernel / bus_gather_thin_kernel (this rank's loudspeakers' rows summed over all ranks,
+//   peers read over NVLink with ordinary loads), out_sum_kernel (stereo partial mixes on the receiver).
+// Every bulk copy (cp.async.bulk) in this file reads this GPU's own memory; there is no multicast.
 #include "kernels.cuh"
 
 #include <type_traits>
