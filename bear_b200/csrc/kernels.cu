@@ -484,7 +484,7 @@ void launch_filter_fft(const float *taps, int n_filters, int taps_len, int B, in
 
 // mix_prep_kernel: the record and the sort key of every (period, channel).
 // Record (kMixRecWords = 8 + 4 kMixSlots words):
-//   [0..3]   per-ear delay ramp in samples: d0L, ddL, d0R, ddR (validated, then clamped to the history)
+//   [0..3]   per-ear delay ramp in samples: d0L, d0R, ddL, ddR (validated, then clamped to the history)
 //   [4]      number of slots | has_diffuse << 8        [5], [6] loudspeaker of slots 0..3, 4.. (bytes; 255 = unused)
 //   [8..]    direct gains, slot pairs:  (g0[2i], g0[2i+1], dg[2i], dg[2i+1]),  i = 0 .. kMixSlots/2 - 1
 //   then     diffuse gains, same layout (objects only)
@@ -553,7 +553,7 @@ __global__ void __launch_bounds__(kPrepThreads) mix_prep_kernel(Layout p, int T)
       if (!(a1 >= 0.f && a1 <= dmax) || !(b1 >= 0.f && b1 <= dmax)) atomicOr(p.err_flag, kErrDelayRange);
       a0 = fminf(fmaxf(a0, 0.f), dmax); a1 = fminf(fmaxf(a1, 0.f), dmax);
       b0 = fminf(fmaxf(b0, 0.f), dmax); b1 = fminf(fmaxf(b1, 0.f), dmax);
-      rec[0] = make_float4(a0, a1 - a0, b0, b1 - b0);
+      rec[0] = make_float4(a0, b0, a1 - a0, b1 - b0);
     }
     unsigned *keys = p.mix_keys + (size_t)k * C;
     if (ns > kMixSlots) {
@@ -896,7 +896,11 @@ __global__ void __launch_bounds__(kMixTile, BEAR_MIX_MINBLOCKS) mix_kernel(Layou
     for (int ci = 0; ci < min(nchunks, kMixStages - 1); ci++) request(ci);
   auto lagrange = [&](const float *rec, const float *xr) {
     const float4 dl = *reinterpret_cast<const float4 *>(rec);
-    return delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
+    // ramped_delay for both ears: the two products in one packed multiply (the same IEEE products), the
+    // sums stay scalar -- a packed add behind a packed multiply would be contracted into FFMA2
+    float pa, pb;
+    unpack2(mul2(pack2(dl.z, dl.w), splat2(rd)), pa, pb);
+    return delayed_read2(xr, __fadd_rn(dl.x, pa), xr, __fadd_rn(dl.y, pb));
   };
   for (int ci = 0; ci < nchunks; ci++) {
     const int st = ci % kMixStages;
@@ -1047,7 +1051,7 @@ __global__ void __launch_bounds__(kMixTile) mix_dense_kernel(Layout p, int T)
       for (int j = 0; j < cnt; j++) {
         const float *xr = xt + j * XW + p.hist + tid;
         const float4 dl = *reinterpret_cast<const float4 *>(sdl + 4 * j);
-        const f32x2 x2 = delayed_read2(xr, ramped_delay(dl.x, dl.y, rd), xr, ramped_delay(dl.z, dl.w, rd));
+        const f32x2 x2 = delayed_read2(xr, ramped_delay(dl.x, dl.z, rd), xr, ramped_delay(dl.y, dl.w, rd));
         const float4 *g4 = reinterpret_cast<const float4 *>(sg + j * 4 * kMaxSpeakers);
 #pragma unroll
         for (int i = 0; i < kMaxSpeakers / 2; i++) {
